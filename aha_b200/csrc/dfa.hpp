@@ -1,0 +1,237 @@
+// dfa.hpp -- flattening of a compiled Aha::AC (cedar double array + @fails + @output + @key_lens)
+// into the dense byte-class DFA the GPU scans, and its serialised ("blob") form.
+//
+// delta[s][c] is the closure of the goto/fail loop of ACX#match_ (ac.cr:176-192):
+//     delta(s,b) = child(s,b)                      if the goto edge exists (cedar.cr:441-447)
+//                = 0                               if s is the root
+//                = delta(fails[s], b)              otherwise
+// States are the label != 0 trie nodes, renumbered in BFS order (root = 0) so that shallow (hot)
+// states have small ids.  Every entry carries three bits about its TARGET state / edge:
+//     kOut  target has a non-empty output list (ACX#fetch, ac.cr:265-278, rule Q1)
+//     kEnd  target is_end? (raw flag bits, cedar.cr:657-660, Q2/Q4) -- drives match_longest
+//     kGoto the edge is a real goto edge (not derived through fail links)
+#pragma once
+#include <cstdint>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "host_cedar.hpp"
+
+namespace aha {
+
+constexpr uint32_t kOut = 0x80000000u;
+constexpr uint32_t kEnd = 0x40000000u;
+constexpr uint32_t kGoto = 0x20000000u;
+constexpr uint32_t kStateMask = 0x1FFFFFFFu;
+constexpr uint64_t kBlobMagic = 0x3130414644414841ull;  // "AHADFA01"
+
+struct BlobHeader {
+  uint64_t magic;
+  uint32_t version;
+  uint32_t n_classes;
+  uint64_t n_states;
+  uint64_t n_keys;
+  uint64_t n_out;
+  uint32_t max_key_len;
+  uint32_t reserved;
+  uint64_t off_classmap;  // u8[256]
+  uint64_t off_delta;     // u32[n_states * n_classes]
+  uint64_t off_out_off;   // u32[n_states + 1]
+  uint64_t off_out_val;   // i32[n_out]
+  uint64_t off_key_len;   // u32[n_keys]
+  uint64_t off_key_tail;  // u32[n_keys]: non-continuation bytes in key[1..]: char-unit start remap
+  uint64_t off_depth;     // u16[n_states]: depth in bytes (diagnostics, hot-set selection)
+  uint64_t total_bytes;
+};
+
+inline uint64_t align16(uint64_t x) { return (x + 15) & ~uint64_t(15); }
+
+// View over a blob (host or device pointer arithmetic only)
+struct DfaView {
+  const uint8_t* classmap;
+  const uint32_t* delta;
+  const uint32_t* out_off;
+  const int32_t* out_val;
+  const uint32_t* key_len;
+  const uint32_t* key_tail;
+  const uint16_t* depth;
+  uint32_t n_classes;
+  uint32_t max_key_len;
+  uint64_t n_states, n_keys, n_out;
+};
+
+inline DfaView view_of(const BlobHeader& h, const uint8_t* base) {
+  DfaView v;
+  v.classmap = base + h.off_classmap;
+  v.delta = reinterpret_cast<const uint32_t*>(base + h.off_delta);
+  v.out_off = reinterpret_cast<const uint32_t*>(base + h.off_out_off);
+  v.out_val = reinterpret_cast<const int32_t*>(base + h.off_out_val);
+  v.key_len = reinterpret_cast<const uint32_t*>(base + h.off_key_len);
+  v.key_tail = reinterpret_cast<const uint32_t*>(base + h.off_key_tail);
+  v.depth = reinterpret_cast<const uint16_t*>(base + h.off_depth);
+  v.n_classes = h.n_classes;
+  v.max_key_len = h.max_key_len;
+  v.n_states = h.n_states;
+  v.n_keys = h.n_keys;
+  v.n_out = h.n_out;
+  return v;
+}
+
+// Flatten.  Returns false + err on malformed input.
+inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* fails, const CedarOut* output,
+                    const uint32_t* key_lens, int64_t n_keys, std::vector<uint8_t>* blob, std::string* err) {
+  auto base_of = [&](int32_t id) { return -(nodes[id].value + 1); };
+  auto is_end = [&](int32_t id) { return (nodes[id].flags & 0x200) != 0 || nodes[id].child == 0; };
+  if (array_size < 256) {
+    *err = "array_size < 256";
+    return false;
+  }
+  // 1. BFS renumbering over the sibling lists (cedar.cr:450-463), same order ACX.compile walks
+  std::vector<int32_t> slot_of;              // state -> cedar slot
+  std::vector<int32_t> parent;               // state -> parent state
+  std::vector<uint8_t> label;                // state -> incoming label
+  std::vector<int32_t> state_of(array_size, -1);
+  slot_of.push_back(0);
+  parent.push_back(0);
+  label.push_back(0);
+  state_of[0] = 0;
+  bool used[256] = {false};
+  for (size_t s = 0; s < slot_of.size(); ++s) {
+    const int32_t id = slot_of[s];
+    const int32_t b = base_of(id);
+    uint8_t sib = nodes[id].child;
+    if (sib == 0 && b > 0) sib = nodes[b].sibling;
+    while (sib != 0) {
+      const int32_t to = b ^ sib;
+      if (to < 0) break;
+      if (to >= array_size || state_of[to] >= 0) {
+        *err = "corrupt sibling list";
+        return false;
+      }
+      state_of[to] = static_cast<int32_t>(slot_of.size());
+      slot_of.push_back(to);
+      parent.push_back(static_cast<int32_t>(s));
+      label.push_back(sib);
+      used[sib] = true;
+      sib = nodes[to].sibling;
+    }
+  }
+  const uint64_t S = slot_of.size();
+  if (S > kStateMask) {
+    *err = "too many states";
+    return false;
+  }
+  // 2. byte classes: every byte used as a label is its own class; all others (incl. NUL, Q6) share class 0
+  uint8_t classmap[256];
+  uint32_t C = 1;
+  for (int b = 0; b < 256; ++b) classmap[b] = (b != 0 && used[b]) ? static_cast<uint8_t>(C++) : 0;
+  // 3. per-state facts
+  std::vector<uint16_t> depth(S, 0);
+  std::vector<uint32_t> tail(S, 0);  // non-continuation bytes among path bytes at index >= 1
+  std::vector<uint32_t> sflags(S, 0);
+  std::vector<uint32_t> out_off(S + 1, 0);
+  std::vector<int32_t> out_val;
+  uint32_t max_depth = 0;
+  for (uint64_t s = 1; s < S; ++s) {
+    const uint32_t d = depth[parent[s]] + 1u;
+    depth[s] = static_cast<uint16_t>(d > 65535u ? 65535u : d);
+    if (d > max_depth) max_depth = d;
+    tail[s] = tail[parent[s]] + ((d >= 2 && (label[s] & 0xC0) != 0x80) ? 1u : 0u);
+  }
+  std::vector<uint32_t> key_tail(n_keys > 0 ? n_keys : 1, 0);
+  for (uint64_t s = 0; s < S; ++s) {
+    out_off[s] = static_cast<uint32_t>(out_val.size());
+    if (s == 0) continue;
+    const int32_t id = slot_of[s];
+    if (is_end(id)) sflags[s] |= kEnd;
+    // ACX#fetch (ac.cr:265-278): walk while value >= 0, follow next while >= 0
+    int32_t e = id;
+    int guard = 0;
+    while (output[e].value >= 0) {
+      const int32_t v = output[e].value;
+      if (v >= n_keys) {
+        *err = "output value out of range";
+        return false;
+      }
+      if (key_lens[v] < 0x7FFFFFFFu) out_val.push_back(v);
+      if (!(output[e].next >= 0)) break;
+      e = output[e].next;
+      if (++guard > 1 << 20) {
+        *err = "output chain loop";
+        return false;
+      }
+    }
+    if (out_val.size() > out_off[s]) sflags[s] |= kOut;
+    if (output[id].value >= 0) key_tail[output[id].value] = tail[s];
+  }
+  out_off[S] = static_cast<uint32_t>(out_val.size());
+  // 4. layout
+  BlobHeader h;
+  memset(&h, 0, sizeof(h));
+  h.magic = kBlobMagic;
+  h.version = 1;
+  h.n_classes = C;
+  h.n_states = S;
+  h.n_keys = static_cast<uint64_t>(n_keys);
+  h.n_out = out_val.size();
+  h.max_key_len = max_depth;
+  uint64_t off = align16(sizeof(BlobHeader));
+  h.off_classmap = off; off = align16(off + 256);
+  h.off_delta = off; off = align16(off + S * C * 4);
+  h.off_out_off = off; off = align16(off + (S + 1) * 4);
+  h.off_out_val = off; off = align16(off + out_val.size() * 4);
+  h.off_key_len = off; off = align16(off + static_cast<uint64_t>(n_keys) * 4);
+  h.off_key_tail = off; off = align16(off + static_cast<uint64_t>(n_keys) * 4);
+  h.off_depth = off; off = align16(off + S * 2);
+  h.total_bytes = off;
+  blob->assign(off, 0);
+  uint8_t* p = blob->data();
+  memcpy(p, &h, sizeof(h));
+  memcpy(p + h.off_classmap, classmap, 256);
+  memcpy(p + h.off_out_off, out_off.data(), (S + 1) * 4);
+  if (!out_val.empty()) memcpy(p + h.off_out_val, out_val.data(), out_val.size() * 4);
+  if (n_keys > 0) {
+    memcpy(p + h.off_key_len, key_lens, static_cast<uint64_t>(n_keys) * 4);
+    memcpy(p + h.off_key_tail, key_tail.data(), static_cast<uint64_t>(n_keys) * 4);
+  }
+  memcpy(p + h.off_depth, depth.data(), S * 2);
+  // 5. delta closure in BFS order: fail targets are shallower, hence already complete; the
+  //    children of a state are contiguous in BFS numbering, so one cursor finds its goto edges.
+  uint32_t* delta = reinterpret_cast<uint32_t*>(p + h.off_delta);
+  uint64_t cursor = 1;
+  for (uint64_t s = 0; s < S; ++s) {
+    uint32_t* row = delta + s * C;
+    if (s == 0) {
+      for (uint32_t c = 0; c < C; ++c) row[c] = 0;
+    } else {
+      const int32_t f = fails[slot_of[s]];
+      if (f < 0 || f >= array_size || state_of[f] < 0 || static_cast<uint64_t>(state_of[f]) >= s) {
+        *err = "fail link does not point to an earlier state";
+        return false;
+      }
+      const uint32_t* frow = delta + static_cast<uint64_t>(state_of[f]) * C;
+      for (uint32_t c = 0; c < C; ++c) row[c] = frow[c] & ~kGoto;
+    }
+    while (cursor < S && static_cast<uint64_t>(parent[cursor]) == s) {
+      row[classmap[label[cursor]]] = static_cast<uint32_t>(cursor) | sflags[cursor] | kGoto;
+      ++cursor;
+    }
+  }
+  return true;
+}
+
+inline bool parse_blob(const uint8_t* blob, int64_t bytes, BlobHeader* h, std::string* err) {
+  if (bytes < static_cast<int64_t>(sizeof(BlobHeader))) {
+    *err = "blob too small";
+    return false;
+  }
+  memcpy(h, blob, sizeof(BlobHeader));
+  if (h->magic != kBlobMagic || h->version != 1 || h->total_bytes != static_cast<uint64_t>(bytes)) {
+    *err = "bad blob header";
+    return false;
+  }
+  return true;
+}
+
+}  // namespace aha

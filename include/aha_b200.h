@@ -1,0 +1,128 @@
+/* aha_b200.h -- C ABI of libaha_b200.so, the B200 drop-in for the Aha::AC scan path.
+ *
+ * The reference (chenkovsky/aha) is pure Crystal and has no FFI boundary; this header IS the
+ * boundary a Crystal `lib LibAhaB200` block binds (see src/aha_gpu.cr and INTEGRATION.md).
+ * Every entry point names the reference code it replaces.  All functions return 0 on success,
+ * a negative aha_status otherwise; aha_b200_last_error() returns a thread-local message that
+ * the host wrapper turns into `raise` (the reference raises strings: ac.cr:66,322; cedar.cr:235,756).
+ *
+ * Ownership: inputs are borrowed for the duration of the call.  aha_dfa / aha_hits are owned by
+ * the library and released only by the *_free calls.  Offsets in aha_hit are per document and
+ * Int32 like Aha::Hit (matcher.cr:2-11): a document must be < 2^31 bytes.
+ */
+#ifndef AHA_B200_H
+#define AHA_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct aha_dfa aha_dfa;         /* flattened automaton, host copy + per-device copies */
+typedef struct aha_builder aha_builder; /* host cedar trie under construction (Aha::Cedar)   */
+
+/* == Aha::Hit (matcher.cr:2-11): [start, end) half open, value = key id */
+typedef struct aha_hit {
+  int32_t start, end, value;
+} aha_hit;
+
+/* result of one scan call */
+typedef struct aha_hits {
+  aha_hit* hits;          /* n_hits records, document order, reference emission order        */
+  int64_t n_hits;
+  int64_t* doc_hit_off;   /* n_docs + 1 offsets into hits[] (exclusive prefix of per-doc counts) */
+  int64_t n_docs;
+  int32_t on_device;      /* 1: hits/doc_hit_off are device pointers (aha_b200_scan_device)  */
+  int32_t device;
+  double scan_ms;         /* device time of the scan kernels only (CUDA events)              */
+  void* opaque;
+} aha_hits;
+
+enum aha_status {
+  AHA_OK = 0,
+  AHA_ERR_ARG = -1,       /* bad argument / contract violation (doc >= 2^31 bytes, sep_size > 256 ...) */
+  AHA_ERR_CUDA = -2,      /* CUDA runtime error */
+  AHA_ERR_KEY = -3,       /* reference raise: duplicate key, empty key, NUL in key */
+  AHA_ERR_NOMEM = -4,
+  AHA_ERR_STATE = -5      /* library not initialised / dfa not on this device */
+};
+
+/* scan mode bits */
+enum aha_mode {
+  AHA_UNITS_CHAR = 1,     /* String overloads: offsets are character indices (matcher.cr:34-46, ac.cr:305-310) */
+  AHA_SEP = 2,            /* ACX#match(seq, sep : BitArray)  (ac.cr:321-340)                           */
+  AHA_LONGEST = 4,        /* ACX#match_longest               (ac.cr:118-143, 297-303)                  */
+  AHA_INTERSECTABLE = 8,  /* match_longest(seq, true)        (ac.cr:131-137)                           */
+  AHA_TRIE_LONGEST = 16,  /* CedarX#match_longest(String, ignore_case, sep) (cedar.cr:1075-1121)       */
+  AHA_IGNORE_CASE = 32,   /* with AHA_TRIE_LONGEST           (cedar.cr:995-996)                        */
+  AHA_COUNT_ONLY = 64     /* no hit records, only doc_hit_off (bench / sizing)                         */
+};
+
+/* ---- library / devices ------------------------------------------------------------------- */
+/* Selects the CUDA devices this process scans on (one per process under torchrun; n > 1 lets a
+ * single process drive several GPUs).  devices == NULL, n == 0 -> current device only.        */
+int32_t aha_b200_init(const int32_t* devices, int32_t n);
+const char* aha_b200_last_error(void);
+int32_t aha_b200_version(void);
+
+/* ---- host builder: Aha::Cedar#insert + Aha::AC.compile where Crystal is absent ----------- */
+/* Aha::Cedar.new (cedar.cr:198-221) */
+int32_t aha_b200_builder_new(aha_builder** out);
+/* Aha::Cedar#insert(Bytes) (cedar.cr:755-778); *id_out = key id.  AHA_ERR_KEY on empty key / NUL byte. */
+int32_t aha_b200_builder_insert(aha_builder* b, const uint8_t* key, int32_t len, int32_t* id_out);
+/* Aha::Cedar#[]?(Bytes) (cedar.cr:822-828); *id_out = -1 when absent */
+int32_t aha_b200_builder_lookup(const aha_builder* b, const uint8_t* key, int32_t len, int32_t* id_out);
+/* Aha::Cedar#[](Int) (cedar.cr:747-749): key bytes of id into out[cap]; *len_out = length */
+int32_t aha_b200_builder_key(const aha_builder* b, int32_t id, uint8_t* out, int32_t cap, int32_t* len_out);
+/* raw views of the arrays the reference holds after AC.compile (ac.cr:35-39); valid until the
+ * next insert / free.  nodes: 12-byte Node(Int32)[array_size]; fails: Int32[array_size];
+ * output: {next,value}[array_size]; key_lens: UInt32[n_keys].  Runs ACX.compile(da) (ac.cr:71-112). */
+int32_t aha_b200_builder_compile(aha_builder* b, const void** nodes, int64_t* array_size, const int32_t** fails,
+                                 const int32_t** output, const uint32_t** key_lens, int64_t* n_keys);
+void aha_b200_builder_free(aha_builder* b);
+
+/* ---- automaton --------------------------------------------------------------------------- */
+/* Flattens the arrays of a compiled Aha::AC (@da.array, @fails, @output, @key_lens: ac.cr:35-39,
+ * cedar.cr:29-36,147-148) into the dense byte-class DFA and uploads it to every selected device. */
+int32_t aha_b200_dfa_from_cedar(const void* nodes, int64_t array_size, const int32_t* fails, const int32_t* output,
+                                const uint32_t* key_lens, int64_t n_keys, aha_dfa** out);
+/* Aha::AC.compile(keys) (ac.cr:62-69) in one call: keys concatenated, key_off has n_keys+1 entries.
+ * AHA_ERR_KEY with "key:... appear twice." on a duplicate, like the reference.                */
+int32_t aha_b200_dfa_compile(const uint8_t* keys, const int64_t* key_off, int64_t n_keys, aha_dfa** out);
+/* serialised DFA (host memory, library-owned until dfa_free) for broadcast / caching */
+int32_t aha_b200_dfa_blob(const aha_dfa* d, const uint8_t** blob, int64_t* bytes);
+/* rebuild from a blob in host memory (e.g. received on another rank) and upload */
+int32_t aha_b200_dfa_from_blob(const uint8_t* blob, int64_t bytes, aha_dfa** out);
+/* rebuild from a blob already resident on the current device (after ncclBroadcast) */
+int32_t aha_b200_dfa_from_device_blob(const void* dev_blob, int64_t bytes, aha_dfa** out);
+/* info: 0 n_states, 1 n_classes, 2 n_keys, 3 max_key_len, 4 n_out_entries, 5 blob bytes,
+ *       6 hot states resident in shared memory, 7 entry width of the global table in bytes   */
+int64_t aha_b200_dfa_info(const aha_dfa* d, int32_t what);
+void aha_b200_dfa_free(aha_dfa* d);
+
+/* ---- scan -------------------------------------------------------------------------------- */
+/* Batch form of ACX#match / match(sep) / match_longest (ac.cr:280-340) and
+ * CedarX#match_longest (cedar.cr:1075-1121) over n_docs documents stored back to back in HOST
+ * memory: document i = text[doc_off[i] .. doc_off[i+1]).  Copies the text to the device(s),
+ * scans, copies the hits back (pinned).  sep_bits: 256-bit set, bit b of byte b>>3; sep_size =
+ * BitArray size (bytes >= sep_size always pass: ac.cr:326,333).                               */
+int32_t aha_b200_scan(const aha_dfa* d, const uint8_t* text, const int64_t* doc_off, int64_t n_docs, uint32_t mode,
+                      const uint8_t* sep_bits, int32_t sep_size, aha_hits** out);
+/* Same, text and doc_off already in the current device's memory; results stay on the device.
+ * stream: a cudaStream_t (0 = default stream).                                                */
+int32_t aha_b200_scan_device(const aha_dfa* d, const void* dev_text, const void* dev_doc_off, int64_t n_docs,
+                             int64_t total_bytes, uint32_t mode, const uint8_t* sep_bits, int32_t sep_size,
+                             void* stream, aha_hits** out);
+void aha_b200_hits_free(aha_hits* h);
+
+/* ---- synthetic corpora: counter-based, identical bytes on host and device -- */
+enum aha_corpus { AHA_CORPUS_EN = 0, AHA_CORPUS_ZH = 1, AHA_CORPUS_MIX = 2 };
+/* fills out[0..bytes) with corpus text starting at absolute byte `first` of the stream */
+int32_t aha_b200_gen_text_host(int32_t corpus, uint64_t seed, int64_t first, int64_t bytes, uint8_t* out);
+int32_t aha_b200_gen_text_device(int32_t corpus, uint64_t seed, int64_t first, int64_t bytes, void* dev_out,
+                                 void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AHA_B200_H */

@@ -1,0 +1,242 @@
+// api.cu -- extern "C" entry points of libaha_b200.so (see include/aha_b200.h).
+#include <cub/device/device_scan.cuh>
+#include <cub/iterator/transform_input_iterator.cuh>
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+
+#include "api_internal.cuh"
+#include "gen.cuh"
+#include "scan_common.cuh"
+#include "scan_v1.cuh"
+#include "scan_fused.cuh"
+
+namespace aha {
+
+thread_local std::string g_err;
+static std::mutex g_mu;
+static std::vector<int> g_devices;  // devices selected by aha_b200_init
+static int g_impl = -1;             // 0: two-pass v1 kernels, 1: fused kernel (default); env AHA_B200_IMPL
+
+static int scan_impl() {
+  if (g_impl < 0) {
+    const char* e = getenv("AHA_B200_IMPL");
+    g_impl = (e && e[0] == '0') ? 0 : 1;
+  }
+  return g_impl;
+}
+
+static int32_t ensure_devices() {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g_devices.empty()) return AHA_OK;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    return set_err(AHA_ERR_CUDA, std::string("no CUDA device: libaha_b200 has no CPU fallback (") +
+                                     cudaGetErrorString(e) + ")");
+  }
+  int cur = 0;
+  AHA_CUDA(cudaGetDevice(&cur));
+  g_devices.push_back(cur);
+  return AHA_OK;
+}
+
+static int32_t upload(aha_dfa* d) {
+  int32_t rc = ensure_devices();
+  if (rc) return rc;
+  int prev = 0;
+  AHA_CUDA(cudaGetDevice(&prev));
+  for (int dev : g_devices) {
+    AHA_CUDA(cudaSetDevice(dev));
+    DeviceDfa dd;
+    dd.device = dev;
+    AHA_CUDA(cudaMalloc(&dd.blob, d->blob.size()));
+    AHA_CUDA(cudaMemcpy(dd.blob, d->blob.data(), d->blob.size(), cudaMemcpyHostToDevice));
+    dd.view = view_of(d->header, dd.blob);
+    rc = build_hot_table(d, &dd);
+    if (rc) return rc;
+    d->dev.push_back(dd);
+  }
+  AHA_CUDA(cudaSetDevice(prev));
+  return AHA_OK;
+}
+
+static int32_t finish_dfa(std::unique_ptr<aha_dfa> d, aha_dfa** out) {
+  std::string err;
+  if (!parse_blob(d->blob.data(), (int64_t)d->blob.size(), &d->header, &err)) return set_err(AHA_ERR_ARG, err);
+  int32_t rc = upload(d.get());
+  if (rc) return rc;
+  *out = d.release();
+  return AHA_OK;
+}
+
+}  // namespace aha
+
+using namespace aha;
+
+extern "C" {
+
+int32_t aha_b200_version(void) { return 100; }
+const char* aha_b200_last_error(void) { return g_err.c_str(); }
+
+int32_t aha_b200_init(const int32_t* devices, int32_t n) {
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0)
+    return set_err(AHA_ERR_CUDA, std::string("no CUDA device: libaha_b200 has no CPU fallback (") + cudaGetErrorString(e) + ")");
+  std::lock_guard<std::mutex> lk(g_mu);
+  g_devices.clear();
+  if (devices == nullptr || n <= 0) {
+    int cur = 0;
+    AHA_CUDA(cudaGetDevice(&cur));
+    g_devices.push_back(cur);
+  } else {
+    for (int i = 0; i < n; ++i) {
+      if (devices[i] < 0 || devices[i] >= count) return set_err(AHA_ERR_ARG, "device index out of range");
+      g_devices.push_back(devices[i]);
+    }
+  }
+  return AHA_OK;
+}
+
+// ---- builder ------------------------------------------------------------------------------
+int32_t aha_b200_builder_new(aha_builder** out) {
+  if (!out) return set_err(AHA_ERR_ARG, "out is null");
+  *out = new aha_builder();
+  return AHA_OK;
+}
+int32_t aha_b200_builder_insert(aha_builder* b, const uint8_t* key, int32_t len, int32_t* id_out) {
+  if (!b || (!key && len > 0) || len < 0) return set_err(AHA_ERR_ARG, "bad argument");
+  int32_t id = b->cedar.insert(key, len);
+  if (id == -2) return set_err(AHA_ERR_KEY, b->cedar.error());
+  if (id_out) *id_out = id;
+  return AHA_OK;
+}
+int32_t aha_b200_builder_lookup(const aha_builder* b, const uint8_t* key, int32_t len, int32_t* id_out) {
+  if (!b || !id_out || len < 0) return set_err(AHA_ERR_ARG, "bad argument");
+  *id_out = b->cedar.find(key, len);
+  return AHA_OK;
+}
+int32_t aha_b200_builder_key(const aha_builder* b, int32_t id, uint8_t* out, int32_t cap, int32_t* len_out) {
+  if (!b || !len_out) return set_err(AHA_ERR_ARG, "bad argument");
+  std::string k;
+  if (!b->cedar.key_of(id, &k)) return set_err(AHA_ERR_ARG, "Index out of bounds");  // IndexError, cedar.cr:832
+  *len_out = (int32_t)k.size();
+  if ((int32_t)k.size() > cap) return set_err(AHA_ERR_ARG, "buffer too small");
+  memcpy(out, k.data(), k.size());
+  return AHA_OK;
+}
+int32_t aha_b200_builder_compile(aha_builder* b, const void** nodes, int64_t* array_size, const int32_t** fails,
+                                 const int32_t** output, const uint32_t** key_lens, int64_t* n_keys) {
+  if (!b) return set_err(AHA_ERR_ARG, "builder is null");
+  b->ac.compile(b->cedar);
+  if (nodes) *nodes = b->cedar.nodes();
+  if (array_size) *array_size = b->cedar.array_size();
+  if (fails) *fails = b->ac.fails.data();
+  if (output) *output = reinterpret_cast<const int32_t*>(b->ac.output.data());
+  if (key_lens) *key_lens = b->ac.key_lens.data();
+  if (n_keys) *n_keys = b->cedar.leaf_size();
+  return AHA_OK;
+}
+void aha_b200_builder_free(aha_builder* b) { delete b; }
+
+// ---- automaton ----------------------------------------------------------------------------
+int32_t aha_b200_dfa_from_cedar(const void* nodes, int64_t array_size, const int32_t* fails, const int32_t* output,
+                                const uint32_t* key_lens, int64_t n_keys, aha_dfa** out) {
+  if (!nodes || !fails || !output || (!key_lens && n_keys > 0) || !out) return set_err(AHA_ERR_ARG, "null argument");
+  std::unique_ptr<aha_dfa> d(new aha_dfa());
+  std::string err;
+  if (!flatten(static_cast<const CedarNode*>(nodes), array_size, fails, reinterpret_cast<const CedarOut*>(output),
+               key_lens, n_keys, &d->blob, &err))
+    return set_err(AHA_ERR_ARG, err);
+  return finish_dfa(std::move(d), out);
+}
+
+int32_t aha_b200_flatten_host(const void* nodes, int64_t array_size, const int32_t* fails, const int32_t* output,
+                              const uint32_t* key_lens, int64_t n_keys, uint8_t** blob, int64_t* bytes) {
+  if (!nodes || !fails || !output || (!key_lens && n_keys > 0) || !blob || !bytes) return set_err(AHA_ERR_ARG, "null argument");
+  std::vector<uint8_t> v;
+  std::string err;
+  if (!flatten(static_cast<const CedarNode*>(nodes), array_size, fails, reinterpret_cast<const CedarOut*>(output),
+               key_lens, n_keys, &v, &err))
+    return set_err(AHA_ERR_ARG, err);
+  *blob = static_cast<uint8_t*>(malloc(v.size()));
+  if (!*blob) return set_err(AHA_ERR_NOMEM, "malloc failed");
+  memcpy(*blob, v.data(), v.size());
+  *bytes = (int64_t)v.size();
+  return AHA_OK;
+}
+void aha_b200_blob_free(uint8_t* blob) { free(blob); }
+
+int32_t aha_b200_dfa_compile(const uint8_t* keys, const int64_t* key_off, int64_t n_keys, aha_dfa** out) {
+  if ((!keys && n_keys > 0) || !key_off || !out || n_keys < 0) return set_err(AHA_ERR_ARG, "null argument");
+  aha_builder b;
+  for (int64_t i = 0; i < n_keys; ++i) {
+    const int64_t len = key_off[i + 1] - key_off[i];
+    if (len < 0 || len > INT32_MAX) return set_err(AHA_ERR_ARG, "bad key_off");
+    int32_t id = b.cedar.insert(keys + key_off[i], (int32_t)len);
+    if (id == -2) return set_err(AHA_ERR_KEY, b.cedar.error());
+    if (id != i)  // ac.cr:66
+      return set_err(AHA_ERR_KEY, "key:" + std::string(reinterpret_cast<const char*>(keys + key_off[i]), (size_t)len) + " appear twice.");
+  }
+  b.ac.compile(b.cedar);
+  return aha_b200_dfa_from_cedar(b.cedar.nodes(), b.cedar.array_size(), b.ac.fails.data(),
+                                 reinterpret_cast<const int32_t*>(b.ac.output.data()), b.ac.key_lens.data(),
+                                 b.cedar.leaf_size(), out);
+}
+
+int32_t aha_b200_dfa_blob(const aha_dfa* d, const uint8_t** blob, int64_t* bytes) {
+  if (!d || !blob || !bytes) return set_err(AHA_ERR_ARG, "null argument");
+  *blob = d->blob.data();
+  *bytes = (int64_t)d->blob.size();
+  return AHA_OK;
+}
+
+int32_t aha_b200_dfa_from_blob(const uint8_t* blob, int64_t bytes, aha_dfa** out) {
+  if (!blob || bytes <= 0 || !out) return set_err(AHA_ERR_ARG, "null argument");
+  std::unique_ptr<aha_dfa> d(new aha_dfa());
+  d->blob.assign(blob, blob + bytes);
+  return finish_dfa(std::move(d), out);
+}
+
+int32_t aha_b200_dfa_from_device_blob(const void* dev_blob, int64_t bytes, aha_dfa** out) {
+  if (!dev_blob || bytes <= 0 || !out) return set_err(AHA_ERR_ARG, "null argument");
+  std::unique_ptr<aha_dfa> d(new aha_dfa());
+  d->blob.resize((size_t)bytes);
+  AHA_CUDA(cudaMemcpy(d->blob.data(), dev_blob, (size_t)bytes, cudaMemcpyDeviceToHost));
+  return finish_dfa(std::move(d), out);
+}
+
+int64_t aha_b200_dfa_info(const aha_dfa* d, int32_t what) {
+  if (!d) return -1;
+  switch (what) {
+    case 0: return (int64_t)d->header.n_states;
+    case 1: return d->header.n_classes;
+    case 2: return (int64_t)d->header.n_keys;
+    case 3: return d->header.max_key_len;
+    case 4: return (int64_t)d->header.n_out;
+    case 5: return (int64_t)d->header.total_bytes;
+    case 6: return d->dev.empty() ? 0 : d->dev[0].hot.n_hot;
+    case 7: return 4;
+    default: return -1;
+  }
+}
+
+void aha_b200_dfa_free(aha_dfa* d) {
+  if (!d) return;
+  int prev = 0;
+  cudaGetDevice(&prev);
+  for (auto& dd : d->dev) {
+    cudaSetDevice(dd.device);
+    cudaFree(dd.blob);
+    if (dd.hot.dev_rows) cudaFree(dd.hot.dev_rows);
+  }
+  cudaSetDevice(prev);
+  delete d;
+}
+
+}  // extern "C"
+
+#include "api_scan.cuh"

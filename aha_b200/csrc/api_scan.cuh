@@ -1,0 +1,302 @@
+// api_scan.cuh -- scan / hits / generator entry points (included at the end of api.cu).
+#pragma once
+
+namespace aha {
+
+struct U32ToU64 {
+  __host__ __device__ __forceinline__ uint64_t operator()(const uint32_t& x) const { return (uint64_t)x; }
+};
+
+static int32_t pool_setup(int device) {
+  static std::mutex mu;
+  static std::vector<int> done;
+  std::lock_guard<std::mutex> lk(mu);
+  if (std::find(done.begin(), done.end(), device) != done.end()) return AHA_OK;
+  cudaMemPool_t pool;
+  AHA_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+  uint64_t thr = UINT64_MAX;
+  AHA_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+  done.push_back(device);
+  return AHA_OK;
+}
+
+static int32_t exclusive_sum_u32_to_u64(const uint32_t* in, uint64_t* out, int64_t n, cudaStream_t st) {
+  cub::TransformInputIterator<uint64_t, U32ToU64, const uint32_t*> it(in, U32ToU64());
+  size_t tmp_bytes = 0;
+  AHA_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, it, out, n, st));
+  void* tmp = nullptr;
+  AHA_CUDA(cudaMallocAsync(&tmp, tmp_bytes ? tmp_bytes : 16, st));
+  AHA_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, it, out, n, st));
+  AHA_CUDA(cudaFreeAsync(tmp, st));
+  return AHA_OK;
+}
+
+static void fill_params(ScanParams* p, const DeviceDfa* dd, const void* dev_text, const void* dev_doc_off, int64_t n_docs,
+                        int64_t total, uint32_t mode, const uint8_t* sep_bits, int32_t sep_size) {
+  memset(p, 0, sizeof(*p));
+  p->text = static_cast<const uint8_t*>(dev_text);
+  p->total = total;
+  p->doc_off = static_cast<const int64_t*>(dev_doc_off);
+  p->n_docs = n_docs;
+  p->classmap = dd->view.classmap;
+  p->delta = dd->view.delta;
+  p->out_off = dd->view.out_off;
+  p->out_val = dd->view.out_val;
+  p->key_len = dd->view.key_len;
+  p->key_tail = dd->view.key_tail;
+  p->C = dd->view.n_classes;
+  p->warm = dd->view.max_key_len > 0 ? dd->view.max_key_len - 1 : 0;
+  p->mode = mode;
+  p->sep_size = (uint32_t)sep_size;
+  if (sep_bits) memcpy(p->sep_bits, sep_bits, 32);
+}
+
+// two-pass baseline: count -> exclusive sum -> emit
+static int32_t run_v1(ScanParams p, cudaStream_t st, aha_hits* res, HitsOwner* own, cudaEvent_t ev0, cudaEvent_t ev1) {
+  const bool longest = (p.mode & AHA_LONGEST) != 0;
+  const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
+  p.chunk = 512;
+  p.n_chunks = (p.total + p.chunk - 1) / p.chunk;
+  const int64_t units = longest ? p.n_docs : p.n_chunks;
+  uint32_t* counts = nullptr;
+  uint64_t* offsets = nullptr;
+  uint32_t* lead_counts = nullptr;
+  uint64_t* lead_prefix = nullptr;
+  uint64_t* doc_lead = nullptr;
+  AHA_CUDA(cudaMallocAsync(&counts, (units + 1) * sizeof(uint32_t), st));
+  AHA_CUDA(cudaMallocAsync(&offsets, (units + 1) * sizeof(uint64_t), st));
+  AHA_CUDA(cudaMemsetAsync(counts, 0, (units + 1) * sizeof(uint32_t), st));
+  AHA_CUDA(cudaMallocAsync(&own->dev_doc_hit_off, (p.n_docs + 1) * sizeof(int64_t), st));
+  AHA_CUDA(cudaMemsetAsync(own->dev_doc_hit_off, 0, (p.n_docs + 1) * sizeof(int64_t), st));
+  p.counts = counts;
+  p.offsets = offsets;
+  p.doc_hit_off = static_cast<int64_t*>(own->dev_doc_hit_off);
+  const int tpb = 128;
+  AHA_CUDA(cudaEventRecord(ev0, st));
+  if (chars && !longest && p.total > 0) {
+    AHA_CUDA(cudaMallocAsync(&lead_counts, (p.n_chunks + 1) * sizeof(uint32_t), st));
+    AHA_CUDA(cudaMallocAsync(&lead_prefix, (p.n_chunks + 1) * sizeof(uint64_t), st));
+    AHA_CUDA(cudaMallocAsync(&doc_lead, (p.n_docs + 1) * sizeof(uint64_t), st));
+    count_leads_kernel<<<(unsigned)((p.n_chunks + 1 + 255) / 256), 256, 0, st>>>(p.text, p.total, p.chunk, p.n_chunks, lead_counts);
+    int32_t rc = exclusive_sum_u32_to_u64(lead_counts, lead_prefix, p.n_chunks + 1, st);
+    if (rc) return rc;
+    doc_lead_base_kernel<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(p.text, p.total, p.doc_off, p.n_docs, p.chunk,
+                                                                              lead_prefix, doc_lead);
+    p.lead_prefix = lead_prefix;
+    p.doc_lead_base = doc_lead;
+  }
+  const unsigned grid = (unsigned)((units + tpb - 1) / tpb);
+  if (units > 0) {
+    if (longest) longest_doc_kernel<false><<<grid, tpb, 0, st>>>(p);
+    else scan_v1_kernel<false><<<grid, tpb, 0, st>>>(p);
+  }
+  int32_t rc = exclusive_sum_u32_to_u64(counts, offsets, units + 1, st);
+  if (rc) return rc;
+  uint64_t total_hits = 0;
+  AHA_CUDA(cudaMemcpyAsync(&total_hits, offsets + units, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+  AHA_CUDA(cudaStreamSynchronize(st));
+  res->n_hits = (int64_t)total_hits;
+  if (!(p.mode & AHA_COUNT_ONLY)) {
+    AHA_CUDA(cudaMallocAsync(&own->dev_hits, (total_hits ? total_hits : 1) * sizeof(aha_hit), st));
+    p.hits = static_cast<aha_hit*>(own->dev_hits);
+  }
+  if (units > 0) {
+    if (longest) {
+      longest_doc_kernel<true><<<grid, tpb, 0, st>>>(p);
+      offsets_to_doc_hit_off<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(offsets, p.n_docs, p.doc_hit_off);
+    } else {
+      scan_v1_kernel<true><<<grid, tpb, 0, st>>>(p);
+    }
+  }
+  AHA_CUDA(cudaEventRecord(ev1, st));
+  AHA_CUDA(cudaGetLastError());
+  AHA_CUDA(cudaFreeAsync(counts, st));
+  AHA_CUDA(cudaFreeAsync(offsets, st));
+  if (lead_counts) {
+    AHA_CUDA(cudaFreeAsync(lead_counts, st));
+    AHA_CUDA(cudaFreeAsync(lead_prefix, st));
+    AHA_CUDA(cudaFreeAsync(doc_lead, st));
+  }
+  return AHA_OK;
+}
+
+#ifndef AHA_HAVE_FUSED
+static int32_t run_fused(ScanParams p, const DeviceDfa*, cudaStream_t st, aha_hits* res, HitsOwner* own, cudaEvent_t ev0, cudaEvent_t ev1) {
+  return run_v1(p, st, res, own, ev0, ev1);
+}
+#endif
+
+static int32_t scan_on_device(const aha_dfa* d, const void* dev_text, const void* dev_doc_off, int64_t n_docs,
+                              int64_t total, uint32_t mode, const uint8_t* sep_bits, int32_t sep_size, cudaStream_t st,
+                              aha_hits* res, HitsOwner* own) {
+  int dev = 0;
+  AHA_CUDA(cudaGetDevice(&dev));
+  const DeviceDfa* dd = d->on(dev);
+  if (!dd) return set_err(AHA_ERR_STATE, "automaton was not uploaded to the current device (aha_b200_init)");
+  if ((mode & AHA_SEP) && (sep_size > 256 || sep_size < 0 || !sep_bits))
+    return set_err(AHA_ERR_ARG, "sep BitArray size > 256 is not supported");  // ac.cr:322
+  if (mode & AHA_TRIE_LONGEST) return set_err(AHA_ERR_ARG, "AHA_TRIE_LONGEST needs a trie handle (aha_b200_trie_*)");
+  int32_t rc = pool_setup(dev);
+  if (rc) return rc;
+  own->device = dev;
+  own->stream = st;
+  ScanParams p;
+  fill_params(&p, dd, dev_text, dev_doc_off, n_docs, total, mode, sep_bits, sep_size);
+  cudaEvent_t ev0, ev1;
+  AHA_CUDA(cudaEventCreate(&ev0));
+  AHA_CUDA(cudaEventCreate(&ev1));
+  const bool fused_ok = scan_impl() == 1 && !(mode & AHA_LONGEST);
+  if (fused_ok) rc = run_fused(p, dd, st, res, own, ev0, ev1);
+  else rc = run_v1(p, st, res, own, ev0, ev1);
+  if (rc == AHA_OK) {
+    AHA_CUDA(cudaEventSynchronize(ev1));
+    float ms = 0;
+    AHA_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
+    res->scan_ms = ms;
+  }
+  cudaEventDestroy(ev0);
+  cudaEventDestroy(ev1);
+  return rc;
+}
+
+}  // namespace aha
+
+extern "C" {
+
+int32_t aha_b200_scan_device(const aha_dfa* d, const void* dev_text, const void* dev_doc_off, int64_t n_docs,
+                             int64_t total_bytes, uint32_t mode, const uint8_t* sep_bits, int32_t sep_size,
+                             void* stream, aha_hits** out) {
+  if (!d || !out || n_docs < 0 || total_bytes < 0 || (!dev_doc_off)) return set_err(AHA_ERR_ARG, "null argument");
+  std::unique_ptr<aha_hits> res(new aha_hits());
+  memset(res.get(), 0, sizeof(aha_hits));
+  HitsOwner* own = new HitsOwner();
+  res->opaque = own;
+  res->n_docs = n_docs;
+  res->on_device = 1;
+  int32_t rc = scan_on_device(d, dev_text, dev_doc_off, n_docs, total_bytes, mode, sep_bits, sep_size,
+                              static_cast<cudaStream_t>(stream), res.get(), own);
+  if (rc) {
+    aha_b200_hits_free(res.release());
+    return rc;
+  }
+  res->device = own->device;
+  res->hits = static_cast<aha_hit*>(own->dev_hits);
+  res->doc_hit_off = static_cast<int64_t*>(own->dev_doc_hit_off);
+  *out = res.release();
+  return AHA_OK;
+}
+
+int32_t aha_b200_scan(const aha_dfa* d, const uint8_t* text, const int64_t* doc_off, int64_t n_docs, uint32_t mode,
+                      const uint8_t* sep_bits, int32_t sep_size, aha_hits** out) {
+  if (!d || !out || n_docs < 0 || !doc_off || (!text && n_docs > 0 && doc_off[n_docs] > 0))
+    return set_err(AHA_ERR_ARG, "null argument");
+  if (doc_off[0] != 0) return set_err(AHA_ERR_ARG, "doc_off[0] must be 0");
+  for (int64_t i = 0; i < n_docs; ++i) {
+    const int64_t len = doc_off[i + 1] - doc_off[i];
+    if (len < 0) return set_err(AHA_ERR_ARG, "doc_off must be non-decreasing");
+    if (len > INT32_MAX) return set_err(AHA_ERR_ARG, "document >= 2^31 bytes: Aha::Hit offsets are Int32");
+  }
+  const int64_t total = doc_off[n_docs];
+  int32_t rc = ensure_devices();
+  if (rc) return rc;
+  std::unique_ptr<aha_hits> res(new aha_hits());
+  memset(res.get(), 0, sizeof(aha_hits));
+  HitsOwner* own = new HitsOwner();
+  res->opaque = own;
+  res->n_docs = n_docs;
+  auto fail = [&](int32_t code) {
+    aha_b200_hits_free(res.release());
+    return code;
+  };
+  cudaStream_t st = nullptr;  // legacy default stream: the per-call API is synchronous like the reference
+  if (cudaMallocAsync(&own->dev_text, total > 0 ? total : 16, st) != cudaSuccess ||
+      cudaMallocAsync(&own->dev_doc_off, (n_docs + 1) * sizeof(int64_t), st) != cudaSuccess)
+    return fail(set_err(AHA_ERR_NOMEM, "device allocation failed"));
+  if (total > 0 && cudaMemcpyAsync(own->dev_text, text, total, cudaMemcpyHostToDevice, st) != cudaSuccess)
+    return fail(set_err(AHA_ERR_CUDA, "H2D copy of text failed"));
+  if (cudaMemcpyAsync(own->dev_doc_off, doc_off, (n_docs + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, st) != cudaSuccess)
+    return fail(set_err(AHA_ERR_CUDA, "H2D copy of doc_off failed"));
+  rc = scan_on_device(d, own->dev_text, own->dev_doc_off, n_docs, total, mode, sep_bits, sep_size, st, res.get(), own);
+  if (rc) return fail(rc);
+  const size_t hbytes = (size_t)(res->n_hits > 0 ? res->n_hits : 1) * sizeof(aha_hit);
+  if (cudaMallocHost(&own->host_doc_hit_off, (n_docs + 1) * sizeof(int64_t)) != cudaSuccess)
+    return fail(set_err(AHA_ERR_NOMEM, "pinned allocation failed"));
+  if (!(mode & AHA_COUNT_ONLY)) {
+    if (cudaMallocHost(&own->host_hits, hbytes) != cudaSuccess) return fail(set_err(AHA_ERR_NOMEM, "pinned allocation failed"));
+    if (res->n_hits > 0 &&
+        cudaMemcpyAsync(own->host_hits, own->dev_hits, (size_t)res->n_hits * sizeof(aha_hit), cudaMemcpyDeviceToHost, st) != cudaSuccess)
+      return fail(set_err(AHA_ERR_CUDA, "D2H copy of hits failed"));
+  }
+  if (cudaMemcpyAsync(own->host_doc_hit_off, own->dev_doc_hit_off, (n_docs + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+      cudaStreamSynchronize(st) != cudaSuccess)
+    return fail(set_err(AHA_ERR_CUDA, std::string("D2H copy failed: ") + cudaGetErrorString(cudaGetLastError())));
+  res->device = own->device;
+  res->on_device = 0;
+  res->hits = static_cast<aha_hit*>(own->host_hits);
+  res->doc_hit_off = static_cast<int64_t*>(own->host_doc_hit_off);
+  *out = res.release();
+  return AHA_OK;
+}
+
+void aha_b200_hits_free(aha_hits* h) {
+  if (!h) return;
+  HitsOwner* own = static_cast<HitsOwner*>(h->opaque);
+  if (own) {
+    int prev = 0;
+    cudaGetDevice(&prev);
+    cudaSetDevice(own->device);
+    if (own->dev_hits) cudaFreeAsync(own->dev_hits, own->stream);
+    if (own->dev_doc_hit_off) cudaFreeAsync(own->dev_doc_hit_off, own->stream);
+    if (own->dev_text) cudaFreeAsync(own->dev_text, own->stream);
+    if (own->dev_doc_off) cudaFreeAsync(own->dev_doc_off, own->stream);
+    if (own->host_hits) cudaFreeHost(own->host_hits);
+    if (own->host_doc_hit_off) cudaFreeHost(own->host_doc_hit_off);
+    cudaSetDevice(prev);
+    delete own;
+  }
+  delete h;
+}
+
+// ---- synthetic corpora --------------------------------------------------------------------
+int32_t aha_b200_gen_text_host(int32_t corpus, uint64_t seed, int64_t first, int64_t bytes, uint8_t* out) {
+  if (corpus < 0 || corpus > 2 || first < 0 || bytes < 0 || (!out && bytes > 0)) return set_err(AHA_ERR_ARG, "bad argument");
+  uint8_t buf[kGenBlock];
+  int64_t pos = first;
+  const int64_t end = first + bytes;
+  while (pos < end) {
+    const int64_t k = pos / kGenBlock;
+    gen_block(corpus, seed, (uint64_t)k, buf);
+    const int64_t b0 = k * kGenBlock;
+    const int64_t lo = pos - b0;
+    const int64_t hi = std::min<int64_t>(kGenBlock, end - b0);
+    memcpy(out + (pos - first), buf + lo, (size_t)(hi - lo));
+    pos = b0 + hi;
+  }
+  return AHA_OK;
+}
+
+}  // extern "C"
+
+namespace aha {
+__global__ void gen_text_kernel(int corpus, uint64_t seed, int64_t first_block, int64_t n_blocks, int64_t bytes, uint8_t* out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_blocks) return;
+  uint8_t buf[kGenBlock];
+  gen_block(corpus, seed, (uint64_t)(first_block + i), buf);
+  const int64_t o = i * kGenBlock;
+  const int64_t n = min((int64_t)kGenBlock, bytes - o);
+  for (int64_t j = 0; j < n; ++j) out[o + j] = buf[j];
+}
+}  // namespace aha
+
+extern "C" int32_t aha_b200_gen_text_device(int32_t corpus, uint64_t seed, int64_t first, int64_t bytes, void* dev_out,
+                                            void* stream) {
+  if (corpus < 0 || corpus > 2 || first < 0 || bytes < 0 || (!dev_out && bytes > 0)) return set_err(AHA_ERR_ARG, "bad argument");
+  if (first % kGenBlock != 0) return set_err(AHA_ERR_ARG, "first must be a multiple of 192");
+  if (bytes == 0) return AHA_OK;
+  const int64_t n_blocks = (bytes + kGenBlock - 1) / kGenBlock;
+  gen_text_kernel<<<(unsigned)((n_blocks + 127) / 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      corpus, seed, first / kGenBlock, n_blocks, bytes, static_cast<uint8_t*>(dev_out));
+  AHA_CUDA(cudaGetLastError());
+  return AHA_OK;
+}

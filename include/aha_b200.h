@@ -89,6 +89,10 @@ int32_t aha_b200_dfa_from_cedar(const void* nodes, int64_t array_size, const int
 /* Aha::AC.compile(keys) (ac.cr:62-69) in one call: keys concatenated, key_off has n_keys+1 entries.
  * AHA_ERR_KEY with "key:... appear twice." on a duplicate, like the reference.                */
 int32_t aha_b200_dfa_compile(const uint8_t* keys, const int64_t* key_off, int64_t n_keys, aha_dfa** out);
+/* host-only flatten (no device needed): malloc'ed blob, release with aha_b200_blob_free */
+int32_t aha_b200_flatten_host(const void* nodes, int64_t array_size, const int32_t* fails, const int32_t* output,
+                              const uint32_t* key_lens, int64_t n_keys, uint8_t** blob, int64_t* bytes);
+void aha_b200_blob_free(uint8_t* blob);
 /* serialised DFA (host memory, library-owned until dfa_free) for broadcast / caching */
 int32_t aha_b200_dfa_blob(const aha_dfa* d, const uint8_t** blob, int64_t* bytes);
 /* rebuild from a blob in host memory (e.g. received on another rank) and upload */

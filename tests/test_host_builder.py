@@ -1,0 +1,162 @@
+"""CPU tests of the product's host side: the C ABI library loads and exports every declared symbol,
+the host cedar builder reproduces the oracle's (= reference-layout) arrays bit for bit, and the
+flattened DFA, walked in pure Python, yields the oracle's hit stream."""
+import ctypes as C
+import os
+import random
+import re
+
+import numpy as np
+import pytest
+
+import aha_b200
+from aha_b200 import _lib
+from oracle import oracle as O
+from tests.test_oracle_kat import _rand_keys, sev
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "aha_b200.h")).read()
+    declared = set(re.findall(r"\b(aha_b200_[a-z0-9_]+)\s*\(", hdr))
+    L = _lib.lib()
+    assert declared, "no declarations found"
+    for name in sorted(declared):
+        assert hasattr(L, name), name
+    assert declared == set(_lib.EXPORTS)
+
+
+def _key_sets():
+    rng = random.Random(7)
+    yield ["我", "我是", "是中"]
+    yield ["Ruby", "ruby", "rub"]
+    yield open(os.path.join(ROOT, "tests", "golden", "cedar_words.txt")).read().split()
+    for seed in range(10):
+        r = random.Random(seed)
+        alphabet = [b"ab", b"abc", b"abcdefgh", bytes(range(1, 256))][seed % 4]
+        yield _rand_keys(r, r.choice([30, 300, 3000]), alphabet, r.choice([3, 5, 9]))
+    words = ["".join(rng.choice("abcdefghijklmnopqrstuvwxyz") for _ in range(rng.randint(2, 10))) for _ in range(20000)]
+    yield list(dict.fromkeys(words))
+
+
+@pytest.mark.parametrize("idx", range(14))
+def test_builder_matches_oracle_layout(idx):
+    keys = list(_key_sets())[idx]
+    o = O.AC.compile(keys)
+    da = aha_b200.Cedar()
+    for i, k in enumerate(keys):
+        assert da.insert(k) == i
+    p_nodes, p_fails, p_out, p_kl = da.compiled_arrays()
+    o_nodes, o_fails, o_out, o_kl = o.arrays()
+    assert np.array_equal(p_nodes, o_nodes)
+    assert np.array_equal(p_fails, o_fails)
+    assert np.array_equal(p_out, o_out)
+    assert np.array_equal(p_kl, o_kl)
+    for i in (0, len(keys) // 2, len(keys) - 1):
+        k = keys[i]
+        assert da.key_bytes(i) == (k.encode() if isinstance(k, str) else bytes(k))
+        assert da.get(k) == i
+
+
+def test_builder_errors_match_reference():
+    da = aha_b200.Cedar()
+    with pytest.raises(aha_b200.AhaError, match="Cannot insert empty key"):  # cedar.cr:756
+        da.insert("")
+    with pytest.raises(aha_b200.AhaError, match=r"key\[1\] is zero"):  # cedar.cr:235
+        da.insert(b"a\x00b")
+    da = aha_b200.Cedar()  # (a raised insert leaves a half-built path behind, in the reference too)
+    assert da.insert("a") == 0
+    assert da.insert("a") == 0  # existing key returns its id (cedar.cr:757-758)
+
+
+class BlobDfa:
+    """pure-Python reader + walker of the flattened DFA blob (test-only)."""
+
+    def __init__(self, arrays):
+        nodes, fails, output, kl = arrays
+        blob, n = C.c_void_p(), C.c_int64()
+        L = _lib.lib()
+        _lib.check(L.aha_b200_flatten_host(nodes.ctypes.data, len(fails), fails.ctypes.data, output.ctypes.data,
+                                           kl.ctypes.data if len(kl) else None, len(kl), C.byref(blob), C.byref(n)))
+        raw = C.string_at(blob.value, n.value)
+        L.aha_b200_blob_free(blob)
+        hdr = np.frombuffer(raw[:120], dtype=np.uint8)
+        u64 = lambda o: int(np.frombuffer(raw[o:o + 8], "<u8")[0])
+        u32 = lambda o: int(np.frombuffer(raw[o:o + 4], "<u4")[0])
+        self.C, self.S, self.K, self.n_out, self.maxlen = u32(12), u64(16), u64(24), u64(32), u32(40)
+        offs = [u64(48 + 8 * i) for i in range(8)]
+        self.classmap = np.frombuffer(raw, np.uint8, 256, offs[0])
+        self.delta = np.frombuffer(raw, "<u4", self.S * self.C, offs[1]).reshape(self.S, self.C)
+        self.out_off = np.frombuffer(raw, "<u4", self.S + 1, offs[2])
+        self.out_val = np.frombuffer(raw, "<i4", self.n_out, offs[3])
+        self.key_len = np.frombuffer(raw, "<u4", self.K, offs[4])
+        self.key_tail = np.frombuffer(raw, "<u4", self.K, offs[5])
+        assert offs[7] == len(raw)
+
+    def match(self, text):
+        hits, s = [], 0
+        for i, b in enumerate(text):
+            e = int(self.delta[s, self.classmap[b]])
+            s = e & 0x1FFFFFFF
+            if e & 0x80000000:
+                for j in range(self.out_off[s], self.out_off[s + 1]):
+                    v = int(self.out_val[j])
+                    hits.append((i + 1 - int(self.key_len[v]), i + 1, v))
+        return hits
+
+    def match_longest(self, text, inter):
+        hits, s, prev_i, prev_s = [], 0, -1, 0
+
+        def flush():
+            j = self.out_off[prev_s]
+            if j < self.out_off[prev_s + 1]:
+                v = int(self.out_val[j])
+                hits.append((prev_i + 1 - int(self.key_len[v]), prev_i + 1, v))
+
+        for i, b in enumerate(text):
+            e = int(self.delta[s, self.classmap[b]])
+            if e & 0x20000000:
+                s = e & 0x1FFFFFFF
+                if e & 0x40000000:
+                    prev_i, prev_s = i, s
+            else:
+                if prev_i >= 0:
+                    flush()
+                    prev_i = -1
+                    if not inter:
+                        s = 0
+                        continue
+                s = e & 0x1FFFFFFF
+                if s != 0 and (e & 0x40000000):
+                    prev_i, prev_s = i, s
+        if prev_i >= 0:
+            flush()
+        return hits
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_flattened_dfa_reproduces_oracle_stream(seed):
+    rng = random.Random(100 + seed)
+    alphabet = [b"ab", b"abc", b"abcdefgh", bytes(range(1, 256))][seed % 4]
+    keys = _rand_keys(rng, rng.choice([5, 50, 500]), alphabet, rng.choice([2, 4, 7]))
+    text = bytes(rng.choice(alphabet) for _ in range(3000))
+    o = O.AC.compile(keys)
+    da = aha_b200.Cedar()
+    for k in keys:
+        da.insert(k)
+    dfa = BlobDfa(da.compiled_arrays())
+    assert dfa.maxlen == max(len(k) for k in keys)
+    assert dfa.match(text) == sev(o.match(text))
+    for inter in (False, True):  # includes the stale-END cases (Q4): the DFA carries raw is_end bits
+        assert dfa.match_longest(text, inter) == sev(o.match_longest(text, inter))
+
+
+def test_generator_is_deterministic_and_nul_free():
+    from aha_b200 import synth
+    for corpus in (synth.EN, synth.ZH, synth.MIX):
+        a = synth.gen_host(corpus, 42, 0, 192 * 50)
+        b = synth.gen_host(corpus, 42, 192 * 10 + 7, 1000)
+        assert np.array_equal(a[192 * 10 + 7:192 * 10 + 1007], b)
+        assert (a != 0).all()
+        a.tobytes().decode("utf-8")  # every block is valid UTF-8

@@ -1,0 +1,163 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (aha_b200.AC -> libaha_b200.so), against the
+CPU oracle on the same inputs.  Bit-exact: integer/byte work, no tolerance."""
+import random
+
+import numpy as np
+import pytest
+
+import aha_b200
+from aha_b200 import synth
+from oracle import oracle as O
+from tests.test_oracle_kat import _rand_keys
+
+pytestmark = pytest.mark.gpu
+
+
+def as_tuples(h):
+    return [(int(x["start"]), int(x["end"]), int(x["value"])) for x in h]
+
+
+def oracle_batch(oac, docs, mode=0, sep=None, sep_size=256):
+    hits, off = [], [0]
+    for d in docs:
+        h = oac.scan(d, mode & ~aha_b200.SEP, sep=sep, sep_size=sep_size)
+        hits.append(h)
+        off.append(off[-1] + len(h))
+    return (np.concatenate(hits) if hits else np.zeros(0, O.HIT_DTYPE)), np.array(off, np.int64)
+
+
+def check_batch(keys, docs, mode=0, sep=None, sep_size=256):
+    g = aha_b200.AC.compile(keys)
+    o = O.AC.compile(keys)
+    res = g.scan_batch(docs, mode, sep, sep_size)
+    want, want_off = oracle_batch(o, docs, mode, sep, sep_size)
+    got = res.hits()
+    assert res.n_hits == len(want)
+    assert np.array_equal(res.doc_hit_off(), want_off)
+    assert got.tobytes() == want.tobytes()
+    return res
+
+
+def test_spec_vectors():
+    m = aha_b200.AC.compile(["我", "我是", "是中"])  # spec/ac_spec.cr:5-12
+    assert [(h[1], h[2]) for h in as_tuples(m.match("我是中国人"))] == [(1, 0), (2, 1), (3, 2)]
+    assert as_tuples(m.match("我是中国人".encode())) == [(0, 3, 0), (0, 6, 1), (3, 9, 2)]
+    m = aha_b200.AC.compile(["a", "aa"])  # spec/ac_spec.cr:25-34
+    assert [(h[1], h[2]) for h in as_tuples(m.match("a aaa", sep=[" "]))] == [(1, 0)]
+    t = aha_b200.Cedar()  # spec/ac_longest_match_spec.cr:5-18
+    for s in ["Ruby", "ruby", "rub"]:
+        t.insert(s)
+    ac = aha_b200.AC.compile(t)
+    assert [(s, e, ac[v]) for s, e, v in as_tuples(ac.match_longest("Ruby on rub"))] == [(0, 4, "Ruby"), (8, 11, "rub")]
+    t = aha_b200.Cedar()  # spec/ac_longest_match_spec.cr:20-33
+    for s in ["Ruby", "ruby", "uby "]:
+        t.insert(s)
+    ac = aha_b200.AC.compile(t)
+    assert [(s, e, ac[v]) for s, e, v in as_tuples(ac.match_longest("ruby ", True))] == [(0, 4, "ruby"), (1, 5, "uby ")]
+
+
+def test_quirks_q1_q5_q7():
+    assert as_tuples(aha_b200.AC.compile(["abcd", "bc"]).match(b"abcd")) == [(0, 4, 0)]
+    assert as_tuples(aha_b200.AC.compile(["xab", "abz", "b"]).match(b"xab")) == [(0, 3, 0)]
+    assert as_tuples(aha_b200.AC.compile(["ab", "b"]).match_longest(b"abb")) == [(0, 2, 0)]
+    m = aha_b200.AC.compile(["a"])
+    assert m.scan_batch([b"\xe4a\xe4"], 0, sep=[" "], sep_size=128).n_hits == 1
+    assert m.scan_batch([b"\xe4a\xe4"], 0, sep=[" "], sep_size=256).n_hits == 0
+
+
+def test_errors():
+    with pytest.raises(aha_b200.AhaError, match="appear twice"):
+        aha_b200.AC.compile(["a", "a"])
+    with pytest.raises(aha_b200.AhaError, match="sep BitArray size > 256"):
+        aha_b200.AC.compile(["a"]).scan_batch([b"a"], 0, sep=[" "], sep_size=300)
+
+
+def _docs(rng, alphabet, n_docs, max_len):
+    docs = []
+    for _ in range(n_docs):
+        L = rng.choice([0, 0, 1, 2, rng.randint(0, max_len), max_len])
+        docs.append(bytes(rng.choice(alphabet) for _ in range(L)))
+    return docs
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_random_ragged_batches(seed):
+    rng = random.Random(seed)
+    alphabet = [b"ab", b"abc", b"abcdefgh", bytes(range(1, 256))][seed % 4]
+    keys = _rand_keys(rng, rng.choice([5, 50, 500, 3000]), alphabet, rng.choice([2, 4, 9]))
+    docs = _docs(rng, alphabet, rng.choice([1, 7, 40]), rng.choice([10, 700, 5000]))
+    check_batch(keys, docs)
+    check_batch(keys, docs, sep=[alphabet[0]])
+    check_batch(keys, docs, aha_b200.LONGEST)
+    check_batch(keys, docs, aha_b200.LONGEST | aha_b200.INTERSECTABLE)
+
+
+def test_empty_inputs():
+    keys = ["ab", "b"]
+    check_batch(keys, [])
+    check_batch(keys, [b""])
+    check_batch(keys, [b"", b"", b"ab", b"", b""])
+    check_batch(keys, [b"", b""], aha_b200.LONGEST)
+
+
+def test_char_units_utf8():
+    rng = random.Random(5)
+    zh = "的一是在不了有和人这中大为上个国我以要他时来用们生到作地于出就分对成会可主发年动同工也能下过子说产种面而方后多定行学法所民得经"
+    keys = list(dict.fromkeys("".join(rng.choice(zh) for _ in range(rng.randint(1, 3))) for _ in range(300)))
+    keys += ["ab", "b c", "é", "日本"]
+    docs = ["".join(rng.choice(zh + "ab cé日本") for _ in range(rng.randint(0, 2000))) for _ in range(12)]
+    check_batch(keys, docs, aha_b200.UNITS_CHAR)
+    check_batch(keys, docs, aha_b200.UNITS_CHAR, sep=[" "])
+    check_batch(keys, docs, aha_b200.UNITS_CHAR | aha_b200.LONGEST)
+    check_batch(keys, docs, aha_b200.UNITS_CHAR | aha_b200.LONGEST | aha_b200.INTERSECTABLE)
+
+
+def _split_docs(text, size):
+    return [text[i:i + size].tobytes() for i in range(0, len(text), size)]
+
+
+@pytest.mark.parametrize("cfg", ["c1_en_1k", "c2_zh_10k", "c3_mix_100k"])
+def test_scaled_baseline_configs(cfg):
+    if cfg == "c1_en_1k":
+        keys, corpus, seed = synth.patterns_en_words(1000), synth.EN, synth.SEED_TEXT
+    elif cfg == "c2_zh_10k":
+        keys, corpus, seed = synth.patterns_zh_ngrams(10000), synth.ZH, synth.SEED_TEXT + 1
+    else:
+        keys, corpus, seed = synth.patterns_mix(100000), synth.MIX, synth.SEED_TEXT + 2
+    D = synth.doc_bytes(1 << 20)
+    text = synth.gen_host(corpus, seed, 0, 8 * D)
+    docs = _split_docs(text, D)
+    res = check_batch(keys, docs)
+    assert res.n_hits > 0
+    check_batch(keys, docs[:2], aha_b200.UNITS_CHAR)
+
+
+def test_device_api_and_generator_parity():
+    import torch
+    keys = synth.patterns_zh_ngrams(2000)
+    g = aha_b200.AC.compile(keys)
+    o = O.AC.compile(keys)
+    D = synth.doc_bytes(1 << 18)
+    n_docs = 16
+    dev = synth.gen_device(synth.ZH, synth.SEED_TEXT + 1, 0, n_docs * D)
+    host = synth.gen_host(synth.ZH, synth.SEED_TEXT + 1, 0, n_docs * D)
+    assert np.array_equal(dev.cpu().numpy(), host)
+    doc_off = torch.arange(0, n_docs + 1, dtype=torch.int64, device="cuda") * D
+    res = g.scan_device(dev, doc_off)
+    got = res.hits_tensor().cpu().numpy()
+    want, want_off = oracle_batch(o, _split_docs(host, D))
+    assert np.array_equal(res.doc_hit_off(), want_off)
+    assert got.astype("<i4").tobytes() == want.tobytes()
+    assert res.scan_ms > 0
+
+
+def test_blob_roundtrip_and_save_load(tmp_path):
+    keys = ["我", "我是", "是中", "abc"]
+    g = aha_b200.AC.compile(keys)
+    g2 = aha_b200.AC.from_blob(g.blob())
+    assert as_tuples(g2.match("我是中国人abc")) == as_tuples(g.match("我是中国人abc"))
+    p = str(tmp_path / "aha.bin")
+    g.save(p)  # spec/ac_spec.cr:14-23
+    g3 = aha_b200.AC.load(p)
+    assert [(h[1], h[2]) for h in as_tuples(g3.match("我是中国人"))] == [(1, 0), (2, 1), (3, 2)]
+    assert g3[1] == "我是"

@@ -19,6 +19,8 @@
 #include <cstring>
 #include <deque>
 #include <string>
+#include <thread>
+#include <atomic>
 #include <vector>
 
 namespace {
@@ -760,6 +762,29 @@ int64_t orc_ac_scan_count(void* a, const uint8_t* seq, int64_t n, uint64_t* chec
   });
   if (checksum) *checksum = cs;
   return cnt;
+}
+
+// Document-parallel timing harness: `threads` workers pull documents from a shared counter and run
+// ACX#match over each (same loop as orc_ac_scan_count); the automaton is shared read-only.
+int64_t orc_ac_scan_count_mt(void* a, const uint8_t* text, const int64_t* doc_off, int64_t n_docs, int32_t threads) {
+  AC* ac = (AC*)a;
+  std::atomic<int64_t> next(0), total(0);
+  auto work = [&]() {
+    int64_t local = 0;
+    for (;;) {
+      int64_t d = next.fetch_add(1);
+      if (d >= n_docs) break;
+      match_(ac, text + doc_off[d], doc_off[d + 1] - doc_off[d], [&](int32_t idx, int32_t nid) {
+        fetch(ac, idx, nid, [&](Hit) { local++; });
+      });
+    }
+    total += local;
+  };
+  std::vector<std::thread> pool;
+  for (int t = 1; t < threads; t++) pool.emplace_back(work);
+  work();
+  for (auto& t : pool) t.join();
+  return total.load();
 }
 
 // CedarX#match_longest(String, ignore_case, sep) (cedar.cr:1075-1121); character offsets.

@@ -62,6 +62,8 @@ def lib():
         L.orc_ac_scan.restype = i64
         L.orc_ac_scan_count.argtypes = [vp, vp, i64, C.POINTER(C.c_uint64)]
         L.orc_ac_scan_count.restype = i64
+        L.orc_ac_scan_count_mt.argtypes = [vp, vp, vp, i64, i32]
+        L.orc_ac_scan_count_mt.restype = i64
         L.orc_cedar_match_longest.argtypes = [vp, vp, i64, i32, i32, C.c_char_p, i32, i32]
         L.orc_cedar_match_longest.restype = i64
         L.orc_trie_hits.restype = vp
@@ -217,3 +219,8 @@ class AC:
         cs = C.c_uint64(0)
         n = self._L.orc_ac_scan_count(self._h, a.ctypes.data, a.size, C.byref(cs))
         return n, cs.value
+
+    def scan_count_mt(self, text, doc_off, threads):
+        a = _as_u8(text)
+        off = np.ascontiguousarray(doc_off, dtype=np.int64)
+        return self._L.orc_ac_scan_count_mt(self._h, a.ctypes.data, off.ctypes.data, len(off) - 1, threads)

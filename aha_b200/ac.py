@@ -43,6 +43,7 @@ class Cedar:
         h = C.c_void_p()
         check(lib().aha_b200_builder_new(C.byref(h)))
         self._h = h
+        self._ac = None
 
     def __del__(self):
         try:
@@ -54,6 +55,7 @@ class Cedar:
         k = _b(key)
         out = C.c_int32()
         check(lib().aha_b200_builder_insert(self._h, k, len(k), C.byref(out)))
+        self._ac = None  # the cached automaton is stale
         return out.value
 
     def get(self, key):  # []?
@@ -77,6 +79,16 @@ class Cedar:
         if r is None:
             raise IndexError(k)
         return r
+
+    def match_longest(self, text, ignore_case=False, sep=None):
+        """CedarX#match_longest(String, ignore_case, sep) (cedar.cr:1075-1121): leftmost-longest,
+        character offsets.  Runs on the GPU over the trie part of the flattened automaton."""
+        return self.match_longest_batch([text], ignore_case, sep).hits()
+
+    def match_longest_batch(self, docs, ignore_case=False, sep=None):
+        if self._ac is None:
+            self._ac = AC.compile(self)
+        return self._ac.scan_batch(docs, TRIE_LONGEST | (IGNORE_CASE if ignore_case else 0), sep)
 
     def compiled_arrays(self):
         """Runs ACX.compile(da) (ac.cr:71-112); returns copies of (nodes, fails, output, key_lens)."""

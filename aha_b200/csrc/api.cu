@@ -11,6 +11,7 @@
 #include "gen.cuh"
 #include "scan_common.cuh"
 #include "scan_v1.cuh"
+#include "scan_trie.cuh"
 #include "scan_fused.cuh"
 
 namespace aha {

@@ -53,7 +53,8 @@ static void fill_params(ScanParams* p, const DeviceDfa* dd, const void* dev_text
 
 // two-pass baseline: count -> exclusive sum -> emit
 static int32_t run_v1(ScanParams p, cudaStream_t st, aha_hits* res, HitsOwner* own, cudaEvent_t ev0, cudaEvent_t ev1) {
-  const bool longest = (p.mode & AHA_LONGEST) != 0;
+  const bool trie = (p.mode & AHA_TRIE_LONGEST) != 0;
+  const bool longest = trie || (p.mode & AHA_LONGEST) != 0;
   const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
   p.chunk = 512;
   p.n_chunks = (p.total + p.chunk - 1) / p.chunk;
@@ -87,7 +88,8 @@ static int32_t run_v1(ScanParams p, cudaStream_t st, aha_hits* res, HitsOwner* o
   }
   const unsigned grid = (unsigned)((units + tpb - 1) / tpb);
   if (units > 0) {
-    if (longest) longest_doc_kernel<false><<<grid, tpb, 0, st>>>(p);
+    if (trie) trie_longest_doc_kernel<false><<<grid, tpb, 0, st>>>(p);
+    else if (longest) longest_doc_kernel<false><<<grid, tpb, 0, st>>>(p);
     else scan_v1_kernel<false><<<grid, tpb, 0, st>>>(p);
   }
   int32_t rc = exclusive_sum_u32_to_u64(counts, offsets, units + 1, st);
@@ -102,7 +104,8 @@ static int32_t run_v1(ScanParams p, cudaStream_t st, aha_hits* res, HitsOwner* o
   }
   if (units > 0) {
     if (longest) {
-      longest_doc_kernel<true><<<grid, tpb, 0, st>>>(p);
+      if (trie) trie_longest_doc_kernel<true><<<grid, tpb, 0, st>>>(p);
+      else longest_doc_kernel<true><<<grid, tpb, 0, st>>>(p);
       offsets_to_doc_hit_off<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(offsets, p.n_docs, p.doc_hit_off);
     } else {
       scan_v1_kernel<true><<<grid, tpb, 0, st>>>(p);
@@ -135,7 +138,8 @@ static int32_t scan_on_device(const aha_dfa* d, const void* dev_text, const void
   if (!dd) return set_err(AHA_ERR_STATE, "automaton was not uploaded to the current device (aha_b200_init)");
   if ((mode & AHA_SEP) && (sep_size > 256 || sep_size < 0 || !sep_bits))
     return set_err(AHA_ERR_ARG, "sep BitArray size > 256 is not supported");  // ac.cr:322
-  if (mode & AHA_TRIE_LONGEST) return set_err(AHA_ERR_ARG, "AHA_TRIE_LONGEST needs a trie handle (aha_b200_trie_*)");
+  if ((mode & AHA_TRIE_LONGEST) && dd->view.max_key_len > (uint32_t)kTrieMaxChars)
+    return set_err(AHA_ERR_ARG, "AHA_TRIE_LONGEST supports keys of at most 96 bytes");
   int32_t rc = pool_setup(dev);
   if (rc) return rc;
   own->device = dev;
@@ -145,7 +149,7 @@ static int32_t scan_on_device(const aha_dfa* d, const void* dev_text, const void
   cudaEvent_t ev0, ev1;
   AHA_CUDA(cudaEventCreate(&ev0));
   AHA_CUDA(cudaEventCreate(&ev1));
-  const bool fused_ok = scan_impl() == 1 && !(mode & AHA_LONGEST);
+  const bool fused_ok = scan_impl() == 1 && !(mode & (AHA_LONGEST | AHA_TRIE_LONGEST));
   if (fused_ok) rc = run_fused(p, dd, st, res, own, ev0, ev1);
   else rc = run_v1(p, st, res, own, ev0, ev1);
   if (rc == AHA_OK) {

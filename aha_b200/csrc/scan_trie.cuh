@@ -1,0 +1,156 @@
+// scan_trie.cuh -- CedarX#match_longest(String, ignore_case, sep) (cedar.cr:1075-1121) on the GPU.
+//
+// One thread per document (the BASELINE config runs it over millions of 4 KiB documents).  The trie
+// is the goto part of the flattened DFA (entries with kGoto); a state's own key id is the head of its
+// output list.  The reference explores case variants with a breadth-first frontier and keeps the FIRST
+// candidate of strictly greatest length (cedar.cr:993-1019, 1102-1104).  Frontier order at a given
+// length is lexicographic in the per-character choice (exact before case-swapped), which is exactly
+// depth-first preorder, so a bounded-memory DFS with the same strict '>' rule picks the same key.
+// Offsets are character indices.  Characters are decoded structurally (lead byte -> length), mapped,
+// re-encoded and walked byte by byte like CedarX#jump(Char) (cedar.cr:946-952).
+#pragma once
+#include "scan_common.cuh"
+
+namespace aha {
+
+constexpr int kTrieMaxChars = 96;  // DFS depth bound = longest key in characters
+
+// simple 1:1 case pairs: ASCII, Latin-1, Greek, Cyrillic basic blocks (Char#uppercase?/upcase/downcase)
+__host__ __device__ __forceinline__ bool cp_upper(uint32_t c) {
+  return (c >= 'A' && c <= 'Z') || (c >= 0xC0 && c <= 0xDE && c != 0xD7) || (c >= 0x391 && c <= 0x3A9 && c != 0x3A2) ||
+         (c >= 0x410 && c <= 0x42F);
+}
+__host__ __device__ __forceinline__ bool cp_lower(uint32_t c) {
+  return (c >= 'a' && c <= 'z') || (c >= 0xE0 && c <= 0xFE && c != 0xF7) || (c >= 0x3B1 && c <= 0x3C9 && c != 0x3C2) ||
+         (c >= 0x430 && c <= 0x44F);
+}
+// chr.uppercase? ? chr.downcase : chr.upcase   (cedar.cr:995-996)
+__host__ __device__ __forceinline__ uint32_t cp_other(uint32_t c) { return cp_upper(c) ? c + 32 : (cp_lower(c) ? c - 32 : c); }
+
+__device__ __forceinline__ int utf8_decode(const uint8_t* s, int64_t i, int64_t n, uint32_t* cp) {
+  const uint32_t b = s[i];
+  if (b < 0x80) { *cp = b; return 1; }
+  if ((b & 0xE0) == 0xC0 && i + 1 < n) { *cp = ((b & 0x1F) << 6) | (s[i + 1] & 0x3F); return 2; }
+  if ((b & 0xF0) == 0xE0 && i + 2 < n) { *cp = ((b & 0x0F) << 12) | ((s[i + 1] & 0x3F) << 6) | (s[i + 2] & 0x3F); return 3; }
+  if ((b & 0xF8) == 0xF0 && i + 3 < n) {
+    *cp = ((b & 0x07) << 18) | ((s[i + 1] & 0x3F) << 12) | ((s[i + 2] & 0x3F) << 6) | (s[i + 3] & 0x3F);
+    return 4;
+  }
+  *cp = b;
+  return 1;
+}
+__device__ __forceinline__ int utf8_encode(uint32_t c, uint8_t* o) {
+  if (c < 0x80) { o[0] = (uint8_t)c; return 1; }
+  if (c < 0x800) { o[0] = 0xC0 | (c >> 6); o[1] = 0x80 | (c & 0x3F); return 2; }
+  if (c < 0x10000) { o[0] = 0xE0 | (c >> 12); o[1] = 0x80 | ((c >> 6) & 0x3F); o[2] = 0x80 | (c & 0x3F); return 3; }
+  o[0] = 0xF0 | (c >> 18); o[1] = 0x80 | ((c >> 12) & 0x3F); o[2] = 0x80 | ((c >> 6) & 0x3F); o[3] = 0x80 | (c & 0x3F);
+  return 4;
+}
+
+template <bool EMIT>
+__global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams p) {
+  __shared__ uint8_t cmap[256];
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) cmap[i] = p.classmap[i];
+  __syncthreads();
+  const int64_t d = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= p.n_docs) return;
+  const uint8_t* s = p.text + p.doc_off[d];
+  const int64_t n = p.doc_off[d + 1] - p.doc_off[d];
+  const bool icase = (p.mode & AHA_IGNORE_CASE) != 0;
+  const bool use_sep = (p.mode & AHA_SEP) != 0;
+  const uint32_t C = p.C;
+  uint64_t run = EMIT ? p.offsets[d] : 0;
+  // jump(chr, from): walk the character's UTF-8 bytes over goto edges only; -1 == no path
+  auto jump = [&](uint32_t cp, uint32_t from) -> int64_t {
+    uint8_t buf[4];
+    const int k = utf8_encode(cp, buf);
+    uint32_t st = from;
+    for (int j = 0; j < k; ++j) {
+      const uint32_t e = p.delta[(uint64_t)st * C + cmap[buf[j]]];
+      if (!(e & kGoto) || buf[j] == 0) return -1;
+      st = e & kStateMask;
+    }
+    return (int64_t)st;
+  };
+  uint32_t node[kTrieMaxChars + 1];
+  int32_t bpos[kTrieMaxChars + 1];
+  uint8_t var[kTrieMaxChars + 1];
+  int64_t pos = 0;
+  int32_t cidx = 0;
+  uint32_t cp;
+  while (pos < n) {
+    if (use_sep) {
+      while (pos < n) {
+        const int l = utf8_decode(s, pos, n, &cp);
+        if (!is_sep(p, cp)) break;
+        pos += l;
+        ++cidx;
+      }
+    }
+    int32_t best_n = 0, best_v = 0, best_bytes = 0;
+    int depth = 0;
+    node[0] = 0;
+    bpos[0] = (int32_t)pos;
+    var[0] = 0;
+    while (depth >= 0) {
+      const int lv = depth;
+      if (var[lv] >= 2 || bpos[lv] >= n || lv >= kTrieMaxChars) {
+        --depth;
+        continue;
+      }
+      const int l = utf8_decode(s, bpos[lv], n, &cp);
+      const int v = var[lv]++;
+      uint32_t cc = cp;
+      if (v == 1) {
+        if (!icase) { var[lv] = 2; continue; }
+        cc = cp_other(cp);
+        if (cc == cp) continue;
+      }
+      const int64_t nn = jump(cc, node[lv]);
+      if (nn < 0) continue;
+      const uint32_t j = p.out_off[nn];
+      if (j < p.out_off[nn + 1] && lv + 1 > best_n) {
+        bool ok = true;
+        if (use_sep) {
+          const int64_t after = bpos[lv] + l;
+          if (after < n) {
+            uint32_t ncp;
+            utf8_decode(s, after, n, &ncp);
+            ok = is_sep(p, ncp);
+          }
+        }
+        if (ok) {
+          best_n = lv + 1;
+          best_v = p.out_val[j];
+          best_bytes = bpos[lv] + l - (int32_t)pos;
+        }
+      }
+      node[lv + 1] = (uint32_t)nn;
+      bpos[lv + 1] = bpos[lv] + l;
+      var[lv + 1] = 0;
+      ++depth;
+    }
+    if (best_n == 0) {
+      if (pos < n) {
+        pos += utf8_decode(s, pos, n, &cp);
+        ++cidx;
+      }
+      if (use_sep) {
+        while (pos < n) {
+          const int l = utf8_decode(s, pos, n, &cp);
+          if (is_sep(p, cp)) break;
+          pos += l;
+          ++cidx;
+        }
+      }
+    } else {
+      if (EMIT && p.hits) p.hits[run] = aha_hit{cidx, cidx + best_n, best_v};
+      ++run;
+      pos += best_bytes;
+      cidx += best_n;
+    }
+  }
+  if (!EMIT) p.counts[d] = (uint32_t)run;
+}
+
+}  // namespace aha

@@ -161,3 +161,40 @@ def test_blob_roundtrip_and_save_load(tmp_path):
     g3 = aha_b200.AC.load(p)
     assert [(h[1], h[2]) for h in as_tuples(g3.match("我是中国人"))] == [(1, 0), (2, 1), (3, 2)]
     assert g3[1] == "我是"
+
+
+def _trie3():
+    t = aha_b200.Cedar()
+    for s in ["Ruby", "ruby", "rub"]:
+        t.insert(s)
+    return t
+
+
+def test_cedar_match_longest_spec_vectors():  # spec/cedar_match_spec.cr:4-30, 51-63
+    t = _trie3()
+    got = [(s, e, t[v]) for s, e, v in as_tuples(t.match_longest("Ruby on rub", False))]
+    assert got == [(0, 4, "Ruby"), (8, 11, "rub")]
+    got = sorted((s, e, t[v]) for s, e, v in as_tuples(t.match_longest("Ruby on ruby", True)))
+    assert got == [(0, 4, "Ruby"), (8, 12, "ruby")]
+    got = sorted((s, e, t[v]) for s, e, v in as_tuples(t.match_longest("Ruby rRuby on rubyx ruby", True, sep=[" "])))
+    assert got == [(0, 4, "Ruby"), (20, 24, "ruby")]
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_cedar_match_longest_random(seed):
+    rng = random.Random(seed)
+    letters = "abAB cCdé日本Я" if seed % 2 else "abAB "
+    words = list(dict.fromkeys("".join(rng.choice(letters.replace(" ", "")) for _ in range(rng.randint(1, 5))) for _ in range(200)))
+    words += ["a b", "ab a"]
+    words = list(dict.fromkeys(words))
+    gt, ot = aha_b200.Cedar(), O.Cedar()
+    for w in words:
+        assert gt.insert(w) == ot.insert(w)
+    docs = ["".join(rng.choice(letters) for _ in range(rng.randint(0, 300))) for _ in range(30)] + ["", " ", "a"]
+    for icase in (False, True):
+        for sep in (None, [" "]):
+            res = gt.match_longest_batch(docs, icase, sep)
+            want = [ot.match_longest(d, icase, sep) for d in docs]
+            off = np.cumsum([0] + [len(w) for w in want])
+            assert np.array_equal(res.doc_hit_off(), off)
+            assert res.hits().tobytes() == np.concatenate(want).tobytes()

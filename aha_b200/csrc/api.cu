@@ -19,14 +19,10 @@ namespace aha {
 thread_local std::string g_err;
 static std::mutex g_mu;
 static std::vector<int> g_devices;  // devices selected by aha_b200_init
-static int g_impl = -1;             // 0: two-pass v1 kernels, 1: fused kernel (default); env AHA_B200_IMPL
-
+// 0: two-pass v1 kernels (checker), 1: fused single-pass kernel (default); env AHA_B200_IMPL, read per call
 static int scan_impl() {
-  if (g_impl < 0) {
-    const char* e = getenv("AHA_B200_IMPL");
-    g_impl = (e && e[0] == '0') ? 0 : 1;
-  }
-  return g_impl;
+  const char* e = getenv("AHA_B200_IMPL");
+  return (e && e[0] == '0') ? 0 : 1;
 }
 
 static int32_t ensure_devices() {

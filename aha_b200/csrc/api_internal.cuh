@@ -61,6 +61,7 @@ struct aha_dfa {
   std::vector<uint8_t> blob;  // host copy
   aha::BlobHeader header;
   std::vector<aha::DeviceDfa> dev;
+  mutable double hits_per_byte = -1.0;  // largest hit density seen so far: sizes the hit buffer of the fused scan
   const aha::DeviceDfa* on(int device) const {
     for (const auto& d : dev)
       if (d.device == device) return &d;

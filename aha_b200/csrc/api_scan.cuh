@@ -123,11 +123,119 @@ static int32_t run_v1(ScanParams p, cudaStream_t st, aha_hits* res, HitsOwner* o
   return AHA_OK;
 }
 
-#ifndef AHA_HAVE_FUSED
-static int32_t run_fused(ScanParams p, const DeviceDfa*, cudaStream_t st, aha_hits* res, HitsOwner* own, cudaEvent_t ev0, cudaEvent_t ev1) {
-  return run_v1(p, st, res, own, ev0, ev1);
+// single-pass fused kernel: see scan_fused.cuh
+template <class Policy>
+static int32_t launch_fused(const FusedParams& fp, const Policy& pol, int n_sm, size_t smem, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    AHA_CUDA(cudaFuncSetAttribute(scan_fused_kernel<Policy>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
+  }
+  scan_fused_kernel<Policy><<<n_sm, kFusedWarps * 32, smem, st>>>(fp, pol);
+  AHA_CUDA(cudaGetLastError());
+  return AHA_OK;
 }
-#endif
+
+static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, cudaStream_t st, aha_hits* res, HitsOwner* own,
+                         cudaEvent_t ev0, cudaEvent_t ev1) {
+  int dev = 0, n_sm = 0;
+  AHA_CUDA(cudaGetDevice(&dev));
+  AHA_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+  FusedParams fp;
+  memset(&fp, 0, sizeof(fp));
+  fp.chunk = 132;
+  fp.tile = 32 * fp.chunk;
+  fp.w16 = (int32_t)((p.warm + 1 + 3 + 15) & ~15u);
+  if (fp.w16 < 16) fp.w16 = 16;
+  fp.buf_bytes = (fp.w16 + fp.tile + 16 + 127) & ~127;
+  fp.n_tiles = (p.total + fp.tile - 1) / fp.tile;
+  const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
+  const int64_t n_warps = (int64_t)n_sm * kFusedWarps;
+  unsigned long long* tile_state = nullptr;
+  unsigned int* counters = nullptr;  // [0] ticket, [1] n_direct, [2..3] total_hits (u64)
+  uint32_t* lead_counts = nullptr;
+  uint64_t* tile_lead = nullptr;
+  uint64_t* doc_lead = nullptr;
+  AHA_CUDA(cudaMallocAsync(&tile_state, (fp.n_tiles + 1) * sizeof(unsigned long long), st));
+  AHA_CUDA(cudaMallocAsync(&counters, 16, st));
+  AHA_CUDA(cudaMallocAsync(&fp.scratch, (size_t)n_warps * 32 * kLaneCap * sizeof(aha_hit), st));
+  AHA_CUDA(cudaMallocAsync(&fp.marks, (size_t)n_warps * 32 * kMarkCap * sizeof(int2), st));
+  AHA_CUDA(cudaMallocAsync(&own->dev_doc_hit_off, (p.n_docs + 1) * sizeof(int64_t), st));
+  p.doc_hit_off = static_cast<int64_t*>(own->dev_doc_hit_off);
+  fp.tile_state = tile_state;
+  fp.ticket = counters;
+  fp.n_direct = counters + 1;
+  fp.total_hits = reinterpret_cast<unsigned long long*>(counters + 2);
+  ByteGlobal pol;
+  pol.cmap_g = p.classmap;
+  pol.cmap = nullptr;
+  const size_t smem = ((ByteGlobal::table_bytes(pol) + 127) & ~127u) + (size_t)kFusedWarps * (fp.buf_bytes + 128);
+
+  AHA_CUDA(cudaEventRecord(ev0, st));
+  if (chars && p.total > 0) {
+    AHA_CUDA(cudaMallocAsync(&lead_counts, (fp.n_tiles + 1) * sizeof(uint32_t), st));
+    AHA_CUDA(cudaMallocAsync(&tile_lead, (fp.n_tiles + 1) * sizeof(uint64_t), st));
+    AHA_CUDA(cudaMallocAsync(&doc_lead, (p.n_docs + 1) * sizeof(uint64_t), st));
+    count_leads_kernel<<<(unsigned)((fp.n_tiles + 1 + 127) / 128), 128, 0, st>>>(p.text, p.total, fp.tile, fp.n_tiles, lead_counts);
+    int32_t rc = exclusive_sum_u32_to_u64(lead_counts, tile_lead, fp.n_tiles + 1, st);
+    if (rc) return rc;
+    doc_lead_base_kernel<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(p.text, p.total, p.doc_off, p.n_docs, fp.tile,
+                                                                              tile_lead, doc_lead);
+    fp.tile_lead = tile_lead;
+    p.doc_lead_base = doc_lead;
+  }
+  // capacity of the hit buffer: exact after a counting run on first use, density history afterwards
+  const bool count_only = (p.mode & AHA_COUNT_ONLY) != 0;
+  unsigned long long total_hits = 0;
+  int64_t cap = 0;
+  bool have_result = false;
+  for (int attempt = 0; attempt < 3 && !have_result; ++attempt) {
+    bool counting = count_only || (attempt == 0 && dfa->hits_per_byte < 0);
+    if (!counting) {
+      if (attempt == 0 || cap == 0) cap = (int64_t)((double)p.total * dfa->hits_per_byte * 1.25) + 4096;
+      if (own->dev_hits) AHA_CUDA(cudaFreeAsync(own->dev_hits, st));
+      AHA_CUDA(cudaMallocAsync(&own->dev_hits, (size_t)cap * sizeof(aha_hit), st));
+    }
+    p.hits = counting ? nullptr : static_cast<aha_hit*>(own->dev_hits);
+    fp.hit_cap = counting ? 0 : cap;
+    fp.sp = p;
+    AHA_CUDA(cudaMemsetAsync(tile_state, 0, (fp.n_tiles + 1) * sizeof(unsigned long long), st));
+    AHA_CUDA(cudaMemsetAsync(counters, 0, 16, st));
+    AHA_CUDA(cudaMemsetAsync(own->dev_doc_hit_off, 0, (p.n_docs + 1) * sizeof(int64_t), st));
+    if (fp.n_tiles > 0) {
+      int32_t rc = launch_fused(fp, pol, n_sm, smem, st);
+      if (rc) return rc;
+    }
+    finalize_doc_off_kernel<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(p.doc_off, p.n_docs, p.total, fp.total_hits,
+                                                                                 p.doc_hit_off);
+    AHA_CUDA(cudaEventRecord(ev1, st));
+    AHA_CUDA(cudaMemcpyAsync(&total_hits, fp.total_hits, sizeof(total_hits), cudaMemcpyDeviceToHost, st));
+    AHA_CUDA(cudaStreamSynchronize(st));
+    const double dens = p.total > 0 ? (double)total_hits / (double)p.total : 0.0;
+    if (dens > dfa->hits_per_byte) dfa->hits_per_byte = dens;
+    if (counting) {
+      if (count_only) have_result = true;
+      else cap = (int64_t)total_hits + 1;  // exact capacity for the real run
+    } else if ((int64_t)total_hits <= cap) {
+      have_result = true;
+    } else {
+      cap = (int64_t)total_hits + 1;  // estimate was too small: rerun with the exact size
+    }
+    if (!have_result) AHA_CUDA(cudaEventRecord(ev0, st));  // time only the run that delivers
+  }
+  if (!have_result) return set_err(AHA_ERR_STATE, "hit buffer sizing did not converge");
+  res->n_hits = (int64_t)total_hits;
+  AHA_CUDA(cudaFreeAsync(tile_state, st));
+  AHA_CUDA(cudaFreeAsync(counters, st));
+  AHA_CUDA(cudaFreeAsync(fp.scratch, st));
+  AHA_CUDA(cudaFreeAsync(fp.marks, st));
+  if (lead_counts) {
+    AHA_CUDA(cudaFreeAsync(lead_counts, st));
+    AHA_CUDA(cudaFreeAsync(tile_lead, st));
+    AHA_CUDA(cudaFreeAsync(doc_lead, st));
+  }
+  return AHA_OK;
+}
 
 static int32_t scan_on_device(const aha_dfa* d, const void* dev_text, const void* dev_doc_off, int64_t n_docs,
                               int64_t total, uint32_t mode, const uint8_t* sep_bits, int32_t sep_size, cudaStream_t st,
@@ -149,8 +257,9 @@ static int32_t scan_on_device(const aha_dfa* d, const void* dev_text, const void
   cudaEvent_t ev0, ev1;
   AHA_CUDA(cudaEventCreate(&ev0));
   AHA_CUDA(cudaEventCreate(&ev1));
-  const bool fused_ok = scan_impl() == 1 && !(mode & (AHA_LONGEST | AHA_TRIE_LONGEST));
-  if (fused_ok) rc = run_fused(p, dd, st, res, own, ev0, ev1);
+  const bool fused_ok = scan_impl() == 1 && !(mode & (AHA_LONGEST | AHA_TRIE_LONGEST)) &&
+                        (reinterpret_cast<uintptr_t>(dev_text) & 15) == 0 && dd->view.max_key_len <= 1024;
+  if (fused_ok) rc = run_fused(p, dd, d, st, res, own, ev0, ev1);
   else rc = run_v1(p, st, res, own, ev0, ev1);
   if (rc == AHA_OK) {
     AHA_CUDA(cudaEventSynchronize(ev1));

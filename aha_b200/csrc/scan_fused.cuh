@@ -1,11 +1,340 @@
-// scan_fused.cuh -- single-pass fused scan kernel (placeholder until the fused kernel lands).
+// scan_fused.cuh -- single-pass fused scan kernel for ACX#match / match(sep) (ac.cr:176-192, 265-286, 321-340).
+//
+// Persistent grid, one CTA per SM, every WARP is an independent worker:
+//   * takes the next tile (32 lanes x `chunk` bytes of the concatenated text) from a global ticket,
+//   * stages it (plus the warm-up bytes in front of it) into its private shared-memory buffer with one
+//     TMA bulk copy (cp.async.bulk + mbarrier), no block-wide barrier in steady state,
+//   * each lane walks its own chunk: warm-up over the preceding max_key_len-1 bytes of the document,
+//     then reports the hits whose last byte falls in [a, b) ("owned region": boundary hits are neither
+//     missed nor duplicated),
+//   * hits go to a lane-private slot of an L2-resident scratch ring; lane counts are prefix-summed in the
+//     warp, the tile's global offset comes from a decoupled look-back over tile_state[], and the warp
+//     copies its hits to their final position -- the stream is already in reference order
+//     (document, end ascending, output-chain order), no sort needed,
+//   * if a lane's scratch slot (or its document-start markers) overflow, the warp re-walks the tile from
+//     shared memory with the now known offsets and writes directly ("direct" pass).
+// The automaton policy decides how one symbol is consumed: ByteGlobal (dense byte-class table in
+// global/L2, any dictionary) or CharTable (UTF-8 character automaton resident in shared memory).
 #pragma once
 #include "api_internal.cuh"
 #include "scan_common.cuh"
 
 namespace aha {
+
+constexpr int kLaneCap = 32;      // scratch records per lane per tile
+constexpr int kMarkCap = 2;       // document-start markers per lane per tile
+constexpr int kFusedWarps = 16;   // warps per CTA
+
+struct FusedParams {
+  ScanParams sp;
+  int32_t chunk;         // bytes per lane; chunk/4 is odd so lanes hit distinct banks
+  int32_t tile;          // 32 * chunk
+  int32_t w16;           // staged bytes in front of the tile (multiple of 16, > warm)
+  int32_t buf_bytes;     // per-warp text buffer = w16 + tile + 16
+  int64_t n_tiles;
+  unsigned long long* tile_state;  // [n_tiles] (value << 2) | flag ; flag 1 = aggregate, 2 = inclusive prefix
+  unsigned int* ticket;
+  unsigned long long* total_hits;  // out: total number of hits
+  int64_t hit_cap;                 // capacity of sp.hits (records); writes beyond are dropped
+  aha_hit* scratch;                // [n_warps_total][32][kLaneCap]
+  int2* marks;                     // [n_warps_total][32][kMarkCap] (doc index low/high packed, seq)
+  unsigned int* n_direct;          // diagnostics: tiles that took the direct pass
+  const uint64_t* tile_lead;       // [n_tiles + 1] non-continuation bytes before each tile (AHA_UNITS_CHAR)
+};
+
+// ---- PTX helpers ---------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n .reg .pred p;\n WAIT_%=:\n mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n @p bra DONE_%=;\n bra WAIT_%=;\n DONE_%=:\n}\n" ::"r"(
+          smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// TMA bulk copy global -> shared, completion signalled on an mbarrier (UBLKCP in SASS)
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// ---- sinks ---------------------------------------------------------------------------------------
+// ScratchSink: first pass; lane-private records + markers, counts everything.
+struct ScratchSink {
+  aha_hit* rec;   // lane slot [kLaneCap]
+  int2* mark;     // lane slot [kMarkCap]
+  uint32_t n = 0, n_mark = 0;
+  __device__ __forceinline__ void hit(int32_t start, int32_t end, int32_t value) {
+    if (n < (uint32_t)kLaneCap) rec[n] = aha_hit{start, end, value};
+    ++n;
+  }
+  __device__ __forceinline__ void doc_start(int64_t d) {
+    if (n_mark < (uint32_t)kMarkCap) mark[n_mark] = make_int2((int)d, (int)n);
+    ++n_mark;
+  }
+  __device__ __forceinline__ bool want_records() const { return true; }
+};
+// DirectSink: offsets known; writes final positions.
+struct DirectSink {
+  aha_hit* out;
+  int64_t* doc_hit_off;
+  int64_t idx, cap;
+  __device__ __forceinline__ void hit(int32_t start, int32_t end, int32_t value) {
+    if (out && idx < cap) out[idx] = aha_hit{start, end, value};
+    ++idx;
+  }
+  __device__ __forceinline__ void doc_start(int64_t d) { doc_hit_off[d] = idx; }
+  __device__ __forceinline__ bool want_records() const { return true; }
+};
+
+// expands the output list of `state` for a match whose last byte is absolute position `pos`
+template <class Sink>
+__device__ __forceinline__ void emit_list(const ScanParams& p, Sink& sink, uint32_t state, int64_t pos, int64_t doc_start,
+                                          int64_t doc_end, uint32_t end_char) {
+  if ((p.mode & AHA_SEP) && pos + 1 < doc_end && sep_rejects(p, p.text[pos + 1])) return;
+  const uint32_t j1 = p.out_off[state + 1];
+  const int32_t end = (int32_t)(pos - doc_start + 1);
+  for (uint32_t j = p.out_off[state]; j < j1; ++j) {
+    const int32_t v = p.out_val[j];
+    const int32_t start = end - (int32_t)p.key_len[v];
+    if ((p.mode & AHA_SEP) && start > 0 && sep_rejects(p, p.text[doc_start + start - 1])) continue;
+    if (p.mode & AHA_UNITS_CHAR) sink.hit((int32_t)end_char - 1 - (int32_t)p.key_tail[v], (int32_t)end_char, v);
+    else sink.hit(start, end, v);
+  }
+}
+
+// ---- policy: dense byte-class table in global memory / L2 -----------------------------------------
+struct ByteGlobal {
+  static constexpr int kExtraWarm = 0;
+  const uint8_t* cmap_g;  // class map in global memory
+  const uint8_t* cmap;    // shared memory copy (set by load_tables)
+  __host__ __device__ static uint32_t table_bytes(const ByteGlobal&) { return 256; }
+  __device__ __forceinline__ void load_tables(uint8_t* tables, int tid, int nthreads) {
+    for (int i = tid; i < 256; i += nthreads) tables[i] = cmap_g[i];
+    cmap = tables;
+  }
+  // Walks lane chunk [a, b) of the staged text.  sbuf[i] is absolute byte (buf_origin + i).
+  template <class Sink>
+  __device__ __forceinline__ void walk(const FusedParams& P, const uint8_t* sbuf, int64_t buf_origin, int64_t a, int64_t b,
+                                       uint32_t lead0, Sink& sink) const {
+    const ScanParams& p = P.sp;
+    if (a >= b) return;
+    int64_t d = last_le(p.doc_off, p.n_docs, a);
+    int64_t doc_start = p.doc_off[d], doc_end = p.doc_off[d + 1];
+    const uint32_t C = p.C;
+    const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
+    uint32_t lead = lead0;  // characters of the current document up to (excluding) position a
+    if (doc_start == a) {
+      for (int64_t e = first_ge(p.doc_off, p.n_docs, a); e <= d; ++e) sink.doc_start(e);
+    }
+    uint32_t s = 0;
+    {
+      int64_t w = a - (int64_t)p.warm;
+      if (w < doc_start) w = doc_start;
+      for (int64_t i = w; i < a; ++i) s = __ldg(&p.delta[(uint64_t)s * C + cmap[sbuf[i - buf_origin]]]) & kStateMask;
+    }
+    int64_t pos = a;
+    while (pos < b) {
+      const int64_t seg_end = min(b, doc_end);
+      for (; pos < seg_end; ++pos) {
+        const uint8_t byte = sbuf[pos - buf_origin];
+        if (chars) lead += ((byte & 0xC0) != 0x80);
+        const uint32_t e = __ldg(&p.delta[(uint64_t)s * C + cmap[byte]]);
+        s = e & kStateMask;
+        if (e & kOut) emit_list(p, sink, s, pos, doc_start, doc_end, lead);
+      }
+      if (pos == doc_end && (pos < b || b == p.total)) {
+        s = 0;
+        lead = 0;
+        ++d;
+        while (d < p.n_docs) {
+          sink.doc_start(d);
+          if (p.doc_off[d + 1] > pos) break;
+          ++d;
+        }
+        if (d >= p.n_docs) break;
+        doc_start = p.doc_off[d];
+        doc_end = p.doc_off[d + 1];
+      }
+    }
+  }
+};
+
+// characters (non-continuation bytes) of the document containing `a` that lie in [doc_start, a): only the
+// part inside this tile is counted here; the caller adds the per-tile prefix.
+__device__ __forceinline__ uint32_t count_leads_smem(const uint8_t* sbuf, int64_t buf_origin, int64_t from, int64_t to) {
+  uint32_t c = 0;
+  for (int64_t i = from; i < to; ++i) c += ((sbuf[i - buf_origin] & 0xC0) != 0x80);
+  return c;
+}
+
+template <class Policy>
+__global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_fused_kernel(const FusedParams P, const Policy policy_in) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const ScanParams& p = P.sp;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // shared layout: [policy tables][per-warp: mbarrier(16 B) + text buffer]
+  uint8_t* tables = smem;
+  const uint32_t table_bytes = Policy::table_bytes(policy_in);
+  Policy policy = policy_in;
+  policy.load_tables(tables, threadIdx.x, blockDim.x);
+  uint8_t* wbase = smem + ((table_bytes + 127) & ~127u) + (size_t)warp * (size_t)(P.buf_bytes + 128);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(wbase);
+  uint8_t* sbuf = wbase + 128;
+  if (lane == 0) mbar_init(bar, 1);
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  __syncthreads();
+
+  const int64_t gwarp = (int64_t)blockIdx.x * kFusedWarps + warp;
+  aha_hit* my_rec = P.scratch + (gwarp * 32 + lane) * kLaneCap;
+  int2* my_mark = P.marks + (gwarp * 32 + lane) * kMarkCap;
+  uint32_t parity = 0;
+
+  for (;;) {
+    unsigned int t = 0;
+    if (lane == 0) t = atomicAdd(P.ticket, 1u);
+    t = __shfl_sync(0xffffffffu, t, 0);
+    if ((int64_t)t >= P.n_tiles) break;
+    const int64_t tile_start = (int64_t)t * P.tile;
+    const int64_t tile_end = min(tile_start + (int64_t)P.tile, p.total);
+    // ---- stage [origin, copy_end) : 16-byte aligned bulk copy + byte tail
+    const int64_t origin = max((int64_t)0, tile_start - (int64_t)P.w16);
+    const int64_t want_end = min(p.total, tile_end + 1);              // +1: right neighbour for the sep test
+    const int64_t bulk_end = origin + ((want_end - origin) & ~(int64_t)15);
+    if (lane == 0) {
+      if (bulk_end > origin) {
+        mbar_expect_tx(bar, (uint32_t)(bulk_end - origin));
+        bulk_g2s(sbuf, p.text + origin, (uint32_t)(bulk_end - origin), bar);
+      }
+    }
+    for (int64_t i = bulk_end + lane; i < want_end; i += 32) sbuf[i - origin] = p.text[i];
+    if (bulk_end > origin) {
+      mbar_wait(bar, parity);
+      parity ^= 1u;
+    }
+    __syncwarp();
+
+    const int64_t a = min(tile_start + (int64_t)lane * P.chunk, tile_end);
+    const int64_t b = min(a + (int64_t)P.chunk, tile_end);
+    // characters before `a` inside the current document (AHA_UNITS_CHAR)
+    uint32_t lead0 = 0;
+    if (p.mode & AHA_UNITS_CHAR) {
+      // per-lane count of its own chunk, exclusive warp scan, plus the tile prefix, minus the document base
+      uint32_t mine = count_leads_smem(sbuf, origin, a, b);
+      uint32_t incl = mine;
+      for (int o = 1; o < 32; o <<= 1) {
+        uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+      }
+      const uint64_t before_a = P.tile_lead[t] + (incl - mine);
+      if (a < b) {
+        const int64_t d = last_le(p.doc_off, p.n_docs, a);
+        lead0 = (uint32_t)(before_a - p.doc_lead_base[d]);
+      }
+    }
+
+    ScratchSink ss;
+    ss.rec = my_rec;
+    ss.mark = my_mark;
+    policy.walk(P, sbuf, origin, a, b, lead0, ss);
+
+    // ---- warp prefix of lane counts, tile aggregate
+    uint32_t incl = ss.n;
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    const uint32_t excl_lane = incl - ss.n;
+    const uint32_t T = __shfl_sync(0xffffffffu, incl, 31);
+    // ---- decoupled look-back
+    unsigned long long prefix = 0;
+    if (t == 0) {
+      if (lane == 0) st_relaxed_u64(&P.tile_state[0], ((unsigned long long)T << 2) | 2ull);
+    } else {
+      if (lane == 0) st_relaxed_u64(&P.tile_state[t], ((unsigned long long)T << 2) | 1ull);
+      int64_t j = (int64_t)t - 1;
+      for (;;) {
+        const int64_t idx = j - lane;
+        unsigned long long v = 2ull;  // virtual "inclusive 0" before tile 0
+        if (idx >= 0) v = ld_relaxed_u64(&P.tile_state[idx]);
+        const unsigned m_incl = __ballot_sync(0xffffffffu, (v & 3ull) == 2ull);
+        const unsigned m_zero = __ballot_sync(0xffffffffu, (v & 3ull) == 0ull);
+        const int first_incl = m_incl ? (__ffs(m_incl) - 1) : 32;
+        const unsigned need = first_incl >= 32 ? 0xffffffffu : ((2u << first_incl) - 1u);
+        if (m_zero & need) continue;  // a needed predecessor has not published yet
+        unsigned long long part = (lane <= first_incl) ? (v >> 2) : 0ull;
+        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+        prefix += part;
+        if (first_incl < 32) break;
+        j -= 32;
+      }
+      if (lane == 0) st_relaxed_u64(&P.tile_state[t], ((prefix + T) << 2) | 2ull);
+    }
+    if ((int64_t)t == P.n_tiles - 1 && lane == 0) *P.total_hits = prefix + T;
+
+    // ---- deliver
+    const bool over = (ss.n > (uint32_t)kLaneCap) || (ss.n_mark > (uint32_t)kMarkCap);
+    const bool any_over = __any_sync(0xffffffffu, over);
+    if (!any_over) {
+      // markers first (they only need the lane base)
+      for (uint32_t k = 0; k < ss.n_mark; ++k) p.doc_hit_off[my_mark[k].x] = (int64_t)(prefix + excl_lane + (uint32_t)my_mark[k].y);
+      if (p.hits && T > 0) {
+        // cooperative copy: output index i -> (lane l, record k) by binary search over the lane prefix
+        __syncwarp();
+        for (uint32_t i = lane; i < ((T + 31u) & ~31u); i += 32) {
+          uint32_t lo = 0;
+#pragma unroll
+          for (int step = 16; step > 0; step >>= 1) {
+            const uint32_t cand = lo + step;
+            const uint32_t ex = __shfl_sync(0xffffffffu, excl_lane, cand & 31);
+            if (cand < 32 && ex <= i) lo = cand;
+          }
+          const uint32_t ex = __shfl_sync(0xffffffffu, excl_lane, lo);
+          if (i < T) {
+            const int64_t dst = (int64_t)prefix + i;
+            if (dst < P.hit_cap) p.hits[dst] = P.scratch[(gwarp * 32 + lo) * kLaneCap + (i - ex)];
+          }
+        }
+      }
+    } else {
+      if (lane == 0) atomicAdd(P.n_direct, 1u);
+      DirectSink ds;
+      ds.out = p.hits;
+      ds.doc_hit_off = p.doc_hit_off;
+      ds.idx = (int64_t)(prefix + excl_lane);
+      ds.cap = P.hit_cap;
+      policy.walk(P, sbuf, origin, a, b, lead0, ds);
+    }
+    __syncwarp();
+    fence_proxy_async();  // reads of sbuf are done before the next bulk copy overwrites it
+  }
+}
+
+// documents that start at the very end of the text (trailing empty documents and the n_docs sentinel)
+__global__ void finalize_doc_off_kernel(const int64_t* doc_off, int64_t n_docs, int64_t total,
+                                        const unsigned long long* total_hits, int64_t* doc_hit_off) {
+  const int64_t d = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (d <= n_docs && doc_off[d] >= total) doc_hit_off[d] = (int64_t)*total_hits;
+}
+
 static int32_t build_hot_table(const aha_dfa*, DeviceDfa* dd) {
   dd->hot = HotTable();
   return AHA_OK;
 }
+
 }  // namespace aha

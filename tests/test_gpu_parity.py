@@ -13,6 +13,13 @@ from tests.test_oracle_kat import _rand_keys
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=["fused", "two-pass"])
+def scan_impl(request, monkeypatch):
+    """every parity test runs against both device paths: the fused single-pass kernel and the two-pass baseline"""
+    monkeypatch.setenv("AHA_B200_IMPL", "1" if request.param == "fused" else "0")
+    return request.param
+
+
 def as_tuples(h):
     return [(int(x["start"]), int(x["end"]), int(x["value"])) for x in h]
 

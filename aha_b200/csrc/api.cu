@@ -9,6 +9,8 @@
 
 #include "api_internal.cuh"
 #include "gen.cuh"
+#include "char_table.hpp"
+#include "char_walk.cuh"
 #include "scan_common.cuh"
 #include "scan_v1.cuh"
 #include "scan_trie.cuh"
@@ -232,6 +234,51 @@ void aha_b200_dfa_free(aha_dfa* d) {
   }
   cudaSetDevice(prev);
   delete d;
+}
+
+int32_t aha_b200_debug_char_scan(const uint8_t* blob, int64_t blob_bytes, const uint8_t* text, int64_t n, int32_t chunk,
+                                 int64_t smem_budget, aha_hit* hits, int64_t cap, int64_t* n_hits, int64_t* info) {
+  if (!blob || !n_hits || !info || chunk <= 0 || n < 0 || n > INT32_MAX - 64) return set_err(AHA_ERR_ARG, "bad argument");
+  BlobHeader h;
+  std::string err;
+  if (!parse_blob(blob, blob_bytes, &h, &err)) return set_err(AHA_ERR_ARG, err);
+  const DfaView v = view_of(h, blob);
+  CharTableHost T = build_char_table(h, blob, (size_t)smem_budget);
+  memset(info, 0, 8 * sizeof(int64_t));
+  *n_hits = 0;
+  if (!T.ok) return set_err(AHA_OK, T.why);
+  info[0] = 1;
+  info[2] = T.n_cid; info[3] = T.m; info[4] = T.n_states; info[5] = (int64_t)T.root.size(); info[6] = T.n_edges;
+  info[7] = (int64_t)T.smem_bytes();
+  CharTablesView tv;
+  tv.root = T.root.data(); tv.check = T.check.data(); tv.val = T.val.data(); tv.gfail = T.gfail.data();
+  for (int c = 0; c < 3; ++c) { tv.lo[c] = T.lo[c]; tv.n[c] = T.n[c]; tv.off[c] = T.off[c]; }
+  tv.m = T.m;
+  const int32_t warmc = (int32_t)(v.max_key_len > 0 ? v.max_key_len - 1 : 0) + 3;
+  int64_t cnt = 0;
+  bool valid = true;
+  for (int64_t a = 0; a < n && valid; a += chunk) {
+    const int32_t b = (int32_t)std::min<int64_t>(a + chunk, n);
+    const int32_t w = (int32_t)std::max<int64_t>(0, a - warmc);
+    const int st = char_walk(tv, text, w, (int32_t)a, b, b, (int32_t)n, w == 0, [&](uint32_t ref, uint32_t multi, int32_t last, uint32_t) {
+      const RefRec rr = T.ref_rec[ref];
+      if ((rr.n > 1) != (multi != 0) || rr.n == 0) { valid = false; return; }
+      if (rr.n == 1) {
+        if (hits && cnt < cap) hits[cnt] = aha_hit{last + 1 - (int32_t)rr.b, last + 1, (int32_t)rr.a};
+        ++cnt;
+        return;
+      }
+      for (uint32_t j = rr.a; j < rr.b; ++j) {
+        const int32_t val = v.out_val[j];
+        if (hits && cnt < cap) hits[cnt] = aha_hit{last + 1 - (int32_t)v.key_len[val], last + 1, val};
+        ++cnt;
+      }
+    });
+    if (st != kWalkOk) valid = false;
+  }
+  info[1] = valid ? 1 : 0;
+  *n_hits = cnt;
+  return AHA_OK;
 }
 
 }  // extern "C"

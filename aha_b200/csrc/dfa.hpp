@@ -42,6 +42,7 @@ struct BlobHeader {
   uint64_t off_key_len;   // u32[n_keys]
   uint64_t off_key_tail;  // u32[n_keys]: non-continuation bytes in key[1..]: char-unit start remap
   uint64_t off_depth;     // u16[n_states]: depth in bytes (diagnostics, hot-set selection)
+  uint64_t off_fail;      // u32[n_states]: failure link (ac.cr:96-105) in state numbering
   uint64_t total_bytes;
 };
 
@@ -56,6 +57,7 @@ struct DfaView {
   const uint32_t* key_len;
   const uint32_t* key_tail;
   const uint16_t* depth;
+  const uint32_t* fail;
   uint32_t n_classes;
   uint32_t max_key_len;
   uint64_t n_states, n_keys, n_out;
@@ -70,6 +72,7 @@ inline DfaView view_of(const BlobHeader& h, const uint8_t* base) {
   v.key_len = reinterpret_cast<const uint32_t*>(base + h.off_key_len);
   v.key_tail = reinterpret_cast<const uint32_t*>(base + h.off_key_tail);
   v.depth = reinterpret_cast<const uint16_t*>(base + h.off_depth);
+  v.fail = reinterpret_cast<const uint32_t*>(base + h.off_fail);
   v.n_classes = h.n_classes;
   v.max_key_len = h.max_key_len;
   v.n_states = h.n_states;
@@ -170,7 +173,7 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
   BlobHeader h;
   memset(&h, 0, sizeof(h));
   h.magic = kBlobMagic;
-  h.version = 1;
+  h.version = 2;
   h.n_classes = C;
   h.n_states = S;
   h.n_keys = static_cast<uint64_t>(n_keys);
@@ -184,6 +187,7 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
   h.off_key_len = off; off = align16(off + static_cast<uint64_t>(n_keys) * 4);
   h.off_key_tail = off; off = align16(off + static_cast<uint64_t>(n_keys) * 4);
   h.off_depth = off; off = align16(off + S * 2);
+  h.off_fail = off; off = align16(off + S * 4);
   h.total_bytes = off;
   blob->assign(off, 0);
   uint8_t* p = blob->data();
@@ -212,6 +216,7 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
       }
       const uint32_t* frow = delta + static_cast<uint64_t>(state_of[f]) * C;
       for (uint32_t c = 0; c < C; ++c) row[c] = frow[c] & ~kGoto;
+      reinterpret_cast<uint32_t*>(p + h.off_fail)[s] = static_cast<uint32_t>(state_of[f]);
     }
     while (cursor < S && static_cast<uint64_t>(parent[cursor]) == s) {
       row[classmap[label[cursor]]] = static_cast<uint32_t>(cursor) | sflags[cursor] | kGoto;
@@ -227,7 +232,7 @@ inline bool parse_blob(const uint8_t* blob, int64_t bytes, BlobHeader* h, std::s
     return false;
   }
   memcpy(h, blob, sizeof(BlobHeader));
-  if (h->magic != kBlobMagic || h->version != 1 || h->total_bytes != static_cast<uint64_t>(bytes)) {
+  if (h->magic != kBlobMagic || h->version != 2 || h->total_bytes != static_cast<uint64_t>(bytes)) {
     *err = "bad blob header";
     return false;
   }

@@ -119,6 +119,15 @@ int32_t aha_b200_scan_device(const aha_dfa* d, const void* dev_text, const void*
                              void* stream, aha_hits** out);
 void aha_b200_hits_free(aha_hits* h);
 
+/* ---- diagnostics ------------------------------------------------------------------------- */
+/* Host-side replay of the shared-memory character automaton the fused kernel uses (same table builder,
+ * same per-lane walk, lanes emulated sequentially with `chunk`-byte owned regions) over ONE document.
+ * info[0] = 1 if the dictionary is eligible (whole UTF-8 units, fits `smem_budget`), info[1] = 1 if the
+ * text was structurally valid UTF-8, info[2..7] = n_cid, slots, b1, root entries, edges, table bytes.
+ * Writes at most cap hits (byte offsets); *n_hits = number found.  No device needed.            */
+int32_t aha_b200_debug_char_scan(const uint8_t* blob, int64_t blob_bytes, const uint8_t* text, int64_t n, int32_t chunk,
+                                 int64_t smem_budget, aha_hit* hits, int64_t cap, int64_t* n_hits, int64_t* info);
+
 /* ---- synthetic corpora: counter-based, identical bytes on host and device -- */
 enum aha_corpus { AHA_CORPUS_EN = 0, AHA_CORPUS_ZH = 1, AHA_CORPUS_MIX = 2 };
 /* fills out[0..bytes) with corpus text starting at absolute byte `first` of the stream */

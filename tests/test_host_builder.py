@@ -85,14 +85,16 @@ class BlobDfa:
         u64 = lambda o: int(np.frombuffer(raw[o:o + 8], "<u8")[0])
         u32 = lambda o: int(np.frombuffer(raw[o:o + 4], "<u4")[0])
         self.C, self.S, self.K, self.n_out, self.maxlen = u32(12), u64(16), u64(24), u64(32), u32(40)
-        offs = [u64(48 + 8 * i) for i in range(8)]
+        offs = [u64(48 + 8 * i) for i in range(9)]
         self.classmap = np.frombuffer(raw, np.uint8, 256, offs[0])
         self.delta = np.frombuffer(raw, "<u4", self.S * self.C, offs[1]).reshape(self.S, self.C)
         self.out_off = np.frombuffer(raw, "<u4", self.S + 1, offs[2])
         self.out_val = np.frombuffer(raw, "<i4", self.n_out, offs[3])
         self.key_len = np.frombuffer(raw, "<u4", self.K, offs[4])
         self.key_tail = np.frombuffer(raw, "<u4", self.K, offs[5])
-        assert offs[7] == len(raw)
+        assert offs[8] == len(raw)
+        self.fail = np.frombuffer(raw, '<u4', self.S, offs[7])
+        self.depth = np.frombuffer(raw, '<u2', self.S, offs[6])
 
     def match(self, text):
         hits, s = [], 0
@@ -160,3 +162,69 @@ def test_generator_is_deterministic_and_nul_free():
         assert np.array_equal(a[192 * 10 + 7:192 * 10 + 1007], b)
         assert (a != 0).all()
         a.tobytes().decode("utf-8")  # every block is valid UTF-8
+
+
+def _char_scan(blob, text, chunk, budget=200 * 1024):
+    L = _lib.lib()
+    a = np.frombuffer(text, dtype=np.uint8)
+    cap = 1 << 20
+    hits = np.zeros(cap, dtype=aha_b200.HIT_DTYPE)
+    n, info = C.c_int64(), (C.c_int64 * 8)()
+    bl = np.frombuffer(blob, dtype=np.uint8)
+    _lib.check(L.aha_b200_debug_char_scan(bl.ctypes.data, bl.size, a.ctypes.data if a.size else None, a.size, chunk, budget,
+                                          hits.ctypes.data, cap, C.byref(n), info))
+    return hits[: n.value], list(info)
+
+
+def _blob_of(keys):
+    da = aha_b200.Cedar()
+    for k in keys:
+        da.insert(k)
+    nodes, fails, output, kl = da.compiled_arrays()
+    blob, n = C.c_void_p(), C.c_int64()
+    L = _lib.lib()
+    _lib.check(L.aha_b200_flatten_host(nodes.ctypes.data, len(fails), fails.ctypes.data, output.ctypes.data,
+                                       kl.ctypes.data if len(kl) else None, len(kl), C.byref(blob), C.byref(n)))
+    raw = C.string_at(blob.value, n.value)
+    L.aha_b200_blob_free(blob)
+    return raw
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_char_automaton_replay_matches_oracle(seed):
+    """the shared-memory character automaton (tables + per-lane walk, replayed on the host) == oracle"""
+    rng = random.Random(seed)
+    alpha = ["ab", "abcé日本語Я𝄞 ", "的一是在不了有和人这中大为上个国我以要他时来用们生到作地于出就分对成会可主发年动同工也能下过子说产种面而方后多定行学法所民得经", "abc"][seed % 4]
+    keys = list(dict.fromkeys("".join(rng.choice(alpha) for _ in range(rng.randint(1, 5))) for _ in range(rng.choice([20, 400, 3000]))))
+    text = "".join(rng.choice(alpha) for _ in range(6000)).encode()
+    o = O.AC.compile(keys)
+    want = o.scan(text)
+    blob = _blob_of(keys)
+    for chunk in (1, 7, 132, 100000):
+        got, info = _char_scan(blob, text, chunk)
+        assert info[0] == 1 and info[1] == 1, info
+        assert got.tobytes() == want.tobytes(), (chunk, len(got), len(want))
+
+
+def test_char_automaton_eligibility_and_bad_text():
+    blob = _blob_of([b"\xe4\xb8", b"ab"])  # a key that stops inside a unit
+    _, info = _char_scan(blob, b"abc", 16)
+    assert info[0] == 0
+    blob = _blob_of([b"\x80x"])  # a key that starts with a continuation byte
+    _, info = _char_scan(blob, b"abc", 16)
+    assert info[0] == 0
+    blob = _blob_of(["日本", "ab"])
+    for bad in (b"ab\xe6\x97", b"ab\x80\x80ab", b"\xff", b"\xe6ab"):
+        _, info = _char_scan(blob, bad, 16)
+        assert info[0] == 1 and info[1] == 0, bad
+
+
+def test_char_automaton_c2_dictionary_fits_shared_memory():
+    from aha_b200 import synth
+    keys = synth.patterns_zh_ngrams(10000)
+    blob = _blob_of(keys)
+    text = synth.gen_host(synth.ZH, synth.SEED_TEXT + 1, 0, 192 * 600).tobytes()
+    got, info = _char_scan(blob, text, 132, 150 * 1024)
+    assert info[0] == 1 and info[1] == 1, info
+    want = O.AC.compile(keys).scan(text)
+    assert got.tobytes() == want.tobytes()

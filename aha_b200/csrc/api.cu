@@ -15,6 +15,7 @@
 #include "scan_v1.cuh"
 #include "scan_trie.cuh"
 #include "scan_fused.cuh"
+#include "scan_char.cuh"
 
 namespace aha {
 
@@ -39,6 +40,51 @@ static int32_t ensure_devices() {
   int cur = 0;
   AHA_CUDA(cudaGetDevice(&cur));
   g_devices.push_back(cur);
+  return AHA_OK;
+}
+
+// per-warp text buffer geometry of the fused kernels (shared by the table budget and the launcher)
+static void fused_geometry(uint32_t max_key_len, int32_t* chunk, int32_t* w16, int32_t* buf_bytes) {
+  const uint32_t warm = max_key_len > 0 ? max_key_len - 1 : 0;
+  *chunk = 132;
+  *w16 = (int32_t)((warm + 1 + 3 + 15) & ~15u);
+  if (*w16 < 16) *w16 = 16;
+  *buf_bytes = (*w16 + 32 * *chunk + 16 + 127) & ~127;
+}
+
+static int32_t build_hot_table(const aha_dfa* d, DeviceDfa* dd) {
+  dd->hot = HotTable();
+  const char* off = getenv("AHA_B200_NO_CHAR");
+  if (off && off[0] == '1') return AHA_OK;
+  int32_t chunk, w16, buf;
+  fused_geometry(d->header.max_key_len, &chunk, &w16, &buf);
+  const size_t total_smem = 227 * 1024;
+  const size_t per_warps = (size_t)kFusedWarps * (buf + 128) + 512;
+  if (per_warps + 4096 > total_smem) return AHA_OK;
+  CharTableHost T = build_char_table(d->header, d->blob.data(), total_smem - per_warps);
+  if (!T.ok) return AHA_OK;  // not eligible: the byte automaton in global memory serves this dictionary
+  HotTable& h = dd->hot;
+  auto place = [](size_t& cursor, size_t bytes) { size_t at = cursor; cursor = (cursor + bytes + 255) & ~size_t(255); return at; };
+  size_t cursor = 0;
+  h.off_root = place(cursor, T.root.size() * 4);
+  h.off_val = place(cursor, T.val.size() * 4);
+  h.off_check = place(cursor, T.check.size() * 2);
+  h.off_gfail = place(cursor, T.gfail.size() * 2);
+  h.off_ref = place(cursor, T.ref_rec.size() * sizeof(RefRec));
+  std::vector<uint8_t> stage(cursor, 0);
+  memcpy(stage.data() + h.off_root, T.root.data(), T.root.size() * 4);
+  memcpy(stage.data() + h.off_val, T.val.data(), T.val.size() * 4);
+  memcpy(stage.data() + h.off_check, T.check.data(), T.check.size() * 2);
+  memcpy(stage.data() + h.off_gfail, T.gfail.data(), T.gfail.size() * 2);
+  memcpy(stage.data() + h.off_ref, T.ref_rec.data(), T.ref_rec.size() * sizeof(RefRec));
+  AHA_CUDA(cudaMalloc(&h.dev, cursor));
+  AHA_CUDA(cudaMemcpy(h.dev, stage.data(), cursor, cudaMemcpyHostToDevice));
+  h.ok = true;
+  h.n_hot = T.n_states;
+  h.n_root = T.n_root;
+  h.m = T.m;
+  for (int c = 0; c < 3; ++c) { h.lo[c] = T.lo[c]; h.n[c] = T.n[c]; h.off[c] = T.off[c]; }
+  h.smem_bytes = T.smem_bytes();
   return AHA_OK;
 }
 
@@ -230,7 +276,7 @@ void aha_b200_dfa_free(aha_dfa* d) {
   for (auto& dd : d->dev) {
     cudaSetDevice(dd.device);
     cudaFree(dd.blob);
-    if (dd.hot.dev_rows) cudaFree(dd.hot.dev_rows);
+    if (dd.hot.dev) cudaFree(dd.hot.dev);
   }
   cudaSetDevice(prev);
   delete d;

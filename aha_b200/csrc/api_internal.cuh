@@ -28,11 +28,15 @@ inline int32_t set_err(int32_t code, const std::string& m) {
     }                                                                                                \
   } while (0)
 
-// hot table placed in shared memory by the fused kernel (built at upload time from the blob)
+// character automaton placed in shared memory by scan_char_kernel (built at upload time from the blob)
 struct HotTable {
-  uint32_t n_hot = 0;         // states [0, n_hot) have rows in shared memory
-  uint32_t row_stride = 0;    // u16 entries per row
-  uint16_t* dev_rows = nullptr;  // [n_hot][row_stride]
+  bool ok = false;            // dictionary is whole-UTF-8-unit and fits the shared-memory budget
+  uint32_t n_hot = 0;         // character-level states resident in shared memory
+  uint32_t n_root = 0, m = 0;
+  uint32_t lo[3] = {0, 0, 0}, n[3] = {0, 0, 0}, off[3] = {0, 0, 0};
+  uint8_t* dev = nullptr;     // one allocation: root | val | check | gfail | ref_rec
+  size_t off_root = 0, off_val = 0, off_check = 0, off_gfail = 0, off_ref = 0;
+  size_t smem_bytes = 0;
 };
 
 struct DeviceDfa {

@@ -126,11 +126,7 @@ static int32_t run_v1(ScanParams p, cudaStream_t st, aha_hits* res, HitsOwner* o
 // single-pass fused kernel: see scan_fused.cuh
 template <class Policy>
 static int32_t launch_fused(const FusedParams& fp, const Policy& pol, int n_sm, size_t smem, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    AHA_CUDA(cudaFuncSetAttribute(scan_fused_kernel<Policy>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set = true;
-  }
+  AHA_CUDA(cudaFuncSetAttribute(scan_fused_kernel<Policy>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   scan_fused_kernel<Policy><<<n_sm, kFusedWarps * 32, smem, st>>>(fp, pol);
   AHA_CUDA(cudaGetLastError());
   return AHA_OK;
@@ -143,11 +139,8 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
   AHA_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
   FusedParams fp;
   memset(&fp, 0, sizeof(fp));
-  fp.chunk = 132;
+  fused_geometry(p.warm + 1, &fp.chunk, &fp.w16, &fp.buf_bytes);
   fp.tile = 32 * fp.chunk;
-  fp.w16 = (int32_t)((p.warm + 1 + 3 + 15) & ~15u);
-  if (fp.w16 < 16) fp.w16 = 16;
-  fp.buf_bytes = (fp.w16 + fp.tile + 16 + 127) & ~127;
   fp.n_tiles = (p.total + fp.tile - 1) / fp.tile;
   const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
   const int64_t n_warps = (int64_t)n_sm * kFusedWarps;
@@ -158,7 +151,25 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
   uint64_t* doc_lead = nullptr;
   AHA_CUDA(cudaMallocAsync(&tile_state, (fp.n_tiles + 1) * sizeof(unsigned long long), st));
   AHA_CUDA(cudaMallocAsync(&counters, 16, st));
-  AHA_CUDA(cudaMallocAsync(&fp.scratch, (size_t)n_warps * 32 * kLaneCap * sizeof(aha_hit), st));
+  // character automaton in shared memory when the dictionary allows it (plain match, with or without char units)
+  const bool use_char = dd->hot.ok && !(p.mode & AHA_SEP);
+  CharParams cp;
+  memset(&cp, 0, sizeof(cp));
+  if (use_char) {
+    const HotTable& h = dd->hot;
+    cp.t.root_g = reinterpret_cast<const uint32_t*>(h.dev + h.off_root);
+    cp.t.val_g = reinterpret_cast<const uint32_t*>(h.dev + h.off_val);
+    cp.t.check_g = reinterpret_cast<const uint16_t*>(h.dev + h.off_check);
+    cp.t.gfail = reinterpret_cast<const uint16_t*>(h.dev + h.off_gfail);
+    cp.t.ref_rec = reinterpret_cast<const RefRec*>(h.dev + h.off_ref);
+    cp.t.n_root = h.n_root;
+    cp.t.m = h.m;
+    for (int c = 0; c < 3; ++c) { cp.t.lo[c] = h.lo[c]; cp.t.n[c] = h.n[c]; cp.t.off[c] = h.off[c]; }
+    cp.cmap_g = p.classmap;
+    AHA_CUDA(cudaMallocAsync(&cp.events, (size_t)n_warps * 32 * kEvCap * sizeof(CharEvent), st));
+  } else {
+    AHA_CUDA(cudaMallocAsync(&fp.scratch, (size_t)n_warps * 32 * kLaneCap * sizeof(aha_hit), st));
+  }
   AHA_CUDA(cudaMallocAsync(&fp.marks, (size_t)n_warps * 32 * kMarkCap * sizeof(int2), st));
   AHA_CUDA(cudaMallocAsync(&own->dev_doc_hit_off, (p.n_docs + 1) * sizeof(int64_t), st));
   p.doc_hit_off = static_cast<int64_t*>(own->dev_doc_hit_off);
@@ -169,7 +180,11 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
   ByteGlobal pol;
   pol.cmap_g = p.classmap;
   pol.cmap = nullptr;
-  const size_t smem = ((ByteGlobal::table_bytes(pol) + 127) & ~127u) + (size_t)kFusedWarps * (fp.buf_bytes + 128);
+  size_t smem = ((ByteGlobal::table_bytes(pol) + 127) & ~127u) + (size_t)kFusedWarps * (fp.buf_bytes + 128);
+  if (use_char) {
+    smem = ((dd->hot.smem_bytes + 127) & ~size_t(127)) + (size_t)kFusedWarps * (fp.buf_bytes + 128);
+    AHA_CUDA(cudaFuncSetAttribute(scan_char_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  }
 
   AHA_CUDA(cudaEventRecord(ev0, st));
   if (chars && p.total > 0) {
@@ -203,8 +218,14 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
     AHA_CUDA(cudaMemsetAsync(counters, 0, 16, st));
     AHA_CUDA(cudaMemsetAsync(own->dev_doc_hit_off, 0, (p.n_docs + 1) * sizeof(int64_t), st));
     if (fp.n_tiles > 0) {
-      int32_t rc = launch_fused(fp, pol, n_sm, smem, st);
-      if (rc) return rc;
+      if (use_char) {
+        cp.f = fp;
+        scan_char_kernel<<<n_sm, kFusedWarps * 32, smem, st>>>(cp);
+        AHA_CUDA(cudaGetLastError());
+      } else {
+        int32_t rc = launch_fused(fp, pol, n_sm, smem, st);
+        if (rc) return rc;
+      }
     }
     finalize_doc_off_kernel<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(p.doc_off, p.n_docs, p.total, fp.total_hits,
                                                                                  p.doc_hit_off);
@@ -227,7 +248,8 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
   res->n_hits = (int64_t)total_hits;
   AHA_CUDA(cudaFreeAsync(tile_state, st));
   AHA_CUDA(cudaFreeAsync(counters, st));
-  AHA_CUDA(cudaFreeAsync(fp.scratch, st));
+  if (fp.scratch) AHA_CUDA(cudaFreeAsync(fp.scratch, st));
+  if (cp.events) AHA_CUDA(cudaFreeAsync(cp.events, st));
   AHA_CUDA(cudaFreeAsync(fp.marks, st));
   if (lead_counts) {
     AHA_CUDA(cudaFreeAsync(lead_counts, st));

@@ -183,6 +183,35 @@ __device__ __forceinline__ uint32_t count_leads_smem(const uint8_t* sbuf, int64_
   return c;
 }
 
+// Decoupled look-back over tile_state[]: publishes this tile's aggregate T, returns the number of hits in
+// all earlier tiles, then publishes the inclusive prefix.  Whole warp participates.
+__device__ __forceinline__ unsigned long long tile_exclusive_prefix(const FusedParams& P, unsigned int t, uint32_t T, int lane) {
+  unsigned long long prefix = 0;
+  if (t == 0) {
+    if (lane == 0) st_relaxed_u64(&P.tile_state[0], ((unsigned long long)T << 2) | 2ull);
+    return 0;
+  }
+  if (lane == 0) st_relaxed_u64(&P.tile_state[t], ((unsigned long long)T << 2) | 1ull);
+  int64_t j = (int64_t)t - 1;
+  for (;;) {
+    const int64_t idx = j - lane;
+    unsigned long long v = 2ull;  // virtual "inclusive 0" before tile 0
+    if (idx >= 0) v = ld_relaxed_u64(&P.tile_state[idx]);
+    const unsigned m_incl = __ballot_sync(0xffffffffu, (v & 3ull) == 2ull);
+    const unsigned m_zero = __ballot_sync(0xffffffffu, (v & 3ull) == 0ull);
+    const int first_incl = m_incl ? (__ffs(m_incl) - 1) : 32;
+    const unsigned need = first_incl >= 31 ? 0xffffffffu : ((2u << first_incl) - 1u);
+    if (m_zero & need) continue;  // a needed predecessor has not published yet
+    unsigned long long part = (lane <= first_incl) ? (v >> 2) : 0ull;
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+    prefix += part;
+    if (first_incl < 32) break;
+    j -= 32;
+  }
+  if (lane == 0) st_relaxed_u64(&P.tile_state[t], ((prefix + T) << 2) | 2ull);
+  return prefix;
+}
+
 template <class Policy>
 __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_fused_kernel(const FusedParams P, const Policy policy_in) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -262,29 +291,7 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_fused_kernel(const F
     const uint32_t excl_lane = incl - ss.n;
     const uint32_t T = __shfl_sync(0xffffffffu, incl, 31);
     // ---- decoupled look-back
-    unsigned long long prefix = 0;
-    if (t == 0) {
-      if (lane == 0) st_relaxed_u64(&P.tile_state[0], ((unsigned long long)T << 2) | 2ull);
-    } else {
-      if (lane == 0) st_relaxed_u64(&P.tile_state[t], ((unsigned long long)T << 2) | 1ull);
-      int64_t j = (int64_t)t - 1;
-      for (;;) {
-        const int64_t idx = j - lane;
-        unsigned long long v = 2ull;  // virtual "inclusive 0" before tile 0
-        if (idx >= 0) v = ld_relaxed_u64(&P.tile_state[idx]);
-        const unsigned m_incl = __ballot_sync(0xffffffffu, (v & 3ull) == 2ull);
-        const unsigned m_zero = __ballot_sync(0xffffffffu, (v & 3ull) == 0ull);
-        const int first_incl = m_incl ? (__ffs(m_incl) - 1) : 32;
-        const unsigned need = first_incl >= 32 ? 0xffffffffu : ((2u << first_incl) - 1u);
-        if (m_zero & need) continue;  // a needed predecessor has not published yet
-        unsigned long long part = (lane <= first_incl) ? (v >> 2) : 0ull;
-        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-        prefix += part;
-        if (first_incl < 32) break;
-        j -= 32;
-      }
-      if (lane == 0) st_relaxed_u64(&P.tile_state[t], ((prefix + T) << 2) | 2ull);
-    }
+    const unsigned long long prefix = tile_exclusive_prefix(P, t, T, lane);
     if ((int64_t)t == P.n_tiles - 1 && lane == 0) *P.total_hits = prefix + T;
 
     // ---- deliver
@@ -330,11 +337,6 @@ __global__ void finalize_doc_off_kernel(const int64_t* doc_off, int64_t n_docs, 
                                         const unsigned long long* total_hits, int64_t* doc_hit_off) {
   const int64_t d = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (d <= n_docs && doc_off[d] >= total) doc_hit_off[d] = (int64_t)*total_hits;
-}
-
-static int32_t build_hot_table(const aha_dfa*, DeviceDfa* dd) {
-  dd->hot = HotTable();
-  return AHA_OK;
 }
 
 }  // namespace aha

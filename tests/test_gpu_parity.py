@@ -13,10 +13,13 @@ from tests.test_oracle_kat import _rand_keys
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(autouse=True, params=["fused", "two-pass"])
+@pytest.fixture(autouse=True, params=["fused", "fused-byte", "two-pass"])
 def scan_impl(request, monkeypatch):
-    """every parity test runs against both device paths: the fused single-pass kernel and the two-pass baseline"""
-    monkeypatch.setenv("AHA_B200_IMPL", "1" if request.param == "fused" else "0")
+    """every parity test runs against all device paths: the fused single-pass kernel (character automaton in
+    shared memory where the dictionary allows), the fused kernel forced to the byte automaton, and the
+    two-pass baseline"""
+    monkeypatch.setenv("AHA_B200_IMPL", "0" if request.param == "two-pass" else "1")
+    monkeypatch.setenv("AHA_B200_NO_CHAR", "1" if request.param == "fused-byte" else "0")
     return request.param
 
 
@@ -205,3 +208,41 @@ def test_cedar_match_longest_random(seed):
             off = np.cumsum([0] + [len(w) for w in want])
             assert np.array_equal(res.doc_hit_off(), off)
             assert res.hits().tobytes() == np.concatenate(want).tobytes()
+
+
+ZH = "的一是在不了有和人这中大为上个国我以要他时来用们生到作地于出就分对成会可主发年动同工也能下过子说产种面而方后多定行学法所民得经"
+
+
+def _utf8_keys(rng, alpha, n, maxlen):
+    return list(dict.fromkeys("".join(rng.choice(alpha) for _ in range(rng.randint(1, maxlen))) for _ in range(n)))
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_char_automaton_paths(seed):
+    """UTF-8 dictionaries (eligible for the shared-memory character automaton): ragged / tiny / empty documents,
+    dense hits (event-slot overflow -> direct pass), malformed UTF-8 documents (byte-automaton fallback)."""
+    rng = random.Random(1000 + seed)
+    alpha = [ZH, "abcé日本語Я𝄞 ", "ab", ZH[:6] + "ab "][seed % 4]
+    keys = _utf8_keys(rng, alpha, rng.choice([30, 600, 4000]), rng.choice([2, 4, 6]))
+    docs = []
+    for _ in range(rng.choice([3, 40, 400])):
+        L = rng.choice([0, 1, 3, rng.randint(0, 50), rng.randint(0, 3000)])
+        docs.append("".join(rng.choice(alpha) for _ in range(L)).encode())
+    check_batch(keys, docs)
+    check_batch(keys, docs, aha_b200.UNITS_CHAR)
+    check_batch(keys, docs, sep=[" "])
+    # malformed UTF-8 sprinkled in (truncated units, stray continuation bytes, 0xFF): byte offsets only
+    bad = []
+    for d in docs[:50]:
+        b = bytearray(d)
+        for _ in range(rng.randint(0, 3)):
+            if b:
+                b[rng.randrange(len(b))] = rng.choice([0x80, 0xBF, 0xE4, 0xFF, 0xC3, 0x41])
+        bad.append(bytes(b))
+    check_batch(keys, bad)
+
+
+def test_char_automaton_dense_hits_and_many_tiny_docs():
+    keys = ["的", "的的", "的的的", "一", "的一", "一的"]
+    check_batch(keys, ["的" * 5000, "的一" * 3000, ("一的的" * 700)])
+    check_batch(keys, ["的一"] * 3000 + [""] * 50 + ["的"] * 500, aha_b200.UNITS_CHAR)

@@ -49,7 +49,7 @@ static void fused_geometry(uint32_t max_key_len, int32_t* chunk, int32_t* w16, i
   *chunk = 132;
   *w16 = (int32_t)((warm + 1 + 3 + 15) & ~15u);
   if (*w16 < 16) *w16 = 16;
-  *buf_bytes = (*w16 + 32 * *chunk + 16 + 127) & ~127;
+  *buf_bytes = (*w16 + 32 * *chunk + 16 + 32 + 127) & ~127;  // 16 staged bytes past the tile + read slack
 }
 
 static int32_t build_hot_table(const aha_dfa* d, DeviceDfa* dd) {
@@ -83,6 +83,7 @@ static int32_t build_hot_table(const aha_dfa* d, DeviceDfa* dd) {
   h.n_hot = T.n_states;
   h.n_root = T.n_root;
   h.m = T.m;
+  h.m_pad = (uint32_t)T.check.size();
   for (int c = 0; c < 3; ++c) { h.lo[c] = T.lo[c]; h.n[c] = T.n[c]; h.off[c] = T.off[c]; }
   h.smem_bytes = T.smem_bytes();
   return AHA_OK;
@@ -306,9 +307,9 @@ int32_t aha_b200_debug_char_scan(const uint8_t* blob, int64_t blob_bytes, const 
   for (int64_t a = 0; a < n && valid; a += chunk) {
     const int32_t b = (int32_t)std::min<int64_t>(a + chunk, n);
     const int32_t w = (int32_t)std::max<int64_t>(0, a - warmc);
-    const int st = char_walk(tv, text, w, (int32_t)a, b, b, (int32_t)n, w == 0, [&](uint32_t ref, uint32_t multi, int32_t last, uint32_t) {
+    const int st = char_walk(tv, text, w, (int32_t)a, b, b, (int32_t)n, w == 0, [&](uint32_t ref, int32_t last, uint32_t) {
       const RefRec rr = T.ref_rec[ref];
-      if ((rr.n > 1) != (multi != 0) || rr.n == 0) { valid = false; return; }
+      if (rr.n == 0) { valid = false; return; }
       if (rr.n == 1) {
         if (hits && cnt < cap) hits[cnt] = aha_hit{last + 1 - (int32_t)rr.b, last + 1, (int32_t)rr.a};
         ++cnt;

@@ -149,7 +149,9 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
   uint32_t* lead_counts = nullptr;
   uint64_t* tile_lead = nullptr;
   uint64_t* doc_lead = nullptr;
-  AHA_CUDA(cudaMallocAsync(&tile_state, (fp.n_tiles + 1) * sizeof(unsigned long long), st));
+  const int64_t n_groups = (fp.n_tiles + 31) / 32;
+  const size_t state_words = (size_t)(fp.n_tiles + 1) + 3 * (size_t)(n_groups + 1);
+  AHA_CUDA(cudaMallocAsync(&tile_state, state_words * sizeof(unsigned long long), st));
   AHA_CUDA(cudaMallocAsync(&counters, 16, st));
   // character automaton in shared memory when the dictionary allows it (plain match, with or without char units)
   const bool use_char = dd->hot.ok && !(p.mode & AHA_SEP);
@@ -164,16 +166,20 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
     cp.t.ref_rec = reinterpret_cast<const RefRec*>(h.dev + h.off_ref);
     cp.t.n_root = h.n_root;
     cp.t.m = h.m;
+    cp.t.m_pad = h.m_pad;
     for (int c = 0; c < 3; ++c) { cp.t.lo[c] = h.lo[c]; cp.t.n[c] = h.n[c]; cp.t.off[c] = h.off[c]; }
     cp.cmap_g = p.classmap;
-    AHA_CUDA(cudaMallocAsync(&cp.events, (size_t)n_warps * 32 * kEvCap * sizeof(CharEvent), st));
+    AHA_CUDA(cudaMallocAsync(&cp.events, (size_t)n_warps * 2 * 32 * kEvCap * sizeof(CharEvent), st));
   } else {
     AHA_CUDA(cudaMallocAsync(&fp.scratch, (size_t)n_warps * 32 * kLaneCap * sizeof(aha_hit), st));
   }
-  AHA_CUDA(cudaMallocAsync(&fp.marks, (size_t)n_warps * 32 * kMarkCap * sizeof(int2), st));
+  AHA_CUDA(cudaMallocAsync(&fp.marks, (size_t)n_warps * 2 * 32 * kMarkCap * sizeof(int2), st));
   AHA_CUDA(cudaMallocAsync(&own->dev_doc_hit_off, (p.n_docs + 1) * sizeof(int64_t), st));
   p.doc_hit_off = static_cast<int64_t*>(own->dev_doc_hit_off);
   fp.tile_state = tile_state;
+  fp.group_acc = tile_state + (fp.n_tiles + 1);
+  fp.group_agg = fp.group_acc + (n_groups + 1);
+  fp.group_excl = fp.group_agg + (n_groups + 1);
   fp.ticket = counters;
   fp.n_direct = counters + 1;
   fp.total_hits = reinterpret_cast<unsigned long long*>(counters + 2);
@@ -214,7 +220,7 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
     p.hits = counting ? nullptr : static_cast<aha_hit*>(own->dev_hits);
     fp.hit_cap = counting ? 0 : cap;
     fp.sp = p;
-    AHA_CUDA(cudaMemsetAsync(tile_state, 0, (fp.n_tiles + 1) * sizeof(unsigned long long), st));
+    AHA_CUDA(cudaMemsetAsync(tile_state, 0, state_words * sizeof(unsigned long long), st));
     AHA_CUDA(cudaMemsetAsync(counters, 0, 16, st));
     AHA_CUDA(cudaMemsetAsync(own->dev_doc_hit_off, 0, (p.n_docs + 1) * sizeof(int64_t), st));
     if (fp.n_tiles > 0) {

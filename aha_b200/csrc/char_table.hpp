@@ -7,9 +7,10 @@
 // can fire in the middle of a unit.  One transition then consumes 1-4 text bytes.
 //
 // Representation (all in shared memory, 6 bytes per edge slot):
-//   root[idx(char)]      -> cid:15 | fires:1 | id of the one-character state:15 | multi:1      (direct table)
+//   root[idx(char)]      -> cid:15 | fires:1 | id of the one-character state:15 | 0               (direct table)
 //   state id == base     -> edge slot = base + cid ; check[slot] == base means the goto edge exists
-//   val[slot]            -> next state id:15 | fires:1 | effective fail of next:15 | multi:1
+//   val[slot]            -> next state id:15 | fires:1 | effective fail of next:15 | deep:1
+//                           deep = the fail link of next has a non-root fail link itself (a third probe may be needed)
 // States without children are never "current": an edge into one stores the nearest fail-ancestor that
 // has children (its transitions are identical by the closure of the goto/fail loop) but still reports
 // the target's own output list (ref_rec[slot], global memory, read only when hits are written out).
@@ -43,12 +44,12 @@ struct CharTableHost {
   uint32_t n_root = 128;
   uint32_t m = 0;                  // slots
   std::vector<uint32_t> root;      // [n_root]
-  std::vector<uint16_t> check;     // [m]
+  std::vector<uint16_t> check;     // [m_pad = m + n_cid + 1 rounded up]: unused / padding = 0xFFFF, so base + cid never needs a bound test
   std::vector<uint32_t> val;       // [m]
   std::vector<RefRec> ref_rec;     // [m + n_cid + 1] what fires at edge slot / at the one-character state of cid (global)
   std::vector<uint16_t> gfail;     // [m] effective fail of the state whose id is the index (global)
   uint32_t n_cid = 0, n_edges = 0, n_states = 0;
-  size_t smem_bytes() const { return root.size() * 4 + (size_t)m * 6 + 256; }
+  size_t smem_bytes() const { return root.size() * 4 + (size_t)m * 4 + check.size() * 2 + 256; }
   uint32_t root_index(uint32_t code) const {
     const uint32_t cls = code >> 30;
     return cls ? off[cls - 1] + ((code & 0x3FFFFFFFu) - lo[cls - 1]) : code;
@@ -88,7 +89,9 @@ inline CharTableHost pack_rows(CharTableHost T, const DfaView& v, const std::vec
   T.ok = false;
   const size_t root_bytes = (size_t)T.n_root * 4;
   if (smem_budget < root_bytes + 256 + 64) { T.why = "shared memory budget too small"; return T; }
-  size_t m_max = (smem_budget - root_bytes - 256) / 6;
+  const size_t pad_bytes = ((size_t)T.n_cid + 1 + 16) * 2;  // check[] is padded by n_cid + 1 entries
+  if (smem_budget < root_bytes + 256 + pad_bytes + 64) { T.why = "shared memory budget too small"; return T; }
+  size_t m_max = (smem_budget - root_bytes - 256 - pad_bytes) / 6;
   if (m_max > 0x7FF0) m_max = 0x7FF0;
   std::vector<uint8_t> used(m_max + 1, 0), base_used(m_max + 1, 0);
   used[0] = 1;
@@ -121,7 +124,7 @@ inline CharTableHost pack_rows(CharTableHost T, const DfaView& v, const std::vec
     if (b + c_last > max_slot) max_slot = b + c_last;
   }
   T.m = (max_slot + 1 + 15) & ~15u;
-  T.check.assign(T.m, 0);
+  T.check.assign(((size_t)T.m + T.n_cid + 1 + 15) & ~size_t(15), 0xFFFFu);
   T.val.assign(T.m, 0);
   T.gfail.assign(T.m, 0);
   T.root.assign(T.n_root, 0);
@@ -141,9 +144,8 @@ inline CharTableHost pack_rows(CharTableHost T, const DfaView& v, const std::vec
     const uint32_t next_id = cont ? id_of[cont] : 0;
     const uint32_t n_out = v.out_off[e.to + 1] - v.out_off[e.to];
     const uint32_t flags = (n_out ? 0x8000u : 0u);
-    const uint32_t multi = (n_out > 1 ? 0x80000000u : 0u);
     if (e.from == 0) {
-      T.root[T.root_index(e.code)] = cid | flags | (next_id << 16) | multi;
+      T.root[T.root_index(e.code)] = cid | flags | (next_id << 16);
       if (n_out) T.ref_rec[(size_t)T.m + cid] = rec_of(e.to);
       continue;
     }
@@ -152,7 +154,8 @@ inline CharTableHost pack_rows(CharTableHost T, const DfaView& v, const std::vec
     const uint32_t cf = cont ? eff[v.fail[cont]] : 0;
     const uint32_t cont_fail = cf ? id_of[cf] : 0;
     T.check[slot] = (uint16_t)base;
-    T.val[slot] = next_id | flags | (cont_fail << 16) | multi;
+    const uint32_t deep = (cf && eff[v.fail[cf]]) ? 0x80000000u : 0u;
+    T.val[slot] = next_id | flags | (cont_fail << 16) | deep;
     if (n_out) T.ref_rec[slot] = rec_of(e.to);
   }
   // characters that never start a key still need their cid in the root table
@@ -259,8 +262,8 @@ inline CharTableHost build_char_table(const BlobHeader& h, const uint8_t* blob, 
   for (int c = 0; c < 3; ++c) {
     T.off[c] = T.n_root;
     if (lo[c] == 0xFFFFFFFFu) continue;
-    T.lo[c] = lo[c];
-    T.n[c] = hi[c] - lo[c] + 1;
+    T.lo[c] = lo[c] & ~63u;  // multiple of 64: the kernel folds it into the decode (scan_char.cuh)
+    T.n[c] = hi[c] - T.lo[c] + 1;
     if (T.n[c] > (1u << 20)) { T.why = "character range too wide for the root table"; return T; }
     T.n_root += T.n[c];
   }

@@ -25,8 +25,8 @@ enum CharWalkStatus { kWalkOk = 0, kWalkBadUtf8 = 1 };
 //   seg_end  min(b, end of the document): no unit may start at or beyond it
 //   doc_end  end of the document: a unit reaching past it is malformed
 //   at_doc_start  w is the first byte of the document (otherwise leading continuation bytes are skipped)
-// emit(ref, multi, last, k): ref = firing edge slot, or m + cid for a one-character state; multi = the
-// output list has more than one key; k = number of units that START in [a, last] (character offsets).
+// emit(ref, last, k): ref = firing edge slot, or m + cid for a one-character state;
+// k = number of units that START in [a, last] (character offsets).
 // Returns kWalkBadUtf8 when the text is not
 // structurally valid UTF-8 inside the walked range (the caller then rescans with the byte automaton).
 template <class Emit>
@@ -86,7 +86,7 @@ AHA_HD int char_walk(const CharTablesView& T, const uint8_t* buf, int32_t w, int
     bool first = true;
     for (;;) {
       if (t == 0) {  // the root: direct table entry of this character
-        if ((r & 0x8000u) && last >= a) emit(T.m + cid, r >> 31, last, k);
+        if ((r & 0x8000u) && last >= a) emit(T.m + cid, last, k);
         s = (r >> 16) & 0x7FFFu;
         f1 = 0;
         break;
@@ -94,7 +94,7 @@ AHA_HD int char_walk(const CharTablesView& T, const uint8_t* buf, int32_t w, int
       const uint32_t slot = t + cid;
       if (slot < T.m && T.check[slot] == t) {
         const uint32_t v = T.val[slot];
-        if ((v & 0x8000u) && last >= a) emit(slot, v >> 31, last, k);
+        if ((v & 0x8000u) && last >= a) emit(slot, last, k);
         s = v & 0x7FFFu;
         f1 = (v >> 16) & 0x7FFFu;
         break;

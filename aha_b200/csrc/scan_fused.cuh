@@ -32,7 +32,11 @@ struct FusedParams {
   int32_t w16;           // staged bytes in front of the tile (multiple of 16, > warm)
   int32_t buf_bytes;     // per-warp text buffer = w16 + tile + 16
   int64_t n_tiles;
-  unsigned long long* tile_state;  // [n_tiles] (value << 2) | flag ; flag 1 = aggregate, 2 = inclusive prefix
+  unsigned long long* tile_state;  // [n_tiles] (hits of the tile << 2) | 1 once the tile has been walked
+  // groups of 32 consecutive tiles (two-level look-back: 32 tiles, then 32 groups = 1024 tiles per step)
+  unsigned long long* group_acc;   // [n_groups] (tiles arrived << 40) | hits so far   (atomicAdd)
+  unsigned long long* group_agg;   // [n_groups] (hits of the group << 2) | 1, written by the last tile to arrive
+  unsigned long long* group_excl;  // [n_groups] (hits before the group << 2) | 2, written by every tile that resolves
   unsigned int* ticket;
   unsigned long long* total_hits;  // out: total number of hits
   int64_t hit_cap;                 // capacity of sp.hits (records); writes beyond are dropped
@@ -183,33 +187,67 @@ __device__ __forceinline__ uint32_t count_leads_smem(const uint8_t* sbuf, int64_
   return c;
 }
 
-// Decoupled look-back over tile_state[]: publishes this tile's aggregate T, returns the number of hits in
-// all earlier tiles, then publishes the inclusive prefix.  Whole warp participates.
-__device__ __forceinline__ unsigned long long tile_exclusive_prefix(const FusedParams& P, unsigned int t, uint32_t T, int lane) {
-  unsigned long long prefix = 0;
-  if (t == 0) {
-    if (lane == 0) st_relaxed_u64(&P.tile_state[0], ((unsigned long long)T << 2) | 2ull);
-    return 0;
+// ---- two-level decoupled look-back -------------------------------------------------------------------
+// A tile needs the number of hits in all earlier tiles.  Tickets are handed out in order, so every earlier
+// tile is already running on some warp and publishes its count without waiting for anybody.
+// publish_aggregate: called once per tile right after its walk (never blocks).
+__device__ __forceinline__ void publish_aggregate(const FusedParams& P, unsigned int t, uint32_t T, int lane) {
+  if (lane != 0) return;
+  st_relaxed_u64(&P.tile_state[t], ((unsigned long long)T << 2) | 1ull);
+  const unsigned int g = t >> 5;
+  const long long left = P.n_tiles - ((long long)g << 5);
+  const unsigned long long size = left < 32 ? (unsigned long long)left : 32ull;
+  const unsigned long long old = atomicAdd(&P.group_acc[g], (1ull << 40) + (unsigned long long)T);
+  if ((old >> 40) + 1ull == size) {
+    const unsigned long long total = (old & ((1ull << 40) - 1ull)) + (unsigned long long)T;
+    st_relaxed_u64(&P.group_agg[g], (total << 2) | 1ull);
   }
-  if (lane == 0) st_relaxed_u64(&P.tile_state[t], ((unsigned long long)T << 2) | 1ull);
-  int64_t j = (int64_t)t - 1;
+}
+// resolve_prefix: hits in all tiles before t.  Whole warp; waits (with back-off) for earlier tiles that have
+// not finished their walk yet.  The caller normally defers this call by one tile so that it never waits.
+__device__ __forceinline__ unsigned long long resolve_prefix(const FusedParams& P, unsigned int t, int lane) {
+  const unsigned int g = t >> 5, j = t & 31u;
+  // (1) tiles of the same group in front of t
+  unsigned long long v = 1ull;
   for (;;) {
-    const int64_t idx = j - lane;
-    unsigned long long v = 2ull;  // virtual "inclusive 0" before tile 0
-    if (idx >= 0) v = ld_relaxed_u64(&P.tile_state[idx]);
-    const unsigned m_incl = __ballot_sync(0xffffffffu, (v & 3ull) == 2ull);
-    const unsigned m_zero = __ballot_sync(0xffffffffu, (v & 3ull) == 0ull);
-    const int first_incl = m_incl ? (__ffs(m_incl) - 1) : 32;
-    const unsigned need = first_incl >= 31 ? 0xffffffffu : ((2u << first_incl) - 1u);
-    if (m_zero & need) continue;  // a needed predecessor has not published yet
-    unsigned long long part = (lane <= first_incl) ? (v >> 2) : 0ull;
-    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-    prefix += part;
-    if (first_incl < 32) break;
-    j -= 32;
+    if ((unsigned)lane < j) v = ld_relaxed_u64(&P.tile_state[((size_t)g << 5) + lane]);
+    if (__all_sync(0xffffffffu, (v & 3ull) != 0ull)) break;
+    __nanosleep(100);
   }
-  if (lane == 0) st_relaxed_u64(&P.tile_state[t], ((prefix + T) << 2) | 2ull);
-  return prefix;
+  unsigned long long in_group = (unsigned)lane < j ? (v >> 2) : 0ull;
+  for (int o = 16; o > 0; o >>= 1) in_group += __shfl_xor_sync(0xffffffffu, in_group, o);
+  // (2) groups in front of g, 32 per step, stopping at the first one whose exclusive prefix is known
+  unsigned long long G = 0;
+  long long h = (long long)g - 1;
+  while (h >= 0) {
+    const long long idx = h - lane;
+    unsigned long long e = 2ull, a = 1ull;  // virtual group before group 0: prefix 0, 0 hits
+    if (idx >= 0) {
+      e = ld_relaxed_u64(&P.group_excl[idx]);
+      a = ld_relaxed_u64(&P.group_agg[idx]);
+    }
+    const bool have_a = (a & 3ull) == 1ull;
+    const unsigned m_incl = __ballot_sync(0xffffffffu, have_a && (e & 3ull) == 2ull);
+    const unsigned m_wait = __ballot_sync(0xffffffffu, !have_a);
+    const int first = m_incl ? (__ffs(m_incl) - 1) : 32;
+    const unsigned need = first >= 31 ? 0xffffffffu : ((2u << first) - 1u);
+    if (m_wait & need) {
+      __nanosleep(100);
+      continue;
+    }
+    unsigned long long part = lane < first ? (a >> 2) : (lane == first ? (a >> 2) + (e >> 2) : 0ull);
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+    G += part;
+    if (first < 32) break;
+    h -= 32;
+  }
+  if (lane == 0) st_relaxed_u64(&P.group_excl[g], (G << 2) | 2ull);
+  return G + in_group;
+}
+// walk-then-resolve in one go (kernels that do not defer)
+__device__ __forceinline__ unsigned long long tile_exclusive_prefix(const FusedParams& P, unsigned int t, uint32_t T, int lane) {
+  publish_aggregate(P, t, T, lane);
+  return resolve_prefix(P, t, lane);
 }
 
 template <class Policy>

@@ -71,12 +71,14 @@ static int32_t build_hot_table(const aha_dfa* d, DeviceDfa* dd) {
   h.off_check = place(cursor, T.check.size() * 2);
   h.off_gfail = place(cursor, T.gfail.size() * 2);
   h.off_ref = place(cursor, T.ref_rec.size() * sizeof(RefRec));
+  h.off_mbits = place(cursor, T.multi_bits.size() * 4);
   std::vector<uint8_t> stage(cursor, 0);
   memcpy(stage.data() + h.off_root, T.root.data(), T.root.size() * 4);
   memcpy(stage.data() + h.off_val, T.val.data(), T.val.size() * 4);
   memcpy(stage.data() + h.off_check, T.check.data(), T.check.size() * 2);
   memcpy(stage.data() + h.off_gfail, T.gfail.data(), T.gfail.size() * 2);
   memcpy(stage.data() + h.off_ref, T.ref_rec.data(), T.ref_rec.size() * sizeof(RefRec));
+  memcpy(stage.data() + h.off_mbits, T.multi_bits.data(), T.multi_bits.size() * 4);
   AHA_CUDA(cudaMalloc(&h.dev, cursor));
   AHA_CUDA(cudaMemcpy(h.dev, stage.data(), cursor, cudaMemcpyHostToDevice));
   h.ok = true;
@@ -84,6 +86,7 @@ static int32_t build_hot_table(const aha_dfa* d, DeviceDfa* dd) {
   h.n_root = T.n_root;
   h.m = T.m;
   h.m_pad = (uint32_t)T.check.size();
+  h.n_mwords = (uint32_t)T.multi_bits.size();
   for (int c = 0; c < 3; ++c) { h.lo[c] = T.lo[c]; h.n[c] = T.n[c]; h.off[c] = T.off[c]; }
   h.smem_bytes = T.smem_bytes();
   return AHA_OK;

@@ -167,6 +167,8 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
     cp.t.n_root = h.n_root;
     cp.t.m = h.m;
     cp.t.m_pad = h.m_pad;
+    cp.t.n_mwords = h.n_mwords;
+    cp.t.mbits_g = reinterpret_cast<const uint32_t*>(h.dev + h.off_mbits);
     for (int c = 0; c < 3; ++c) { cp.t.lo[c] = h.lo[c]; cp.t.n[c] = h.n[c]; cp.t.off[c] = h.off[c]; }
     cp.cmap_g = p.classmap;
     AHA_CUDA(cudaMallocAsync(&cp.events, (size_t)n_warps * 2 * 32 * kEvCap * sizeof(CharEvent), st));

@@ -31,6 +31,8 @@ struct CharDeviceTables {
   const RefRec* ref_rec;    // stays in global memory
   uint32_t n_root, m;
   uint32_t m_pad;           // entries of check[] (m + n_cid + 1, padding = 0xFFFF)
+  uint32_t n_mwords;        // words of the multi bitmap
+  const uint32_t* mbits_g;  // bit ref: more than one key fires there
   uint32_t lo[3], n[3], off[3];
 };
 
@@ -115,6 +117,7 @@ struct CharSmem {
   const uint32_t* val;     // [m]
   const uint16_t* check;   // [m_pad]
   const uint16_t* gfail;   // global
+  const uint32_t* mbits;   // [n_mwords] bit ref: ref_rec[ref].n > 1
   uint32_t m;
   uint32_t lo2, n2, off2, lo3, n3, off3, lo4, n4, off4;  // root index ranges of 2-, 3-, 4-byte units
   uint32_t neg_lo3_64;     // -(lo3 / 64): lo is a multiple of 64 (char_table.hpp)
@@ -167,7 +170,7 @@ template <bool kChars, class OnDoc>
 __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanParams& p, const uint8_t* sbuf, int64_t origin, int64_t a,
                                                int64_t b, int32_t stage_end, int32_t warmc, bool one_doc, int64_t cd,
                                                int64_t cdoc_start, int64_t cdoc_end, uint32_t lead0, CharEvent* my_ev,
-                                               uint32_t& n_ev_out, OnDoc on_doc) {
+                                               uint32_t& n_ev_out, uint32_t& multi_mask_out, OnDoc on_doc) {
   constexpr unsigned kFull = 0xffffffffu;
   const int32_t rb = (int32_t)(b - origin);
   bool done = a >= b, ok = true;
@@ -177,7 +180,7 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
     doc_start = p.doc_off[d];
     doc_end = p.doc_off[d + 1];
   }
-  uint32_t n_ev = 0;
+  uint32_t n_ev = 0, multi_mask = 0;  // bit i: event i of this lane reports more than one key
   if (!done && doc_start == a) {
     for (int64_t e = first_ge(p.doc_off, p.n_docs, a); e <= d; ++e) on_doc(e, n_ev);
   }
@@ -214,7 +217,10 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
     if (kChars) k += (cs >= a_seg) ? 1u : 0u;
     const bool fire = (v & 0x8000u) && (uint32_t)(last - a_seg) < (uint32_t)(rb - a_seg);
     if (fire) {
-      if (n_ev < (uint32_t)kEvCap) my_ev[n_ev] = CharEvent{kChars ? (int32_t)(lead + k) : last + ebase, ref};
+      if (n_ev < (uint32_t)kEvCap) {
+        my_ev[n_ev] = CharEvent{kChars ? (int32_t)(lead + k) : last + ebase, ref};
+        multi_mask |= ((S.mbits[ref >> 5] >> (ref & 31u)) & 1u) << n_ev;
+      }
       ++n_ev;
     }
   };
@@ -318,6 +324,7 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
     }
   }
   n_ev_out = n_ev;
+  multi_mask_out = multi_mask;
   return true;
 }
 
@@ -325,14 +332,16 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
 // Document-start markers, then cooperative expansion of the warp's events (lane, sequence order = output
 // order) into final Aha::Hit records: one event per lane per round, output tables read event-parallel.
 __device__ __forceinline__ void deliver_events(const CharParams& P, unsigned long long prefix, uint32_t excl_lane, uint32_t n_ev,
-                                               uint32_t n_mark, const CharEvent* warp_ev, const int2* my_mark, int lane) {
+                                               uint32_t n_mark, uint32_t multi_mask, const CharEvent* warp_ev, const int2* my_mark,
+                                               int lane) {
   const ScanParams& p = P.f.sp;
   const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
   const CharEvent* my_ev = warp_ev + lane * kEvCap;
   for (uint32_t k = 0; k < n_mark; ++k) {
     const int y = my_mark[k].y;  // events of this lane before the document start
-    uint32_t before = 0;
-    for (int i = 0; i < y; ++i) before += P.t.ref_rec[my_ev[i].ref].n;
+    uint32_t before = (uint32_t)y;
+    for (uint32_t mm = multi_mask & (y >= 32 ? 0xffffffffu : ((1u << y) - 1u)); mm; mm &= mm - 1)
+      before += P.t.ref_rec[my_ev[__ffs(mm) - 1].ref].n - 1u;
     p.doc_hit_off[my_mark[k].x] = (int64_t)(prefix + excl_lane + before);
   }
   uint32_t ev_incl = n_ev;
@@ -375,16 +384,18 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
   const FusedParams& F = P.f;
   const ScanParams& p = F.sp;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // shared layout: root u32[n_root] | val u32[m] | check u16[m_pad] | cmap u8[256] | per-warp {mbarrier, text}
+  // shared layout: root u32[n_root] | val u32[m] | multi bits u32[n_mwords] | check u16[m_pad] | cmap u8[256] | per-warp {mbarrier, text}
   uint32_t* s_root = reinterpret_cast<uint32_t*>(smem);
   uint32_t* s_val = s_root + P.t.n_root;
-  uint16_t* s_check = reinterpret_cast<uint16_t*>(s_val + P.t.m);
+  uint32_t* s_mbits = s_val + P.t.m;
+  uint16_t* s_check = reinterpret_cast<uint16_t*>(s_mbits + P.t.n_mwords);
+  for (uint32_t i = threadIdx.x; i < P.t.n_mwords; i += blockDim.x) s_mbits[i] = P.t.mbits_g[i];
   uint8_t* s_cmap = reinterpret_cast<uint8_t*>(s_check + P.t.m_pad);
   for (uint32_t i = threadIdx.x; i < P.t.n_root; i += blockDim.x) s_root[i] = P.t.root_g[i];
   for (uint32_t i = threadIdx.x; i < P.t.m; i += blockDim.x) s_val[i] = P.t.val_g[i];
   for (uint32_t i = threadIdx.x; i < P.t.m_pad; i += blockDim.x) s_check[i] = P.t.check_g[i];
   for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) s_cmap[i] = P.cmap_g[i];
-  const uint32_t table_bytes = P.t.n_root * 4 + P.t.m * 4 + P.t.m_pad * 2 + 256;
+  const uint32_t table_bytes = P.t.n_root * 4 + P.t.m * 4 + P.t.n_mwords * 4 + P.t.m_pad * 2 + 256;
   uint8_t* wbase = smem + ((table_bytes + 127) & ~127u) + (size_t)warp * (size_t)(F.buf_bytes + 128);
   uint64_t* bar = reinterpret_cast<uint64_t*>(wbase);
   uint8_t* sbuf = wbase + 128;
@@ -397,7 +408,7 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
 #pragma unroll
   for (int c = 0; c < 3; ++c) { T.lo[c] = P.t.lo[c]; T.n[c] = P.t.n[c]; T.off[c] = P.t.off[c]; }
   CharSmem S;        // fast walk
-  S.root = s_root; S.root3 = s_root + P.t.off[1]; S.val = s_val; S.check = s_check; S.gfail = P.t.gfail;
+  S.root = s_root; S.root3 = s_root + P.t.off[1]; S.val = s_val; S.check = s_check; S.gfail = P.t.gfail; S.mbits = s_mbits;
   S.m = P.t.m;
   S.lo2 = P.t.lo[0]; S.n2 = P.t.n[0]; S.off2 = P.t.off[0];
   S.lo3 = P.t.lo[1]; S.n3 = P.t.n[1]; S.off3 = P.t.off[1];
@@ -415,7 +426,7 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
   // the tile walked in the previous round, delivered after the next walk so that its look-back never waits
   bool pend = false;
   unsigned int pend_t = 0;
-  uint32_t pend_excl = 0, pend_T = 0, pend_n_ev = 0, pend_n_mark = 0;
+  uint32_t pend_excl = 0, pend_T = 0, pend_n_ev = 0, pend_n_mark = 0, pend_multi = 0;
   int pend_buf = 0;
   // document that contained the previous tile (tiles come in increasing order)
   int64_t cd = 0, cdoc_start = 0, cdoc_end = -1;
@@ -426,7 +437,7 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
     t = __shfl_sync(0xffffffffu, t, 0);
     const bool have = (int64_t)t < F.n_tiles;
     bool bad = false, over = false;
-    uint32_t n_ev = 0, n_mark = 0, excl_lane = 0, Ttile = 0, lead0 = 0;
+    uint32_t n_ev = 0, n_mark = 0, multi_mask = 0, excl_lane = 0, Ttile = 0, lead0 = 0;
     int64_t origin = 0, a = 0, b = 0;
     CharEvent* warp_ev = P.events + ((gwarp * 2 + buf) * 32) * kEvCap;
     CharEvent* my_ev = warp_ev + lane * kEvCap;
@@ -480,9 +491,9 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
       };
       const int32_t stage_end = (int32_t)(want_end - origin);
       const bool ok = chars ? char_tile_walk<true>(S, p, sbuf, origin, a, b, stage_end, warmc, fast, cd, cdoc_start, cdoc_end, lead0, my_ev,
-                                                   n_ev, on_doc)
+                                                   n_ev, multi_mask, on_doc)
                             : char_tile_walk<false>(S, p, sbuf, origin, a, b, stage_end, warmc, fast, cd, cdoc_start, cdoc_end, lead0, my_ev,
-                                                    n_ev, on_doc);
+                                                    n_ev, multi_mask, on_doc);
       bad = __any_sync(0xffffffffu, !ok);
       over = __any_sync(0xffffffffu, n_ev > (uint32_t)kEvCap || n_mark > (uint32_t)kMarkCap);
       __syncwarp();
@@ -499,8 +510,8 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
                        [&](int64_t) {});
         n_hits = c;
       } else {
-        n_hits = 0;
-        for (uint32_t i = 0; i < n_ev; ++i) n_hits += P.t.ref_rec[my_ev[i].ref].n;
+        n_hits = n_ev;
+        for (uint32_t mm = multi_mask; mm; mm &= mm - 1) n_hits += P.t.ref_rec[my_ev[__ffs(mm) - 1].ref].n - 1u;
       }
       uint32_t incl = n_hits;
       for (int o = 1; o < 32; o <<= 1) {
@@ -518,7 +529,7 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
       if ((int64_t)pend_t == F.n_tiles - 1 && lane == 0) *F.total_hits = prefix + pend_T;
       const CharEvent* pev = P.events + ((gwarp * 2 + pend_buf) * 32) * kEvCap;
       const int2* pmark = F.marks + ((gwarp * 2 + pend_buf) * 32 + lane) * kMarkCap;
-      deliver_events(P, prefix, pend_excl, pend_n_ev, pend_n_mark, pev, pmark, lane);
+      deliver_events(P, prefix, pend_excl, pend_n_ev, pend_n_mark, pend_multi, pev, pmark, lane);
       pend = false;
     }
     if (!have) break;
@@ -545,7 +556,7 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
       }
     } else {
       pend = true;
-      pend_t = t; pend_excl = excl_lane; pend_T = Ttile; pend_n_ev = n_ev; pend_n_mark = n_mark;
+      pend_t = t; pend_excl = excl_lane; pend_T = Ttile; pend_n_ev = n_ev; pend_n_mark = n_mark; pend_multi = multi_mask;
       pend_buf = buf;
       buf ^= 1;
     }

@@ -205,18 +205,24 @@ __device__ __forceinline__ void publish_aggregate(const FusedParams& P, unsigned
 }
 // resolve_prefix: hits in all tiles before t.  Whole warp; waits (with back-off) for earlier tiles that have
 // not finished their walk yet.  The caller normally defers this call by one tile so that it never waits.
+// Only the first tile of a group looks back over the group arrays (all warps polling the same few lines
+// serialises in L2); the other 31 tiles read the group's exclusive prefix it publishes.
 __device__ __forceinline__ unsigned long long resolve_prefix(const FusedParams& P, unsigned int t, int lane) {
   const unsigned int g = t >> 5, j = t & 31u;
-  // (1) tiles of the same group in front of t
-  unsigned long long v = 1ull;
-  for (;;) {
-    if ((unsigned)lane < j) v = ld_relaxed_u64(&P.tile_state[((size_t)g << 5) + lane]);
-    if (__all_sync(0xffffffffu, (v & 3ull) != 0ull)) break;
-    __nanosleep(100);
+  if (j != 0) {
+    // tiles of the same group in front of t (lanes < j) and the group's exclusive prefix (lane 31)
+    unsigned long long v = 1ull;
+    for (;;) {
+      if ((unsigned)lane < j) v = ld_relaxed_u64(&P.tile_state[((size_t)g << 5) + lane]);
+      else if (lane == 31) v = ld_relaxed_u64(&P.group_excl[g]);
+      if (__all_sync(0xffffffffu, (v & 3ull) != 0ull)) break;
+      __nanosleep(64);
+    }
+    unsigned long long sum = ((unsigned)lane < j || lane == 31) ? (v >> 2) : 0ull;
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    return sum;
   }
-  unsigned long long in_group = (unsigned)lane < j ? (v >> 2) : 0ull;
-  for (int o = 16; o > 0; o >>= 1) in_group += __shfl_xor_sync(0xffffffffu, in_group, o);
-  // (2) groups in front of g, 32 per step, stopping at the first one whose exclusive prefix is known
+  // first tile of group g: groups in front of g, 32 per step, stopping at the first one whose exclusive prefix is known
   unsigned long long G = 0;
   long long h = (long long)g - 1;
   while (h >= 0) {
@@ -232,7 +238,7 @@ __device__ __forceinline__ unsigned long long resolve_prefix(const FusedParams& 
     const int first = m_incl ? (__ffs(m_incl) - 1) : 32;
     const unsigned need = first >= 31 ? 0xffffffffu : ((2u << first) - 1u);
     if (m_wait & need) {
-      __nanosleep(100);
+      __nanosleep(64);
       continue;
     }
     unsigned long long part = lane < first ? (a >> 2) : (lane == first ? (a >> 2) + (e >> 2) : 0ull);
@@ -242,7 +248,7 @@ __device__ __forceinline__ unsigned long long resolve_prefix(const FusedParams& 
     h -= 32;
   }
   if (lane == 0) st_relaxed_u64(&P.group_excl[g], (G << 2) | 2ull);
-  return G + in_group;
+  return G;
 }
 // walk-then-resolve in one go (kernels that do not defer)
 __device__ __forceinline__ unsigned long long tile_exclusive_prefix(const FusedParams& P, unsigned int t, uint32_t T, int lane) {

@@ -171,7 +171,7 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
     cp.t.mbits_g = reinterpret_cast<const uint32_t*>(h.dev + h.off_mbits);
     for (int c = 0; c < 3; ++c) { cp.t.lo[c] = h.lo[c]; cp.t.n[c] = h.n[c]; cp.t.off[c] = h.off[c]; }
     cp.cmap_g = p.classmap;
-    AHA_CUDA(cudaMallocAsync(&cp.events, (size_t)n_warps * 2 * 32 * kEvCap * sizeof(CharEvent), st));
+    AHA_CUDA(cudaMallocAsync(&cp.events, (size_t)n_warps * 2 * 32 * kEvSlots * sizeof(CharEvent), st));
   } else {
     AHA_CUDA(cudaMallocAsync(&fp.scratch, (size_t)n_warps * 32 * kLaneCap * sizeof(aha_hit), st));
   }

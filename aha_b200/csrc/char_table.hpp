@@ -7,7 +7,7 @@
 // can fire in the middle of a unit.  One transition then consumes 1-4 text bytes.
 //
 // Representation (all in shared memory, 6 bytes per edge slot):
-//   root[idx(char)]      -> cid:15 | fires:1 | id of the one-character state:15 | 0               (direct table)
+//   root[idx(char)]      -> id of the one-character state:15 | fires:1 | cid:15 | 0               (direct table)
 //   state id == base     -> edge slot = base + cid ; check[slot] == base means the goto edge exists
 //   val[slot]            -> next state id:15 | fires:1 | effective fail of next:15 | deep:1
 //                           deep = the fail link of next has a non-root fail link itself (a third probe may be needed)
@@ -40,8 +40,8 @@ struct CharTableHost {
   std::string why;                 // reason when !ok
   // multi-byte root index, one contiguous range per unit length L = 2, 3, 4:
   //   idx = off[L-2] + (payload - lo[L-2]) when payload - lo < n ; ASCII: idx = byte
-  uint32_t lo[3] = {0, 0, 0}, n[3] = {0, 0, 0}, off[3] = {128, 128, 128};
-  uint32_t n_root = 128;
+  uint32_t lo[3] = {0, 0, 0}, n[3] = {0, 0, 0}, off[3] = {256, 256, 256};  // entries 128..255 stay 0: idle lanes of the ASCII step may index them
+  uint32_t n_root = 256;
   uint32_t m = 0;                  // slots
   std::vector<uint32_t> root;      // [n_root]
   std::vector<uint16_t> check;     // [m_pad = m + n_cid + 1 rounded up]: unused / padding = 0xFFFF, so base + cid never needs a bound test
@@ -147,7 +147,7 @@ inline CharTableHost pack_rows(CharTableHost T, const DfaView& v, const std::vec
     const uint32_t n_out = v.out_off[e.to + 1] - v.out_off[e.to];
     const uint32_t flags = (n_out ? 0x8000u : 0u);
     if (e.from == 0) {
-      T.root[T.root_index(e.code)] = cid | flags | (next_id << 16);
+      T.root[T.root_index(e.code)] = next_id | flags | (cid << 16);
       if (n_out) T.ref_rec[(size_t)T.m + cid] = rec_of(e.to);
       continue;
     }
@@ -163,7 +163,7 @@ inline CharTableHost pack_rows(CharTableHost T, const DfaView& v, const std::vec
   // characters that never start a key still need their cid in the root table
   for (const auto& kv : cid_of) {
     const uint32_t idx = T.root_index(kv.first);
-    if (T.root[idx] == 0) T.root[idx] = kv.second;
+    if (T.root[idx] == 0) T.root[idx] = kv.second << 16;
   }
   for (const CharRow& r : rows) {
     const uint32_t f = eff[v.fail[r.st]];
@@ -263,7 +263,7 @@ inline CharTableHost build_char_table(const BlobHeader& h, const uint8_t* blob, 
   for (auto& kv : cid_of) kv.second = ++n_cid;
   if (n_cid >= 0x7FFF) { T.why = "more than 32766 distinct characters"; return T; }
   T.n_cid = n_cid;
-  T.n_root = 128;
+  T.n_root = 256;
   for (int c = 0; c < 3; ++c) {
     T.off[c] = T.n_root;
     if (lo[c] == 0xFFFFFFFFu) continue;

@@ -77,7 +77,7 @@ AHA_HD int char_walk(const CharTablesView& T, const uint8_t* buf, int32_t w, int
     if (cs >= a) ++k;
     cs += len;
     const uint32_t r = idx == 0xFFFFFFFFu ? 0u : T.root[idx];
-    const uint32_t cid = r & 0x7FFFu;
+    const uint32_t cid = r >> 16;
     if (cid == 0) {  // character not in the dictionary: every suffix dies, back to the root
       s = 0;
       continue;
@@ -87,7 +87,7 @@ AHA_HD int char_walk(const CharTablesView& T, const uint8_t* buf, int32_t w, int
     for (;;) {
       if (t == 0) {  // the root: direct table entry of this character
         if ((r & 0x8000u) && last >= a) emit(T.m + cid, last, k);
-        s = (r >> 16) & 0x7FFFu;
+        s = r & 0x7FFFu;
         f1 = 0;
         break;
       }

@@ -16,7 +16,8 @@
 
 namespace aha {
 
-constexpr int kEvCap = 32;  // events per lane per tile kept in the scratch ring
+constexpr int kEvCap = 32;     // events per lane per tile the deferred delivery can handle (more: direct pass)
+constexpr int kEvSlots = 144;  // ring slots per lane: one per byte of the lane's chunk, so the walk never checks a bound
 
 struct alignas(8) CharEvent {
   int32_t end;   // document-relative end offset (bytes, or characters with AHA_UNITS_CHAR)
@@ -39,7 +40,7 @@ struct CharDeviceTables {
 struct CharParams {
   FusedParams f;            // f.scratch is unused here
   CharDeviceTables t;
-  CharEvent* events;        // [n_warps_total][2][32][kEvCap]  (two tiles in flight per warp)
+  CharEvent* events;        // [n_warps_total][2][32][kEvSlots]  (two tiles in flight per warp)
   const uint8_t* cmap_g;    // byte class map for the fallback walk
 };
 
@@ -111,13 +112,33 @@ __device__ __forceinline__ void expand_event(const ScanParams& p, const RefRec& 
 
 // ---- fast tile walk -----------------------------------------------------------------------------------
 // Tables as seen by one warp (all in shared memory except gfail).
+// 32-bit shared-window addresses: plain pointers make the compiler rebuild the generic->shared base (S2R of the
+// CTA id in the cluster + LEA) in front of every predicated table load.
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+  uint32_t v;
+  asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_u16(uint32_t addr) {
+  uint16_t v;
+  asm("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
+  return v;
+}
+struct SmemU32 {
+  uint32_t base;
+  __device__ __forceinline__ uint32_t operator[](uint32_t i) const { return lds_u32(base + i * 4u); }
+};
+struct SmemU16 {
+  uint32_t base;
+  __device__ __forceinline__ uint32_t operator[](uint32_t i) const { return lds_u16(base + i * 2u); }
+};
 struct CharSmem {
-  const uint32_t* root;    // [n_root]
-  const uint32_t* root3;   // root + off[1]: entries of the 3-byte units
-  const uint32_t* val;     // [m]
-  const uint16_t* check;   // [m_pad]
+  SmemU32 root;            // [n_root]
+  SmemU32 root3;           // root + off[1]: entries of the 3-byte units
+  SmemU32 val;             // [m]
+  SmemU16 check;           // [m_pad]
   const uint16_t* gfail;   // global
-  const uint32_t* mbits;   // [n_mwords] bit ref: ref_rec[ref].n > 1
+  SmemU32 mbits;           // [n_mwords] bit ref: ref_rec[ref].n > 1
   uint32_t m;
   uint32_t lo2, n2, off2, lo3, n3, off3, lo4, n4, off4;  // root index ranges of 2-, 3-, 4-byte units
   uint32_t neg_lo3_64;     // -(lo3 / 64): lo is a multiple of 64 (char_table.hpp)
@@ -130,13 +151,13 @@ struct CharSmem {
 // missed as well", which walks gfail[] in global memory; kVote = the whole warp is converged here.
 template <bool kVote>
 __device__ __forceinline__ uint32_t char_advance(const CharSmem& S, uint32_t r, uint32_t s, uint32_t f1, bool deep, uint32_t& ref) {
-  const uint32_t cid = r & 0x7FFFu;
+  const uint32_t cid = r >> 16;
   const uint32_t slot1 = s + cid, slot2 = f1 + cid;
   const uint32_t c1 = S.check[slot1], c2 = S.check[slot2];
   const bool hit1 = c1 == s, hit2 = c2 == f1;
   bool hit = hit1 || hit2;
   uint32_t slotv = hit1 ? slot1 : slot2;
-  uint32_t v = ((r >> 16) & 0x7FFFu) | (r & 0x8000u);  // the root entry in val[] format (fail = 0)
+  uint32_t v = r & 0xFFFFu;  // the root entry in val[] format (fail = 0)
   if (hit) v = S.val[slotv];
   const bool rare = !hit && deep && cid != 0;
   if (kVote ? __any_sync(0xffffffffu, rare) : rare) {
@@ -158,192 +179,334 @@ __device__ __forceinline__ uint32_t char_advance(const CharSmem& S, uint32_t r, 
   return v;
 }
 
-// Walks one tile.  Every lane owns [a, b) of the concatenated text and runs the same per-document segment
-// logic as char_lane_walk() (warm-up, owned region, document boundaries with markers), but as a state machine
-// driven by a warp-uniform loop, so that whenever every busy lane has 12 well-formed bytes of one kind in
-// front of it (four 3-byte units, or twelve ASCII characters) the warp takes a branch-free unrolled step.
-// Lanes near a boundary (region end, document end, mixed unit lengths) make the warp fall back to one
-// unit per iteration.  one_doc: the whole tile lies in document cd = [cdoc_start, cdoc_end).
-// Events of the lane go to my_ev[0 .. kEvCap); n_ev counts all of them.  Returns false (warp-uniform) when
-// the text is not structurally valid UTF-8: the caller rescans the tile with the byte automaton.
+// The same transition split in two for the interleaved walk: char_probe() is straight-line code (so that the
+// probes of several sub-chunks share one basic block and overlap their shared-memory latencies),
+// char_rare() is the out-of-line continuation along gfail[].
+struct ProbeResult {
+  uint32_t v, slotv, cid;
+  bool hit, rare;
+};
+__device__ __forceinline__ ProbeResult char_probe(const CharSmem& S, uint32_t r, uint32_t s, uint32_t f1, bool deep) {
+  ProbeResult q;
+  q.cid = r >> 16;
+  const uint32_t slot1 = s + q.cid, slot2 = f1 + q.cid;
+  const uint32_t c1 = S.check[slot1], c2 = S.check[slot2];
+  const bool hit1 = c1 == s, hit2 = c2 == f1;
+  q.hit = hit1 || hit2;
+  q.slotv = hit1 ? slot1 : slot2;
+  q.v = r & 0xFFFFu;  // the root entry in val[] format (fail = 0)
+  if (q.hit) q.v = S.val[q.slotv];
+  q.rare = !q.hit && deep && q.cid != 0;
+  return q;
+}
+// returns {val entry, slot} of the first fail-chain state behind f1 that has an edge for cid; slot 0 = none
+__device__ __noinline__ uint2 char_rare(SmemU16 check, SmemU32 val, const uint16_t* gfail, uint32_t f1, uint32_t cid) {
+  uint32_t t = gfail[f1];
+  while (t != 0) {
+    const uint32_t sl = t + cid;
+    if (check[sl] == t) return make_uint2(val[sl], sl);
+    t = gfail[t];
+  }
+  return make_uint2(0u, 0u);
+}
+
+constexpr int kChains = 2;              // independent automata per lane: the lane's chunk is split in kChains sub-chunks
+constexpr int kEvCapC = kEvCap / kChains;      // events per sub-chunk the deferred delivery can handle
+constexpr int kEvSlotsC = kEvSlots / kChains;  // ring slots per sub-chunk (>= bytes of a sub-chunk)
+
+// Walks one tile.  Every lane owns [a, b) of the concatenated text, split into kChains sub-chunks of `sub`
+// bytes that the lane walks INTERLEAVED (independent dependency chains hide the shared-memory latency of the
+// root -> check -> val lookups).  Each sub-chunk runs the same per-document segment logic as char_lane_walk()
+// (warm-up, owned region, document boundaries with markers) as a state machine driven by a warp-uniform loop:
+// whenever every busy sub-chunk has 12 well-formed bytes of one kind in front of it (four 3-byte units, or
+// twelve ASCII characters) the warp takes a branch-free unrolled step; near a boundary (region end, document
+// end, mixed unit lengths) the warp falls back to one unit per iteration.
+// one_doc: the whole tile lies in document cd = [cdoc_start, cdoc_end).
+// Events of sub-chunk c go to my_ev[c * kEvSlotsC ...); n_ev[c] counts all of them; multi_mask bit (c * kEvCapC + i)
+// = event i of sub-chunk c reports more than one key.  Returns false (warp-uniform) when the text is not
+// structurally valid UTF-8: the caller rescans the tile with the byte automaton.
 template <bool kChars, class OnDoc>
 __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanParams& p, const uint8_t* sbuf, int64_t origin, int64_t a,
-                                               int64_t b, int32_t stage_end, int32_t warmc, bool one_doc, int64_t cd,
-                                               int64_t cdoc_start, int64_t cdoc_end, uint32_t lead0, CharEvent* my_ev,
-                                               uint32_t& n_ev_out, uint32_t& multi_mask_out, OnDoc on_doc) {
+                                               int64_t b, int32_t sub, int32_t stage_end, int32_t warmc, bool one_doc, int64_t cd,
+                                               int64_t cdoc_start, int64_t cdoc_end, const uint32_t (&lead0)[kChains], CharEvent* my_ev,
+                                               uint32_t (&n_ev)[kChains], uint32_t& multi_mask_out, OnDoc on_doc) {
   constexpr unsigned kFull = 0xffffffffu;
-  const int32_t rb = (int32_t)(b - origin);
-  bool done = a >= b, ok = true;
-  int64_t d = cd, doc_start = cdoc_start, doc_end = cdoc_end;
-  if (!done && !one_doc) {
-    d = last_le(p.doc_off, p.n_docs, a);
-    doc_start = p.doc_off[d];
-    doc_end = p.doc_off[d + 1];
-  }
-  uint32_t n_ev = 0, multi_mask = 0;  // bit i: event i of this lane reports more than one key
-  if (!done && doc_start == a) {
-    for (int64_t e = first_ge(p.doc_off, p.n_docs, a); e <= d; ++e) on_doc(e, n_ev);
-  }
-  // current segment: owned bytes [a_seg, seg_end) of the document that ends at de (all relative to sbuf)
-  int32_t a_seg = (int32_t)(a - origin), pos = rb, de = 0, seg_end = 0, ebase = 0;
-  uint32_t s = 0, f1 = 0, k = 0, lead = lead0;
-  bool deep = false;
-  auto enter_segment = [&]() {
-    de = (int32_t)min(doc_end - origin, (int64_t)1 << 30);
-    seg_end = min(rb, de);
-    ebase = (int32_t)(origin - doc_start) + 1;
-    int64_t w = origin + a_seg - warmc;
-    const bool at_start = w < doc_start || origin + a_seg == doc_start;
-    if (at_start) w = doc_start;
-    pos = (int32_t)(w - origin);
-    s = 0; f1 = 0; k = 0; deep = false;
+  bool ok = true;
+  uint32_t multi_mask = 0;
+  // per sub-chunk state (all offsets relative to sbuf)
+  int32_t rb[kChains], a_seg[kChains], pos[kChains], de[kChains], seg_end[kChains], ebase[kChains];
+  uint32_t s[kChains], f1[kChains], k[kChains], lead[kChains];
+  bool deep[kChains], done[kChains];
+  int64_t d[kChains], doc_start[kChains], doc_end[kChains], bb[kChains];
+
+  auto enter_segment = [&](int c) {
+    de[c] = (int32_t)min(doc_end[c] - origin, (int64_t)1 << 30);
+    seg_end[c] = min(rb[c], de[c]);
+    ebase[c] = (int32_t)(origin - doc_start[c]) + 1;
+    int64_t w = origin + a_seg[c] - warmc;
+    const bool at_start = w < doc_start[c] || origin + a_seg[c] == doc_start[c];
+    if (at_start) w = doc_start[c];
+    pos[c] = (int32_t)(w - origin);
+    s[c] = 0; f1[c] = 0; k[c] = 0; deep[c] = false;
     if (!at_start) {  // the warm-up may begin inside a unit
       int skipped = 0;
-      while (pos < seg_end && (sbuf[pos] & 0xC0) == 0x80) {
-        ++pos;
+      while (pos[c] < seg_end[c] && (sbuf[pos[c]] & 0xC0) == 0x80) {
+        ++pos[c];
         if (++skipped > 3) { ok = false; break; }
       }
     }
   };
-  if (!done) enter_segment();
-
-  // consume one character whose root entry is r; cs / last = offsets of its first / last byte
-  auto step = [&](uint32_t r, int32_t cs, int32_t last, auto vote) {
-    uint32_t ref;
-    const uint32_t v = char_advance<decltype(vote)::value>(S, r, s, f1, deep, ref);
-    s = v & 0x7FFFu;
-    f1 = (v >> 16) & 0x7FFFu;
-    deep = (v >> 31) != 0u;
-    if (kChars) k += (cs >= a_seg) ? 1u : 0u;
-    const bool fire = (v & 0x8000u) && (uint32_t)(last - a_seg) < (uint32_t)(rb - a_seg);
-    if (fire) {
-      if (n_ev < (uint32_t)kEvCap) {
-        my_ev[n_ev] = CharEvent{kChars ? (int32_t)(lead + k) : last + ebase, ref};
-        multi_mask |= ((S.mbits[ref >> 5] >> (ref & 31u)) & 1u) << n_ev;
+#pragma unroll
+  for (int c = 0; c < kChains; ++c) {
+    const int64_t ac = min(a + (int64_t)c * sub, b);
+    bb[c] = c == kChains - 1 ? b : min(ac + sub, b);
+    rb[c] = (int32_t)(bb[c] - origin);
+    a_seg[c] = (int32_t)(ac - origin);
+    done[c] = ac >= bb[c];
+    n_ev[c] = 0;
+    lead[c] = lead0[c];
+    d[c] = cd; doc_start[c] = cdoc_start; doc_end[c] = cdoc_end;
+    pos[c] = rb[c]; de[c] = 0; seg_end[c] = 0; ebase[c] = 0; s[c] = 0; f1[c] = 0; k[c] = 0; deep[c] = false;
+    if (!done[c]) {
+      if (!one_doc) {
+        d[c] = last_le(p.doc_off, p.n_docs, ac);
+        doc_start[c] = p.doc_off[d[c]];
+        doc_end[c] = p.doc_off[d[c] + 1];
       }
-      ++n_ev;
+      if (doc_start[c] == ac) {
+        for (int64_t e = first_ge(p.doc_off, p.n_docs, ac); e <= d[c]; ++e) on_doc(c, e, 0u);
+      }
+      enter_segment(c);
+    }
+  }
+
+  // consume one character of sub-chunk c whose root entry is r; cs / last = offsets of its first / last byte
+  auto step = [&](int c, uint32_t r, int32_t cs, int32_t last, auto vote) {
+    uint32_t ref;
+    const uint32_t v = char_advance<decltype(vote)::value>(S, r, s[c], f1[c], deep[c], ref);
+    s[c] = v & 0x7FFFu;
+    f1[c] = (v >> 16) & 0x7FFFu;
+    deep[c] = (v >> 31) != 0u;
+    if (kChars) k[c] += (cs >= a_seg[c]) ? 1u : 0u;
+    const bool fire = (v & 0x8000u) && (uint32_t)(last - a_seg[c]) < (uint32_t)(rb[c] - a_seg[c]);
+    if (fire) {
+      my_ev[c * kEvSlotsC + n_ev[c]] = CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : last + ebase[c], ref};
+      multi_mask |= ((S.mbits[ref >> 5] >> (ref & 31u)) & 1u) << ((c * kEvCapC + n_ev[c]) & 31u);  // garbage beyond kEvCapC: direct pass
+      ++n_ev[c];
+    }
+  };
+
+  // one character of EVERY sub-chunk (warp converged): probes first, then the rare continuation behind a single
+  // vote, then the state update, then the events behind a single branch
+  auto multi_step = [&](const uint32_t (&r)[kChains], const int32_t (&cs)[kChains], int32_t len) {
+    ProbeResult q[kChains];
+    bool any_rare = false;
+#pragma unroll
+    for (int c = 0; c < kChains; ++c) {
+      q[c] = char_probe(S, r[c], s[c], f1[c], deep[c]);
+      any_rare = any_rare || q[c].rare;
+    }
+    if (__any_sync(kFull, any_rare)) {
+#pragma unroll
+      for (int c = 0; c < kChains; ++c)
+        if (q[c].rare) {
+          const uint2 x = char_rare(S.check, S.val, S.gfail, f1[c], q[c].cid);
+          if (x.y) { q[c].v = x.x; q[c].slotv = x.y; q[c].hit = true; }
+        }
+    }
+    bool fire[kChains], any_fire = false;
+#pragma unroll
+    for (int c = 0; c < kChains; ++c) {
+      const uint32_t v = q[c].v;
+      s[c] = v & 0x7FFFu;
+      f1[c] = (v >> 16) & 0x7FFFu;
+      deep[c] = (v >> 31) != 0u;
+      if (kChars) k[c] += (cs[c] >= a_seg[c]) ? 1u : 0u;
+      fire[c] = (v & 0x8000u) && (uint32_t)(cs[c] + len - 1 - a_seg[c]) < (uint32_t)(rb[c] - a_seg[c]);
+      any_fire = any_fire || fire[c];
+    }
+    if (any_fire) {
+#pragma unroll
+      for (int c = 0; c < kChains; ++c) {
+        if (fire[c]) {
+          const uint32_t ref = q[c].hit ? q[c].slotv : S.m + q[c].cid;
+          my_ev[c * kEvSlotsC + n_ev[c]] = CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : cs[c] + len - 1 + ebase[c], ref};
+          multi_mask |= ((S.mbits[ref >> 5] >> (ref & 31u)) & 1u) << ((c * kEvCapC + n_ev[c]) & 31u);
+          ++n_ev[c];
+        }
+      }
     }
   };
 
   for (;;) {
     if (__any_sync(kFull, !ok)) return false;
-    if (__all_sync(kFull, done)) break;
-    const uint32_t* wp = reinterpret_cast<const uint32_t*>(sbuf + (pos & ~3));
-    const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3];
-    const uint32_t sh = ((uint32_t)pos & 3u) * 8u;
-    const uint32_t A = __funnelshift_r(w0, w1, sh), B = __funnelshift_r(w1, w2, sh), C = __funnelshift_r(w2, w3, sh);
-    const bool room = pos < seg_end && pos + 12 <= min(de, stage_end);
-    const uint32_t bad3 = ((A ^ 0xE08080E0u) & 0xF0C0C0F0u) | ((B ^ 0x80E08080u) & 0xC0F0C0C0u) | ((C ^ 0x8080E080u) & 0xC0C0F0C0u);
-    if (__all_sync(kFull, done || (room && bad3 == 0u))) {
-      // four 3-byte units: payload = (b0 & 0xF) << 12 | (b1 & 0x3F) << 6 | (b2 & 0x3F), root index = payload - lo
-      auto step3 = [&](uint32_t w, int32_t cs) {
+    bool all_done = true;
+#pragma unroll
+    for (int c = 0; c < kChains; ++c) all_done = all_done && done[c];
+    if (__all_sync(kFull, all_done)) break;
+    uint32_t A[kChains], B[kChains], C[kChains];
+    bool can3 = true, can1 = true;
+#pragma unroll
+    for (int c = 0; c < kChains; ++c) {
+      const uint32_t* wp = reinterpret_cast<const uint32_t*>(sbuf + (pos[c] & ~3));
+      const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3];
+      const uint32_t sh = ((uint32_t)pos[c] & 3u) * 8u;
+      A[c] = __funnelshift_r(w0, w1, sh);
+      B[c] = __funnelshift_r(w1, w2, sh);
+      C[c] = __funnelshift_r(w2, w3, sh);
+      const bool room = pos[c] < seg_end[c] && pos[c] + 12 <= min(de[c], stage_end);
+      const uint32_t bad3 =
+          ((A[c] ^ 0xE08080E0u) & 0xF0C0C0F0u) | ((B[c] ^ 0x80E08080u) & 0xC0F0C0C0u) | ((C[c] ^ 0x8080E080u) & 0xC0C0F0C0u);
+      can3 = can3 && (done[c] || (room && bad3 == 0u));
+      can1 = can1 && (done[c] || (room && ((A[c] | B[c] | C[c]) & 0x80808080u) == 0u));
+    }
+    if (__all_sync(kFull, can3)) {
+      // four 3-byte units per sub-chunk: payload = (b0 & 0xF) << 12 | (b1 & 0x3F) << 6 | (b2 & 0x3F), root index = payload - lo
+      auto root3 = [&](uint32_t w) {
         const uint32_t wm = w & 0x3F3F0Fu;
         const uint32_t h = __dp4a(wm, 0x00000140u, S.neg_lo3_64);
         const uint32_t rel = h * 64u + (wm >> 16);
-        const uint32_t r = rel < S.n3 ? S.root3[rel] : 0u;
-        step(r, cs, cs + 2, std::true_type());
+        return rel < S.n3 ? S.root3[rel] : 0u;
       };
-      step3(A, pos);
-      step3(__byte_perm(A, B, 0x0543), pos + 3);
-      step3(__byte_perm(B, C, 0x0432), pos + 6);
-      step3(C >> 8, pos + 9);
-      if (!done) pos += 12;
-    } else if (__all_sync(kFull, done || (room && ((A | B | C) & 0x80808080u) == 0u))) {
-      // twelve ASCII characters
-      const uint32_t w[3] = {A, B, C};
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        uint32_t r[kChains];
+        int32_t cs[kChains];
+#pragma unroll
+        for (int c = 0; c < kChains; ++c) {
+          const uint32_t w = u == 0 ? A[c] : (u == 1 ? __byte_perm(A[c], B[c], 0x0543) : (u == 2 ? __byte_perm(B[c], C[c], 0x0432) : C[c] >> 8));
+          r[c] = root3(w);
+          cs[c] = pos[c] + 3 * u;
+        }
+        multi_step(r, cs, 3);
+      }
+#pragma unroll
+      for (int c = 0; c < kChains; ++c)
+        if (!done[c]) pos[c] += 12;
+    } else if (__all_sync(kFull, can1)) {
+      // twelve ASCII characters per sub-chunk
 #pragma unroll
       for (int i = 0; i < 12; ++i) {
-        const uint32_t byte = (w[i >> 2] >> ((i & 3) * 8)) & 0xFFu;
-        step(S.root[byte], pos + i, pos + i, std::true_type());
+        uint32_t r[kChains];
+        int32_t cs[kChains];
+#pragma unroll
+        for (int c = 0; c < kChains; ++c) {
+          const uint32_t w = i < 4 ? A[c] : (i < 8 ? B[c] : C[c]);
+          r[c] = S.root[(w >> ((i & 3) * 8)) & 0xFFu];
+          cs[c] = pos[c] + i;
+        }
+        multi_step(r, cs, 1);
       }
-      if (!done) pos += 12;
-    } else if (!done) {
-      if (pos >= seg_end) {
-        // end of the segment: the region is finished, or the next document starts here
-        const bool more = doc_end <= b && (doc_end < b || b == p.total);
-        if (!more) {
-          done = true;
+#pragma unroll
+      for (int c = 0; c < kChains; ++c)
+        if (!done[c]) pos[c] += 12;
+    } else {
+#pragma unroll
+      for (int c = 0; c < kChains; ++c) {
+        if (done[c]) continue;
+        if (pos[c] >= seg_end[c]) {
+          // end of the segment: the region is finished, or the next document starts here
+          const bool more = doc_end[c] <= bb[c] && (doc_end[c] < bb[c] || bb[c] == p.total);
+          if (!more) {
+            done[c] = true;
+          } else {
+            const int64_t at = doc_end[c];
+            ++d[c];
+            while (d[c] < p.n_docs) {
+              on_doc(c, d[c], n_ev[c]);
+              if (p.doc_off[d[c] + 1] > at) break;
+              ++d[c];
+            }
+            if (d[c] >= p.n_docs || at >= bb[c]) {
+              done[c] = true;
+            } else {
+              doc_start[c] = p.doc_off[d[c]];
+              doc_end[c] = p.doc_off[d[c] + 1];
+              a_seg[c] = (int32_t)(doc_start[c] - origin);
+              lead[c] = 0;
+              enter_segment(c);
+            }
+          }
         } else {
-          const int64_t at = doc_end;
-          ++d;
-          while (d < p.n_docs) {
-            on_doc(d, n_ev);
-            if (p.doc_off[d + 1] > at) break;
-            ++d;
-          }
-          if (d >= p.n_docs || at >= b) {
-            done = true;
+          // one unit of any length
+          const uint32_t b0 = A[c] & 0xFFu;
+          int32_t len = 1;
+          uint32_t r = 0;
+          if (b0 < 0x80u) {
+            r = S.root[b0];
+          } else if (b0 < 0xC0u || b0 >= 0xF8u) {
+            ok = false;
           } else {
-            doc_start = p.doc_off[d];
-            doc_end = p.doc_off[d + 1];
-            a_seg = (int32_t)(doc_start - origin);
-            lead = 0;
-            enter_segment();
+            len = b0 < 0xE0u ? 2 : (b0 < 0xF0u ? 3 : 4);
+            const uint32_t b1 = (A[c] >> 8) & 0xFFu, b2 = (A[c] >> 16) & 0xFFu, b3 = A[c] >> 24;
+            if (pos[c] + len > de[c]) ok = false;  // cut by the end of the document
+            if ((b1 & 0xC0u) != 0x80u) ok = false;
+            if (len >= 3 && (b2 & 0xC0u) != 0x80u) ok = false;
+            if (len == 4 && (b3 & 0xC0u) != 0x80u) ok = false;
+            uint32_t code, lo, n, off;
+            if (len == 2) {
+              code = ((b0 & 0x1Fu) << 6) | (b1 & 0x3Fu);
+              lo = S.lo2; n = S.n2; off = S.off2;
+            } else if (len == 3) {
+              code = ((b0 & 0x0Fu) << 12) | ((b1 & 0x3Fu) << 6) | (b2 & 0x3Fu);
+              lo = S.lo3; n = S.n3; off = S.off3;
+            } else {
+              code = ((b0 & 0x07u) << 18) | ((b1 & 0x3Fu) << 12) | ((b2 & 0x3Fu) << 6) | (b3 & 0x3Fu);
+              lo = S.lo4; n = S.n4; off = S.off4;
+            }
+            const uint32_t rel = code - lo;
+            if (ok && rel < n) r = S.root[off + rel];
+          }
+          if (ok) {
+            if (pos[c] + len - 1 >= rb[c]) {
+              done[c] = true;  // the unit ends in the next region (the document goes on beyond it)
+            } else {
+              step(c, r, pos[c], pos[c] + len - 1, std::false_type());
+              pos[c] += len;
+            }
           }
         }
-      } else {
-        // one unit of any length
-        const uint32_t b0 = A & 0xFFu;
-        int32_t len = 1;
-        uint32_t r = 0;
-        if (b0 < 0x80u) {
-          r = S.root[b0];
-        } else if (b0 < 0xC0u || b0 >= 0xF8u) {
-          ok = false;
-        } else {
-          len = b0 < 0xE0u ? 2 : (b0 < 0xF0u ? 3 : 4);
-          const uint32_t b1 = (A >> 8) & 0xFFu, b2 = (A >> 16) & 0xFFu, b3 = A >> 24;
-          if (pos + len > de) ok = false;  // cut by the end of the document
-          if ((b1 & 0xC0u) != 0x80u) ok = false;
-          if (len >= 3 && (b2 & 0xC0u) != 0x80u) ok = false;
-          if (len == 4 && (b3 & 0xC0u) != 0x80u) ok = false;
-          uint32_t code, lo, n, off;
-          if (len == 2) {
-            code = ((b0 & 0x1Fu) << 6) | (b1 & 0x3Fu);
-            lo = S.lo2; n = S.n2; off = S.off2;
-          } else if (len == 3) {
-            code = ((b0 & 0x0Fu) << 12) | ((b1 & 0x3Fu) << 6) | (b2 & 0x3Fu);
-            lo = S.lo3; n = S.n3; off = S.off3;
-          } else {
-            code = ((b0 & 0x07u) << 18) | ((b1 & 0x3Fu) << 12) | ((b2 & 0x3Fu) << 6) | (b3 & 0x3Fu);
-            lo = S.lo4; n = S.n4; off = S.off4;
-          }
-          const uint32_t rel = code - lo;
-          if (ok && rel < n) r = S.root[off + rel];
-        }
-        if (ok) {
-          if (pos + len - 1 >= rb) {
-            done = true;  // the unit ends in the next lane's region (the document goes on beyond b)
-          } else {
-            step(r, pos, pos + len - 1, std::false_type());
-            pos += len;
-          }
-        }
+        if (done[c]) pos[c] = rb[c];
       }
-      if (done) pos = rb;
     }
   }
-  n_ev_out = n_ev;
   multi_mask_out = multi_mask;
   return true;
 }
 
 // ---- delivery of a walked tile --------------------------------------------------------------------------
-// Document-start markers, then cooperative expansion of the warp's events (lane, sequence order = output
-// order) into final Aha::Hit records: one event per lane per round, output tables read event-parallel.
-__device__ __forceinline__ void deliver_events(const CharParams& P, unsigned long long prefix, uint32_t excl_lane, uint32_t n_ev,
-                                               uint32_t n_mark, uint32_t multi_mask, const CharEvent* warp_ev, const int2* my_mark,
-                                               int lane) {
+// Document-start markers, then cooperative expansion of the warp's events (lane, sub-chunk, sequence order =
+// output order) into final Aha::Hit records: one event per lane per round, kDeliverRounds rounds in flight so
+// that the L2 latency of the event ring and of ref_rec[] is paid once per batch.
+constexpr int kDeliverRounds = 4;
+
+struct WalkedTile {
+  uint32_t excl_lane;   // hits of lower lanes in the tile
+  uint32_t hits0;       // hits of this lane's sub-chunk 0 (base of sub-chunk 1)
+  uint32_t n_ev0, n_ev1;
+  uint32_t n_mark0, n_mark1;
+  uint32_t multi_mask;
+};
+
+__device__ __forceinline__ void deliver_events(const CharParams& P, unsigned long long prefix, const WalkedTile& w,
+                                               const CharEvent* warp_ev, const int2* my_mark, int lane) {
   const ScanParams& p = P.f.sp;
   const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
-  const CharEvent* my_ev = warp_ev + lane * kEvCap;
-  for (uint32_t k = 0; k < n_mark; ++k) {
-    const int y = my_mark[k].y;  // events of this lane before the document start
-    uint32_t before = (uint32_t)y;
-    for (uint32_t mm = multi_mask & (y >= 32 ? 0xffffffffu : ((1u << y) - 1u)); mm; mm &= mm - 1)
-      before += P.t.ref_rec[my_ev[__ffs(mm) - 1].ref].n - 1u;
-    p.doc_hit_off[my_mark[k].x] = (int64_t)(prefix + excl_lane + before);
+  const CharEvent* my_ev = warp_ev + lane * kEvSlots;
+#pragma unroll
+  for (int c = 0; c < kChains; ++c) {
+    const uint32_t n_mark = c ? w.n_mark1 : w.n_mark0;
+    const uint32_t cmask = (w.multi_mask >> (c * kEvCapC)) & ((1u << kEvCapC) - 1u);
+    for (uint32_t k = 0; k < n_mark; ++k) {
+      const int2 mk = my_mark[c * kMarkCapC + k];
+      const int y = mk.y;  // events of this sub-chunk before the document start
+      uint32_t before = (uint32_t)y;
+      for (uint32_t mm = cmask & ((1u << y) - 1u); mm; mm &= mm - 1)
+        before += P.t.ref_rec[my_ev[c * kEvSlotsC + __ffs(mm) - 1].ref].n - 1u;
+      p.doc_hit_off[mk.x] = (int64_t)(prefix + w.excl_lane + (c ? w.hits0 : 0u) + before);
+    }
   }
+  const uint32_t n_ev = w.n_ev0 + w.n_ev1;
   uint32_t ev_incl = n_ev;
   for (int o = 1; o < 32; o <<= 1) {
     uint32_t v = __shfl_up_sync(0xffffffffu, ev_incl, o);
@@ -353,29 +516,50 @@ __device__ __forceinline__ void deliver_events(const CharParams& P, unsigned lon
   const uint32_t E = __shfl_sync(0xffffffffu, ev_incl, 31);
   if (!p.hits || E == 0) return;
   uint32_t run = 0;
-  for (uint32_t base = 0; base < E; base += 32) {
-    const uint32_t i = base + lane;
-    uint32_t lo = 0;
+  for (uint32_t base = 0; base < E; base += 32 * kDeliverRounds) {
+    CharEvent ev[kDeliverRounds];
+    RefRec rr[kDeliverRounds];
+    // phase 1: which event does this lane expand in each round; fetch it
 #pragma unroll
-    for (int step = 16; step > 0; step >>= 1) {
-      const uint32_t cand = lo + step;
-      const uint32_t ex = __shfl_sync(0xffffffffu, ev_excl, cand & 31);
-      if (cand < 32 && ex <= i) lo = cand;
+    for (int r = 0; r < kDeliverRounds; ++r) {
+      const uint32_t i = base + r * 32 + lane;
+      ev[r] = CharEvent{0, 0};
+      if (base + r * 32 < E) {  // warp-uniform
+        uint32_t lo = 0;
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1) {
+          const uint32_t cand = lo + step;
+          const uint32_t ex = __shfl_sync(0xffffffffu, ev_excl, cand & 31);
+          if (cand < 32 && ex <= i) lo = cand;
+        }
+        const uint32_t ex = __shfl_sync(0xffffffffu, ev_excl, lo);
+        const uint32_t n0 = __shfl_sync(0xffffffffu, w.n_ev0, lo);
+        if (i < E) {
+          const uint32_t idx = i - ex;
+          ev[r] = warp_ev[lo * kEvSlots + (idx < n0 ? idx : kEvSlotsC + (idx - n0))];
+        }
+      }
     }
-    const uint32_t ex = __shfl_sync(0xffffffffu, ev_excl, lo);
-    CharEvent ev{0, 0};
-    RefRec rr{0, 0, 0, 0};
-    if (i < E) {
-      ev = warp_ev[lo * kEvCap + (i - ex)];
-      rr = P.t.ref_rec[ev.ref];
+    // phase 2: what fires there
+#pragma unroll
+    for (int r = 0; r < kDeliverRounds; ++r) {
+      rr[r] = RefRec{0, 0, 0, 0};
+      if (base + r * 32 + lane < E) rr[r] = P.t.ref_rec[ev[r].ref];
     }
-    uint32_t len_incl = rr.n;
-    for (int o = 1; o < 32; o <<= 1) {
-      uint32_t v = __shfl_up_sync(0xffffffffu, len_incl, o);
-      if (lane >= o) len_incl += v;
+    // phase 3: positions and stores
+#pragma unroll
+    for (int r = 0; r < kDeliverRounds; ++r) {
+      if (base + r * 32 < E) {  // warp-uniform
+        uint32_t len_incl = rr[r].n;
+        for (int o = 1; o < 32; o <<= 1) {
+          uint32_t v = __shfl_up_sync(0xffffffffu, len_incl, o);
+          if (lane >= o) len_incl += v;
+        }
+        if (base + r * 32 + lane < E)
+          expand_event(p, rr[r], ev[r].end, chars, p.hits, (int64_t)prefix + run + (len_incl - rr[r].n), P.f.hit_cap);
+        run += __shfl_sync(0xffffffffu, len_incl, 31);
+      }
     }
-    if (i < E) expand_event(p, rr, ev.end, chars, p.hits, (int64_t)prefix + run + (len_incl - rr.n), P.f.hit_cap);
-    run += __shfl_sync(0xffffffffu, len_incl, 31);
   }
 }
 
@@ -408,7 +592,8 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
 #pragma unroll
   for (int c = 0; c < 3; ++c) { T.lo[c] = P.t.lo[c]; T.n[c] = P.t.n[c]; T.off[c] = P.t.off[c]; }
   CharSmem S;        // fast walk
-  S.root = s_root; S.root3 = s_root + P.t.off[1]; S.val = s_val; S.check = s_check; S.gfail = P.t.gfail; S.mbits = s_mbits;
+  S.root.base = smem_u32(s_root); S.root3.base = smem_u32(s_root + P.t.off[1]); S.val.base = smem_u32(s_val);
+  S.check.base = smem_u32(s_check); S.gfail = P.t.gfail; S.mbits.base = smem_u32(s_mbits);
   S.m = P.t.m;
   S.lo2 = P.t.lo[0]; S.n2 = P.t.n[0]; S.off2 = P.t.off[0];
   S.lo3 = P.t.lo[1]; S.n3 = P.t.n[1]; S.off3 = P.t.off[1];
@@ -421,13 +606,15 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
   const int64_t gwarp = (int64_t)blockIdx.x * kFusedWarps + warp;
   const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
   const int32_t warmc = (int32_t)p.warm + 3;
+  const int32_t sub = F.chunk / kChains;
   uint32_t parity = 0;
   int buf = 0;
   // the tile walked in the previous round, delivered after the next walk so that its look-back never waits
   bool pend = false;
   unsigned int pend_t = 0;
-  uint32_t pend_excl = 0, pend_T = 0, pend_n_ev = 0, pend_n_mark = 0, pend_multi = 0;
+  uint32_t pend_T = 0;
   int pend_buf = 0;
+  WalkedTile pw = {0, 0, 0, 0, 0, 0, 0};
   // document that contained the previous tile (tiles come in increasing order)
   int64_t cd = 0, cdoc_start = 0, cdoc_end = -1;
 
@@ -437,10 +624,11 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
     t = __shfl_sync(0xffffffffu, t, 0);
     const bool have = (int64_t)t < F.n_tiles;
     bool bad = false, over = false;
-    uint32_t n_ev = 0, n_mark = 0, multi_mask = 0, excl_lane = 0, Ttile = 0, lead0 = 0;
+    WalkedTile w = {0, 0, 0, 0, 0, 0, 0};
+    uint32_t Ttile = 0, lead0[kChains] = {0, 0};
     int64_t origin = 0, a = 0, b = 0;
-    CharEvent* warp_ev = P.events + ((gwarp * 2 + buf) * 32) * kEvCap;
-    CharEvent* my_ev = warp_ev + lane * kEvCap;
+    CharEvent* warp_ev = P.events + ((gwarp * 2 + buf) * 32) * kEvSlots;
+    CharEvent* my_ev = warp_ev + lane * kEvSlots;
     int2* my_mark = F.marks + ((gwarp * 2 + buf) * 32 + lane) * kMarkCap;
     if (have) {
       const int64_t tile_start = (int64_t)t * F.tile;
@@ -459,11 +647,11 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
         cdoc_start = p.doc_off[cd];
         cdoc_end = p.doc_off[cd + 1];
       }
-      const bool fast = cdoc_start <= tile_start && cdoc_end >= tile_end;  // the tile lies inside one document
+      const bool one_doc = cdoc_start <= tile_start && cdoc_end >= tile_end;  // the tile lies inside one document
       uint64_t tl = 0, dlb = 0;
       if (chars) {
         tl = F.tile_lead[t];
-        if (fast) dlb = p.doc_lead_base[cd];
+        if (one_doc) dlb = p.doc_lead_base[cd];
       }
       if (bulk_end > origin) {
         mbar_wait(bar, parity);
@@ -474,51 +662,62 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
       a = min(tile_start + (int64_t)lane * F.chunk, tile_end);
       b = min(a + (int64_t)F.chunk, tile_end);
       if (chars) {
-        uint32_t mine = count_leads_smem(sbuf, origin, a, b);
+        const int64_t a1 = min(a + sub, b);
+        const uint32_t mine0 = count_leads_smem(sbuf, origin, a, a1);
+        const uint32_t mine = mine0 + count_leads_smem(sbuf, origin, a1, b);
         uint32_t incl = mine;
         for (int o = 1; o < 32; o <<= 1) {
           uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
           if (lane >= o) incl += v;
         }
         const uint64_t before_a = tl + (incl - mine);
-        if (a < b) lead0 = (uint32_t)(before_a - (fast ? dlb : p.doc_lead_base[last_le(p.doc_off, p.n_docs, a)]));
+        if (a < b) lead0[0] = (uint32_t)(before_a - (one_doc ? dlb : p.doc_lead_base[last_le(p.doc_off, p.n_docs, a)]));
+        if (a1 < b) lead0[1] = (uint32_t)(before_a + mine0 - (one_doc ? dlb : p.doc_lead_base[last_le(p.doc_off, p.n_docs, a1)]));
       }
 
-      // ---- walk: events to the lane's ring slot, no global loads on the chain
-      auto on_doc = [&](int64_t d, uint32_t nev) {
-        if (n_mark < (uint32_t)kMarkCap) my_mark[n_mark] = make_int2((int)d, (int)nev);
-        ++n_mark;
+      // ---- walk: events to the lane's ring slots, no global loads on the chain
+      uint32_t n_ev[kChains] = {0, 0}, n_mark[kChains] = {0, 0};
+      auto on_doc = [&](int c, int64_t d, uint32_t nev) {
+        if (n_mark[c] < (uint32_t)kMarkCapC) my_mark[c * kMarkCapC + n_mark[c]] = make_int2((int)d, (int)nev);
+        ++n_mark[c];
       };
       const int32_t stage_end = (int32_t)(want_end - origin);
-      const bool ok = chars ? char_tile_walk<true>(S, p, sbuf, origin, a, b, stage_end, warmc, fast, cd, cdoc_start, cdoc_end, lead0, my_ev,
-                                                   n_ev, multi_mask, on_doc)
-                            : char_tile_walk<false>(S, p, sbuf, origin, a, b, stage_end, warmc, fast, cd, cdoc_start, cdoc_end, lead0, my_ev,
-                                                    n_ev, multi_mask, on_doc);
+      const bool ok = chars ? char_tile_walk<true>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start, cdoc_end, lead0,
+                                                   my_ev, n_ev, w.multi_mask, on_doc)
+                            : char_tile_walk<false>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start, cdoc_end, lead0,
+                                                    my_ev, n_ev, w.multi_mask, on_doc);
       bad = __any_sync(0xffffffffu, !ok);
-      over = __any_sync(0xffffffffu, n_ev > (uint32_t)kEvCap || n_mark > (uint32_t)kMarkCap);
+      over = __any_sync(0xffffffffu, n_ev[0] > (uint32_t)kEvCapC || n_ev[1] > (uint32_t)kEvCapC || n_mark[0] > (uint32_t)kMarkCapC ||
+                                         n_mark[1] > (uint32_t)kMarkCapC);
+      w.n_ev0 = n_ev[0]; w.n_ev1 = n_ev[1]; w.n_mark0 = n_mark[0]; w.n_mark1 = n_mark[1];
       __syncwarp();
 
       // ---- hits per lane, tile aggregate, published at once (nobody ever waits for a walk to be delivered)
       uint32_t n_hits;
       if (bad) {
         CountSink cs;
-        fallback.walk(F, sbuf, origin, a, b, lead0, cs);
+        fallback.walk(F, sbuf, origin, a, b, lead0[0], cs);
         n_hits = cs.n;
       } else if (over) {
         uint32_t c = 0;
-        char_lane_walk(P, T, sbuf, origin, a, b, lead0, [&](int32_t, uint32_t ref) { c += P.t.ref_rec[ref].n; },
-                       [&](int64_t) {});
+        char_lane_walk(P, T, sbuf, origin, a, b, lead0[0], [&](int32_t, uint32_t ref) { c += P.t.ref_rec[ref].n; }, [&](int64_t) {});
         n_hits = c;
       } else {
-        n_hits = n_ev;
-        for (uint32_t mm = multi_mask; mm; mm &= mm - 1) n_hits += P.t.ref_rec[my_ev[__ffs(mm) - 1].ref].n - 1u;
+        uint32_t extra[kChains] = {0, 0};
+#pragma unroll
+        for (int c = 0; c < kChains; ++c) {
+          for (uint32_t mm = (w.multi_mask >> (c * kEvCapC)) & ((1u << kEvCapC) - 1u); mm; mm &= mm - 1)
+            extra[c] += P.t.ref_rec[my_ev[c * kEvSlotsC + __ffs(mm) - 1].ref].n - 1u;
+        }
+        w.hits0 = n_ev[0] + extra[0];
+        n_hits = w.hits0 + n_ev[1] + extra[1];
       }
       uint32_t incl = n_hits;
       for (int o = 1; o < 32; o <<= 1) {
         uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
         if (lane >= o) incl += v;
       }
-      excl_lane = incl - n_hits;
+      w.excl_lane = incl - n_hits;
       Ttile = __shfl_sync(0xffffffffu, incl, 31);
       publish_aggregate(F, t, Ttile, lane);
     }
@@ -527,9 +726,9 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
     if (pend) {
       const unsigned long long prefix = resolve_prefix(F, pend_t, lane);
       if ((int64_t)pend_t == F.n_tiles - 1 && lane == 0) *F.total_hits = prefix + pend_T;
-      const CharEvent* pev = P.events + ((gwarp * 2 + pend_buf) * 32) * kEvCap;
+      const CharEvent* pev = P.events + ((gwarp * 2 + pend_buf) * 32) * kEvSlots;
       const int2* pmark = F.marks + ((gwarp * 2 + pend_buf) * 32 + lane) * kMarkCap;
-      deliver_events(P, prefix, pend_excl, pend_n_ev, pend_n_mark, pend_multi, pev, pmark, lane);
+      deliver_events(P, prefix, pw, pev, pmark, lane);
       pend = false;
     }
     if (!have) break;
@@ -541,12 +740,12 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
       if (lane == 0) atomicAdd(F.n_direct, 1u);
       if (bad) {
         DirectSink ds;
-        ds.out = p.hits; ds.doc_hit_off = p.doc_hit_off; ds.idx = (int64_t)(prefix + excl_lane); ds.cap = F.hit_cap;
-        fallback.walk(F, sbuf, origin, a, b, lead0, ds);
+        ds.out = p.hits; ds.doc_hit_off = p.doc_hit_off; ds.idx = (int64_t)(prefix + w.excl_lane); ds.cap = F.hit_cap;
+        fallback.walk(F, sbuf, origin, a, b, lead0[0], ds);
       } else {
-        int64_t idx = (int64_t)(prefix + excl_lane);
+        int64_t idx = (int64_t)(prefix + w.excl_lane);
         char_lane_walk(
-            P, T, sbuf, origin, a, b, lead0,
+            P, T, sbuf, origin, a, b, lead0[0],
             [&](int32_t end, uint32_t ref) {
               const RefRec rr = P.t.ref_rec[ref];
               if (p.hits) expand_event(p, rr, end, chars, p.hits, idx, F.hit_cap);
@@ -556,8 +755,8 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
       }
     } else {
       pend = true;
-      pend_t = t; pend_excl = excl_lane; pend_T = Ttile; pend_n_ev = n_ev; pend_n_mark = n_mark; pend_multi = multi_mask;
-      pend_buf = buf;
+      pend_t = t; pend_T = Ttile; pend_buf = buf;
+      pw = w;
       buf ^= 1;
     }
     __syncwarp();

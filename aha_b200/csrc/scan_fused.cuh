@@ -22,7 +22,8 @@
 namespace aha {
 
 constexpr int kLaneCap = 32;      // scratch records per lane per tile
-constexpr int kMarkCap = 2;       // document-start markers per lane per tile
+constexpr int kMarkCap = 4;       // document-start markers per lane per tile
+constexpr int kMarkCapC = 2;      // ... per sub-chunk (scan_char.cuh walks two sub-chunks per lane)
 constexpr int kFusedWarps = 16;   // warps per CTA
 
 struct FusedParams {
@@ -203,26 +204,26 @@ __device__ __forceinline__ void publish_aggregate(const FusedParams& P, unsigned
     st_relaxed_u64(&P.group_agg[g], (total << 2) | 1ull);
   }
 }
-// resolve_prefix: hits in all tiles before t.  Whole warp; waits (with back-off) for earlier tiles that have
-// not finished their walk yet.  The caller normally defers this call by one tile so that it never waits.
-// Only the first tile of a group looks back over the group arrays (all warps polling the same few lines
-// serialises in L2); the other 31 tiles read the group's exclusive prefix it publishes.
+// resolve_prefix: hits in all tiles before t.  Whole warp; waits (with back-off) only for earlier tiles that
+// have not finished their WALK yet (never for another warp's delivery).  The caller normally defers this call
+// by one tile so that it does not wait at all.  The group's exclusive prefix is computed by the first tile of the
+// group that gets here and published for the other 31 (all warps polling the same few group lines would
+// serialise in L2).
 __device__ __forceinline__ unsigned long long resolve_prefix(const FusedParams& P, unsigned int t, int lane) {
   const unsigned int g = t >> 5, j = t & 31u;
-  if (j != 0) {
-    // tiles of the same group in front of t (lanes < j) and the group's exclusive prefix (lane 31)
-    unsigned long long v = 1ull;
-    for (;;) {
-      if ((unsigned)lane < j) v = ld_relaxed_u64(&P.tile_state[((size_t)g << 5) + lane]);
-      else if (lane == 31) v = ld_relaxed_u64(&P.group_excl[g]);
-      if (__all_sync(0xffffffffu, (v & 3ull) != 0ull)) break;
-      __nanosleep(64);
-    }
-    unsigned long long sum = ((unsigned)lane < j || lane == 31) ? (v >> 2) : 0ull;
-    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    return sum;
+  // tiles of the same group in front of t (lanes < j); lane 31 peeks at the group's exclusive prefix
+  unsigned long long v = 1ull;
+  for (;;) {
+    if ((unsigned)lane < j) v = ld_relaxed_u64(&P.tile_state[((size_t)g << 5) + lane]);
+    else if (lane == 31) v = ld_relaxed_u64(&P.group_excl[g]);
+    if (__all_sync(0xffffffffu, lane == 31 || (v & 3ull) != 0ull)) break;
+    __nanosleep(64);
   }
-  // first tile of group g: groups in front of g, 32 per step, stopping at the first one whose exclusive prefix is known
+  unsigned long long in_group = (unsigned)lane < j ? (v >> 2) : 0ull;
+  for (int o = 16; o > 0; o >>= 1) in_group += __shfl_xor_sync(0xffffffffu, in_group, o);
+  const unsigned long long e31 = __shfl_sync(0xffffffffu, v, 31);
+  if ((e31 & 3ull) == 2ull) return (e31 >> 2) + in_group;
+  // groups in front of g, 32 per step, stopping at the first one whose exclusive prefix is known
   unsigned long long G = 0;
   long long h = (long long)g - 1;
   while (h >= 0) {
@@ -248,7 +249,7 @@ __device__ __forceinline__ unsigned long long resolve_prefix(const FusedParams& 
     h -= 32;
   }
   if (lane == 0) st_relaxed_u64(&P.group_excl[g], (G << 2) | 2ull);
-  return G;
+  return G + in_group;
 }
 // walk-then-resolve in one go (kernels that do not defer)
 __device__ __forceinline__ unsigned long long tile_exclusive_prefix(const FusedParams& P, unsigned int t, uint32_t T, int lane) {

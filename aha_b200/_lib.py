@@ -31,7 +31,8 @@ def build(force=False, verbose=False):
         if all(os.path.getmtime(s) <= t for s in _sources()):
             return SO_PATH
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + ["-o", SO_PATH, os.path.join(CSRC, "api.cu")]
+    extra = os.environ.get("AHA_B200_NVCC_EXTRA", "").split()  # e.g. -DAHA_B200_PHASES (per-phase cycle counters on stderr)
+    cmd = [nvcc] + NVCC_FLAGS + extra + ["-o", SO_PATH, os.path.join(CSRC, "api.cu")]
     if verbose:
         print(" ".join(cmd))
     subprocess.check_call(cmd)

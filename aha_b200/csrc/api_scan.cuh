@@ -1,5 +1,6 @@
 // api_scan.cuh -- scan / hits / generator entry points (included at the end of api.cu).
 #pragma once
+#include <chrono>
 
 namespace aha {
 
@@ -78,7 +79,7 @@ static int32_t run_v1(ScanParams p, cudaStream_t st, aha_hits* res, HitsOwner* o
     AHA_CUDA(cudaMallocAsync(&lead_counts, (p.n_chunks + 1) * sizeof(uint32_t), st));
     AHA_CUDA(cudaMallocAsync(&lead_prefix, (p.n_chunks + 1) * sizeof(uint64_t), st));
     AHA_CUDA(cudaMallocAsync(&doc_lead, (p.n_docs + 1) * sizeof(uint64_t), st));
-    count_leads_kernel<<<(unsigned)((p.n_chunks + 1 + 255) / 256), 256, 0, st>>>(p.text, p.total, p.chunk, p.n_chunks, lead_counts);
+    count_leads_kernel<<<(unsigned)((p.n_chunks + 1 + 7) / 8), 256, 0, st>>>(p.text, p.total, p.chunk, p.n_chunks, lead_counts);
     int32_t rc = exclusive_sum_u32_to_u64(lead_counts, lead_prefix, p.n_chunks + 1, st);
     if (rc) return rc;
     doc_lead_base_kernel<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(p.text, p.total, p.doc_off, p.n_docs, p.chunk,
@@ -150,9 +151,9 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
   uint64_t* tile_lead = nullptr;
   uint64_t* doc_lead = nullptr;
   const int64_t n_groups = (fp.n_tiles + 31) / 32;
-  const size_t state_words = (size_t)(fp.n_tiles + 1) + 3 * (size_t)(n_groups + 1);
+  const size_t state_words = (size_t)(fp.n_tiles + 1) + (size_t)(n_groups + 1);
   AHA_CUDA(cudaMallocAsync(&tile_state, state_words * sizeof(unsigned long long), st));
-  AHA_CUDA(cudaMallocAsync(&counters, 16, st));
+  AHA_CUDA(cudaMallocAsync(&counters, 16 + 8 * 8, st));  // + 8 phase-cycle counters (AHA_B200_PHASES)
   // character automaton in shared memory when the dictionary allows it (plain match, with or without char units)
   const bool use_char = dd->hot.ok && !(p.mode & AHA_SEP);
   CharParams cp;
@@ -179,9 +180,7 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
   AHA_CUDA(cudaMallocAsync(&own->dev_doc_hit_off, (p.n_docs + 1) * sizeof(int64_t), st));
   p.doc_hit_off = static_cast<int64_t*>(own->dev_doc_hit_off);
   fp.tile_state = tile_state;
-  fp.group_acc = tile_state + (fp.n_tiles + 1);
-  fp.group_agg = fp.group_acc + (n_groups + 1);
-  fp.group_excl = fp.group_agg + (n_groups + 1);
+  fp.group_excl = tile_state + (fp.n_tiles + 1);
   fp.ticket = counters;
   fp.n_direct = counters + 1;
   fp.total_hits = reinterpret_cast<unsigned long long*>(counters + 2);
@@ -194,36 +193,52 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
     AHA_CUDA(cudaFuncSetAttribute(scan_char_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   }
 
-  AHA_CUDA(cudaEventRecord(ev0, st));
+#ifdef AHA_B200_PHASES
+  auto h_now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+  const double h0 = h_now();
+#define AHA_HSTAMP(what) fprintf(stderr, "[host] %-14s +%.3f ms\n", what, h_now() - h0)
+#else
+#define AHA_HSTAMP(what) do { } while (0)
+#endif
+  // every allocation happens before the timed region: growing the pool synchronises with the stream
+  const bool count_only = (p.mode & AHA_COUNT_ONLY) != 0;
+  int64_t cap = 0;
+  if (!count_only && dfa->hits_per_byte >= 0) {
+    cap = (int64_t)((double)p.total * dfa->hits_per_byte * 1.25) + 4096;
+    AHA_CUDA(cudaMallocAsync(&own->dev_hits, (size_t)cap * sizeof(aha_hit), st));
+  }
   if (chars && p.total > 0) {
     AHA_CUDA(cudaMallocAsync(&lead_counts, (fp.n_tiles + 1) * sizeof(uint32_t), st));
     AHA_CUDA(cudaMallocAsync(&tile_lead, (fp.n_tiles + 1) * sizeof(uint64_t), st));
     AHA_CUDA(cudaMallocAsync(&doc_lead, (p.n_docs + 1) * sizeof(uint64_t), st));
-    count_leads_kernel<<<(unsigned)((fp.n_tiles + 1 + 127) / 128), 128, 0, st>>>(p.text, p.total, fp.tile, fp.n_tiles, lead_counts);
+  }
+  AHA_CUDA(cudaEventRecord(ev0, st));
+  if (chars && p.total > 0) {
+    count_leads_kernel<<<(unsigned)((fp.n_tiles + 1 + 7) / 8), 256, 0, st>>>(p.text, p.total, fp.tile, fp.n_tiles, lead_counts);
     int32_t rc = exclusive_sum_u32_to_u64(lead_counts, tile_lead, fp.n_tiles + 1, st);
     if (rc) return rc;
     doc_lead_base_kernel<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(p.text, p.total, p.doc_off, p.n_docs, fp.tile,
                                                                               tile_lead, doc_lead);
     fp.tile_lead = tile_lead;
     p.doc_lead_base = doc_lead;
+    AHA_HSTAMP("lead prepass");
   }
   // capacity of the hit buffer: exact after a counting run on first use, density history afterwards
-  const bool count_only = (p.mode & AHA_COUNT_ONLY) != 0;
   unsigned long long total_hits = 0;
-  int64_t cap = 0;
   bool have_result = false;
   for (int attempt = 0; attempt < 3 && !have_result; ++attempt) {
-    bool counting = count_only || (attempt == 0 && dfa->hits_per_byte < 0);
-    if (!counting) {
-      if (attempt == 0 || cap == 0) cap = (int64_t)((double)p.total * dfa->hits_per_byte * 1.25) + 4096;
+    bool counting = count_only || (attempt == 0 && cap == 0);
+    if (!counting && attempt > 0) {  // the first estimate was missing or too small: cap holds the exact size now
       if (own->dev_hits) AHA_CUDA(cudaFreeAsync(own->dev_hits, st));
+      own->dev_hits = nullptr;
       AHA_CUDA(cudaMallocAsync(&own->dev_hits, (size_t)cap * sizeof(aha_hit), st));
     }
+    AHA_HSTAMP("hits alloc");
     p.hits = counting ? nullptr : static_cast<aha_hit*>(own->dev_hits);
     fp.hit_cap = counting ? 0 : cap;
     fp.sp = p;
     AHA_CUDA(cudaMemsetAsync(tile_state, 0, state_words * sizeof(unsigned long long), st));
-    AHA_CUDA(cudaMemsetAsync(counters, 0, 16, st));
+    AHA_CUDA(cudaMemsetAsync(counters, 0, 16 + 8 * 8, st));
     AHA_CUDA(cudaMemsetAsync(own->dev_doc_hit_off, 0, (p.n_docs + 1) * sizeof(int64_t), st));
     if (fp.n_tiles > 0) {
       if (use_char) {
@@ -238,8 +253,19 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
     finalize_doc_off_kernel<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(p.doc_off, p.n_docs, p.total, fp.total_hits,
                                                                                  p.doc_hit_off);
     AHA_CUDA(cudaEventRecord(ev1, st));
+    AHA_HSTAMP("launched");
     AHA_CUDA(cudaMemcpyAsync(&total_hits, fp.total_hits, sizeof(total_hits), cudaMemcpyDeviceToHost, st));
     AHA_CUDA(cudaStreamSynchronize(st));
+#ifdef AHA_B200_PHASES
+    {
+      unsigned long long ph[8];
+      cudaMemcpy(ph, counters + 4, sizeof(ph), cudaMemcpyDeviceToHost);
+      unsigned int nd = 0;
+      cudaMemcpy(&nd, counters + 1, 4, cudaMemcpyDeviceToHost);
+      fprintf(stderr, "[phases] tiles=%lld direct=%u  mega-cycles: stage_wait=%.1f prep=%.1f walk=%.1f count=%.1f next=%.1f deliver=%.1f direct=%.1f\n",
+              (long long)fp.n_tiles, nd, ph[0] / 1e6, ph[1] / 1e6, ph[2] / 1e6, ph[3] / 1e6, ph[4] / 1e6, ph[5] / 1e6, ph[6] / 1e6);
+    }
+#endif
     const double dens = p.total > 0 ? (double)total_hits / (double)p.total : 0.0;
     if (dens > dfa->hits_per_byte) dfa->hits_per_byte = dens;
     if (counting) {

@@ -46,7 +46,8 @@ struct CharTableHost {
   std::vector<uint32_t> root;      // [n_root]
   std::vector<uint16_t> check;     // [m_pad = m + n_cid + 1 rounded up]: unused / padding = 0xFFFF, so base + cid never needs a bound test
   std::vector<uint32_t> val;       // [m]
-  std::vector<uint32_t> multi_bits; // bit ref: ref_rec[ref].n > 1 (shared memory; lets the walk count hits without touching ref_rec)
+  std::vector<uint32_t> multi_bits; // 2 bits per ref: ref_rec[ref].n when it is 1..3, 0 = look it up (shared memory: the walk
+                                    // counts hits without touching ref_rec)
   std::vector<RefRec> ref_rec;     // [m + n_cid + 1] what fires at edge slot / at the one-character state of cid (global)
   std::vector<uint16_t> gfail;     // [m] effective fail of the state whose id is the index (global)
   uint32_t n_cid = 0, n_edges = 0, n_states = 0;
@@ -91,9 +92,9 @@ inline CharTableHost pack_rows(CharTableHost T, const DfaView& v, const std::vec
   const size_t root_bytes = (size_t)T.n_root * 4;
   if (smem_budget < root_bytes + 256 + 64) { T.why = "shared memory budget too small"; return T; }
   // check[] is padded by n_cid + 1 entries; plus the multi bitmap (1 bit per edge slot and per character)
-  const size_t pad_bytes = ((size_t)T.n_cid + 1 + 16) * 2 + ((size_t)T.n_cid + 64) / 8 + 8;
+  const size_t pad_bytes = ((size_t)T.n_cid + 1 + 16) * 2 + ((size_t)T.n_cid + 64) / 4 + 8;
   if (smem_budget < root_bytes + 256 + pad_bytes + 64) { T.why = "shared memory budget too small"; return T; }
-  size_t m_max = (smem_budget - root_bytes - 256 - pad_bytes) * 8 / 49;  // 6 bytes + 1 bit per slot
+  size_t m_max = (smem_budget - root_bytes - 256 - pad_bytes) * 4 / 25;  // 6 bytes + 2 bits per slot
   if (m_max > 0x7FF0) m_max = 0x7FF0;
   std::vector<uint8_t> used(m_max + 1, 0), base_used(m_max + 1, 0);
   used[0] = 1;
@@ -169,9 +170,9 @@ inline CharTableHost pack_rows(CharTableHost T, const DfaView& v, const std::vec
     const uint32_t f = eff[v.fail[r.st]];
     T.gfail[id_of[r.st]] = (uint16_t)(f ? id_of[f] : 0);
   }
-  T.multi_bits.assign((T.ref_rec.size() + 31) / 32, 0u);
+  T.multi_bits.assign((T.ref_rec.size() + 15) / 16, 0u);
   for (size_t i = 0; i < T.ref_rec.size(); ++i)
-    if (T.ref_rec[i].n > 1) T.multi_bits[i >> 5] |= 1u << (i & 31);
+    if (T.ref_rec[i].n >= 1 && T.ref_rec[i].n <= 3) T.multi_bits[i >> 4] |= T.ref_rec[i].n << ((i & 15) * 2);
   T.ok = true;
   return T;
 }

@@ -32,8 +32,8 @@ struct CharDeviceTables {
   const RefRec* ref_rec;    // stays in global memory
   uint32_t n_root, m;
   uint32_t m_pad;           // entries of check[] (m + n_cid + 1, padding = 0xFFFF)
-  uint32_t n_mwords;        // words of the multi bitmap
-  const uint32_t* mbits_g;  // bit ref: more than one key fires there
+  uint32_t n_mwords;        // words of the hit-count table
+  const uint32_t* mbits_g;  // 2 bits per ref: keys that fire there (1..3), 0 = see ref_rec
   uint32_t lo[3], n[3], off[3];
 };
 
@@ -124,6 +124,16 @@ __device__ __forceinline__ uint32_t lds_u16(uint32_t addr) {
   asm("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
   return v;
 }
+// makes a value opaque to the compiler: it stays in a register instead of being recomputed at every use
+__device__ __forceinline__ uint32_t pin_u32(uint32_t x) {
+  asm volatile("" : "+r"(x));
+  return x;
+}
+template <class T>
+__device__ __forceinline__ T* pin_ptr(T* p) {
+  asm volatile("" : "+l"(p));
+  return p;
+}
 struct SmemU32 {
   uint32_t base;
   __device__ __forceinline__ uint32_t operator[](uint32_t i) const { return lds_u32(base + i * 4u); }
@@ -138,7 +148,7 @@ struct CharSmem {
   SmemU32 val;             // [m]
   SmemU16 check;           // [m_pad]
   const uint16_t* gfail;   // global
-  SmemU32 mbits;           // [n_mwords] bit ref: ref_rec[ref].n > 1
+  SmemU32 mbits;           // [n_mwords] 2 bits per ref: ref_rec[ref].n if 1..3, else 0
   uint32_t m;
   uint32_t lo2, n2, off2, lo3, n3, off3, lo4, n4, off4;  // root index ranges of 2-, 3-, 4-byte units
   uint32_t neg_lo3_64;     // -(lo3 / 64): lo is a multiple of 64 (char_table.hpp)
@@ -229,23 +239,24 @@ template <bool kChars, class OnDoc>
 __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanParams& p, const uint8_t* sbuf, int64_t origin, int64_t a,
                                                int64_t b, int32_t sub, int32_t stage_end, int32_t warmc, bool one_doc, int64_t cd,
                                                int64_t cdoc_start, int64_t cdoc_end, const uint32_t (&lead0)[kChains], CharEvent* my_ev,
-                                               uint32_t (&n_ev)[kChains], uint32_t& multi_mask_out, OnDoc on_doc) {
+                                               uint32_t (&n_ev)[kChains], uint32_t (&n_hit)[kChains], bool& lookup_out, OnDoc on_doc) {
   constexpr unsigned kFull = 0xffffffffu;
   bool ok = true;
-  uint32_t multi_mask = 0;
+  bool lookup = false;  // an event reports more than 3 keys: n_hit is a lower bound, the caller counts through ref_rec
   // per sub-chunk state (all offsets relative to sbuf)
   int32_t rb[kChains], a_seg[kChains], pos[kChains], de[kChains], seg_end[kChains], ebase[kChains];
   uint32_t s[kChains], f1[kChains], k[kChains], lead[kChains];
   bool deep[kChains], done[kChains];
-  int64_t d[kChains], doc_start[kChains], doc_end[kChains], bb[kChains];
+  // (the document index and its 64-bit bounds are not carried: the boundary code below re-derives them from
+  // ebase / de, which keeps 16 registers out of the hot loop)
 
-  auto enter_segment = [&](int c) {
-    de[c] = (int32_t)min(doc_end[c] - origin, (int64_t)1 << 30);
+  auto enter_segment = [&](int c, int64_t doc_start, int64_t doc_end) {
+    de[c] = (int32_t)min(doc_end - origin, (int64_t)1 << 30);
     seg_end[c] = min(rb[c], de[c]);
-    ebase[c] = (int32_t)(origin - doc_start[c]) + 1;
+    ebase[c] = (int32_t)(origin - doc_start) + 1;
     int64_t w = origin + a_seg[c] - warmc;
-    const bool at_start = w < doc_start[c] || origin + a_seg[c] == doc_start[c];
-    if (at_start) w = doc_start[c];
+    const bool at_start = w < doc_start || origin + a_seg[c] == doc_start;
+    if (at_start) w = doc_start;
     pos[c] = (int32_t)(w - origin);
     s[c] = 0; f1[c] = 0; k[c] = 0; deep[c] = false;
     if (!at_start) {  // the warm-up may begin inside a unit
@@ -259,24 +270,25 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
 #pragma unroll
   for (int c = 0; c < kChains; ++c) {
     const int64_t ac = min(a + (int64_t)c * sub, b);
-    bb[c] = c == kChains - 1 ? b : min(ac + sub, b);
-    rb[c] = (int32_t)(bb[c] - origin);
+    const int64_t bc = c == kChains - 1 ? b : min(ac + sub, b);
+    rb[c] = (int32_t)(bc - origin);
     a_seg[c] = (int32_t)(ac - origin);
-    done[c] = ac >= bb[c];
+    done[c] = ac >= bc;
     n_ev[c] = 0;
+    n_hit[c] = 0;
     lead[c] = lead0[c];
-    d[c] = cd; doc_start[c] = cdoc_start; doc_end[c] = cdoc_end;
     pos[c] = rb[c]; de[c] = 0; seg_end[c] = 0; ebase[c] = 0; s[c] = 0; f1[c] = 0; k[c] = 0; deep[c] = false;
     if (!done[c]) {
+      int64_t d = cd, doc_start = cdoc_start, doc_end = cdoc_end;
       if (!one_doc) {
-        d[c] = last_le(p.doc_off, p.n_docs, ac);
-        doc_start[c] = p.doc_off[d[c]];
-        doc_end[c] = p.doc_off[d[c] + 1];
+        d = last_le(p.doc_off, p.n_docs, ac);
+        doc_start = p.doc_off[d];
+        doc_end = p.doc_off[d + 1];
       }
-      if (doc_start[c] == ac) {
-        for (int64_t e = first_ge(p.doc_off, p.n_docs, ac); e <= d[c]; ++e) on_doc(c, e, 0u);
+      if (doc_start == ac) {
+        for (int64_t e = first_ge(p.doc_off, p.n_docs, ac); e <= d; ++e) on_doc(c, e, 0u);
       }
-      enter_segment(c);
+      enter_segment(c, doc_start, doc_end);
     }
   }
 
@@ -291,7 +303,9 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
     const bool fire = (v & 0x8000u) && (uint32_t)(last - a_seg[c]) < (uint32_t)(rb[c] - a_seg[c]);
     if (fire) {
       my_ev[c * kEvSlotsC + n_ev[c]] = CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : last + ebase[c], ref};
-      multi_mask |= ((S.mbits[ref >> 5] >> (ref & 31u)) & 1u) << ((c * kEvCapC + n_ev[c]) & 31u);  // garbage beyond kEvCapC: direct pass
+      const uint32_t cnt = (S.mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
+      n_hit[c] += cnt;
+      lookup = lookup || cnt == 0u;
       ++n_ev[c];
     }
   };
@@ -331,7 +345,9 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
         if (fire[c]) {
           const uint32_t ref = q[c].hit ? q[c].slotv : S.m + q[c].cid;
           my_ev[c * kEvSlotsC + n_ev[c]] = CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : cs[c] + len - 1 + ebase[c], ref};
-          multi_mask |= ((S.mbits[ref >> 5] >> (ref & 31u)) & 1u) << ((c * kEvCapC + n_ev[c]) & 31u);
+          const uint32_t cnt = (S.mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
+          n_hit[c] += cnt;
+          lookup = lookup || cnt == 0u;
           ++n_ev[c];
         }
       }
@@ -368,15 +384,18 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
         const uint32_t rel = h * 64u + (wm >> 16);
         return rel < S.n3 ? S.root3[rel] : 0u;
       };
+      // rolled on purpose: A:B:C is a 96-bit shift register, one copy of the step keeps the loop in the instruction cache
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         uint32_t r[kChains];
         int32_t cs[kChains];
 #pragma unroll
         for (int c = 0; c < kChains; ++c) {
-          const uint32_t w = u == 0 ? A[c] : (u == 1 ? __byte_perm(A[c], B[c], 0x0543) : (u == 2 ? __byte_perm(B[c], C[c], 0x0432) : C[c] >> 8));
-          r[c] = root3(w);
+          r[c] = root3(A[c]);
           cs[c] = pos[c] + 3 * u;
+          A[c] = __funnelshift_r(A[c], B[c], 24);
+          B[c] = __funnelshift_r(B[c], C[c], 24);
+          C[c] >>= 24;
         }
         multi_step(r, cs, 3);
       }
@@ -385,15 +404,17 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
         if (!done[c]) pos[c] += 12;
     } else if (__all_sync(kFull, can1)) {
       // twelve ASCII characters per sub-chunk
-#pragma unroll
+#pragma unroll 1
       for (int i = 0; i < 12; ++i) {
         uint32_t r[kChains];
         int32_t cs[kChains];
 #pragma unroll
         for (int c = 0; c < kChains; ++c) {
-          const uint32_t w = i < 4 ? A[c] : (i < 8 ? B[c] : C[c]);
-          r[c] = S.root[(w >> ((i & 3) * 8)) & 0xFFu];
+          r[c] = S.root[A[c] & 0xFFu];
           cs[c] = pos[c] + i;
+          A[c] = __funnelshift_r(A[c], B[c], 8);
+          B[c] = __funnelshift_r(B[c], C[c], 8);
+          C[c] >>= 8;
         }
         multi_step(r, cs, 1);
       }
@@ -406,25 +427,24 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
         if (done[c]) continue;
         if (pos[c] >= seg_end[c]) {
           // end of the segment: the region is finished, or the next document starts here
-          const bool more = doc_end[c] <= bb[c] && (doc_end[c] < bb[c] || bb[c] == p.total);
+          const int64_t bc = origin + rb[c];
+          const int64_t at = origin + de[c];  // end of the current document (a clamped de only ever makes it larger than bc)
+          const bool more = at <= bc && (at < bc || bc == p.total);
           if (!more) {
             done[c] = true;
           } else {
-            const int64_t at = doc_end[c];
-            ++d[c];
-            while (d[c] < p.n_docs) {
-              on_doc(c, d[c], n_ev[c]);
-              if (p.doc_off[d[c] + 1] > at) break;
-              ++d[c];
+            int64_t d = last_le(p.doc_off, p.n_docs, at - 1) + 1;  // the current document is not empty
+            while (d < p.n_docs) {
+              on_doc(c, d, n_ev[c]);
+              if (p.doc_off[d + 1] > at) break;
+              ++d;
             }
-            if (d[c] >= p.n_docs || at >= bb[c]) {
+            if (d >= p.n_docs || at >= bc) {
               done[c] = true;
             } else {
-              doc_start[c] = p.doc_off[d[c]];
-              doc_end[c] = p.doc_off[d[c] + 1];
-              a_seg[c] = (int32_t)(doc_start[c] - origin);
+              a_seg[c] = (int32_t)(p.doc_off[d] - origin);
               lead[c] = 0;
-              enter_segment(c);
+              enter_segment(c, p.doc_off[d], p.doc_off[d + 1]);
             }
           }
         } else {
@@ -470,7 +490,7 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
       }
     }
   }
-  multi_mask_out = multi_mask;
+  lookup_out = lookup;
   return true;
 }
 
@@ -485,27 +505,13 @@ struct WalkedTile {
   uint32_t hits0;       // hits of this lane's sub-chunk 0 (base of sub-chunk 1)
   uint32_t n_ev0, n_ev1;
   uint32_t n_mark0, n_mark1;
-  uint32_t multi_mask;
 };
 
-__device__ __forceinline__ void deliver_events(const CharParams& P, unsigned long long prefix, const WalkedTile& w,
+__device__ __noinline__ void deliver_events(const CharParams& P, unsigned int t, uint32_t Ttile, const WalkedTile w,
                                                const CharEvent* warp_ev, const int2* my_mark, int lane) {
   const ScanParams& p = P.f.sp;
   const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
   const CharEvent* my_ev = warp_ev + lane * kEvSlots;
-#pragma unroll
-  for (int c = 0; c < kChains; ++c) {
-    const uint32_t n_mark = c ? w.n_mark1 : w.n_mark0;
-    const uint32_t cmask = (w.multi_mask >> (c * kEvCapC)) & ((1u << kEvCapC) - 1u);
-    for (uint32_t k = 0; k < n_mark; ++k) {
-      const int2 mk = my_mark[c * kMarkCapC + k];
-      const int y = mk.y;  // events of this sub-chunk before the document start
-      uint32_t before = (uint32_t)y;
-      for (uint32_t mm = cmask & ((1u << y) - 1u); mm; mm &= mm - 1)
-        before += P.t.ref_rec[my_ev[c * kEvSlotsC + __ffs(mm) - 1].ref].n - 1u;
-      p.doc_hit_off[mk.x] = (int64_t)(prefix + w.excl_lane + (c ? w.hits0 : 0u) + before);
-    }
-  }
   const uint32_t n_ev = w.n_ev0 + w.n_ev1;
   uint32_t ev_incl = n_ev;
   for (int o = 1; o < 32; o <<= 1) {
@@ -514,12 +520,8 @@ __device__ __forceinline__ void deliver_events(const CharParams& P, unsigned lon
   }
   const uint32_t ev_excl = ev_incl - n_ev;
   const uint32_t E = __shfl_sync(0xffffffffu, ev_incl, 31);
-  if (!p.hits || E == 0) return;
-  uint32_t run = 0;
-  for (uint32_t base = 0; base < E; base += 32 * kDeliverRounds) {
-    CharEvent ev[kDeliverRounds];
-    RefRec rr[kDeliverRounds];
-    // phase 1: which event does this lane expand in each round; fetch it
+  // which event does this lane expand in round r of a batch; fetch it and what fires there
+  auto fetch = [&](uint32_t base, CharEvent (&ev)[kDeliverRounds], RefRec (&rr)[kDeliverRounds]) {
 #pragma unroll
     for (int r = 0; r < kDeliverRounds; ++r) {
       const uint32_t i = base + r * 32 + lane;
@@ -540,13 +542,33 @@ __device__ __forceinline__ void deliver_events(const CharParams& P, unsigned lon
         }
       }
     }
-    // phase 2: what fires there
 #pragma unroll
     for (int r = 0; r < kDeliverRounds; ++r) {
       rr[r] = RefRec{0, 0, 0, 0};
       if (base + r * 32 + lane < E) rr[r] = P.t.ref_rec[ev[r].ref];
     }
-    // phase 3: positions and stores
+  };
+  CharEvent ev[kDeliverRounds];
+  RefRec rr[kDeliverRounds];
+  const bool want = p.hits != nullptr && E > 0;
+  if (want) fetch(0, ev, rr);  // in flight while the look-back runs
+  const unsigned long long prefix = resolve_prefix(P.f, t, lane);
+  if ((int64_t)t == P.f.n_tiles - 1 && lane == 0) *P.f.total_hits = prefix + Ttile;
+#pragma unroll
+  for (int c = 0; c < kChains; ++c) {
+    const uint32_t n_mark = c ? w.n_mark1 : w.n_mark0;
+    for (uint32_t k = 0; k < n_mark; ++k) {
+      const int2 mk = my_mark[c * kMarkCapC + k];
+      const int y = mk.y;  // events of this sub-chunk before the document start
+      uint32_t before = 0;
+      for (int i = 0; i < y; ++i) before += P.t.ref_rec[my_ev[c * kEvSlotsC + i].ref].n;
+      p.doc_hit_off[mk.x] = (int64_t)(prefix + w.excl_lane + (c ? w.hits0 : 0u) + before);
+    }
+  }
+  if (!want) return;
+  uint32_t run = 0;
+  for (uint32_t base = 0; base < E; base += 32 * kDeliverRounds) {
+    if (base != 0) fetch(base, ev, rr);
 #pragma unroll
     for (int r = 0; r < kDeliverRounds; ++r) {
       if (base + r * 32 < E) {  // warp-uniform
@@ -563,7 +585,7 @@ __device__ __forceinline__ void deliver_events(const CharParams& P, unsigned lon
   }
 }
 
-__global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const CharParams P) {
+__global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const __grid_constant__ CharParams P) {
   extern __shared__ __align__(128) uint8_t smem[];
   const FusedParams& F = P.f;
   const ScanParams& p = F.sp;
@@ -592,8 +614,8 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
 #pragma unroll
   for (int c = 0; c < 3; ++c) { T.lo[c] = P.t.lo[c]; T.n[c] = P.t.n[c]; T.off[c] = P.t.off[c]; }
   CharSmem S;        // fast walk
-  S.root.base = smem_u32(s_root); S.root3.base = smem_u32(s_root + P.t.off[1]); S.val.base = smem_u32(s_val);
-  S.check.base = smem_u32(s_check); S.gfail = P.t.gfail; S.mbits.base = smem_u32(s_mbits);
+  S.root.base = pin_u32(smem_u32(s_root)); S.root3.base = pin_u32(smem_u32(s_root + P.t.off[1])); S.val.base = pin_u32(smem_u32(s_val));
+  S.check.base = pin_u32(smem_u32(s_check)); S.gfail = P.t.gfail; S.mbits.base = pin_u32(smem_u32(s_mbits));
   S.m = P.t.m;
   S.lo2 = P.t.lo[0]; S.n2 = P.t.n[0]; S.off2 = P.t.off[0];
   S.lo3 = P.t.lo[1]; S.n3 = P.t.n[1]; S.off3 = P.t.off[1];
@@ -614,21 +636,48 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
   unsigned int pend_t = 0;
   uint32_t pend_T = 0;
   int pend_buf = 0;
-  WalkedTile pw = {0, 0, 0, 0, 0, 0, 0};
+  WalkedTile pw = {0, 0, 0, 0, 0, 0};
   // document that contained the previous tile (tiles come in increasing order)
   int64_t cd = 0, cdoc_start = 0, cdoc_end = -1;
 
+  // takes the next ticket and starts staging its text: one TMA bulk copy (16-byte granules) plus a byte tail.
+  // Called as soon as the previous tile no longer needs the buffer, so the copy overlaps that tile's delivery.
+  unsigned int ticket_ahead = 0;  // lane 0: a ticket requested one tile early, so the atomic's latency is never waited for
+  if (lane == 0) ticket_ahead = atomicAdd(F.ticket, 1u);
+  auto next_tile = [&]() -> unsigned int {
+    unsigned int nt = __shfl_sync(0xffffffffu, ticket_ahead, 0);
+    if (lane == 0 && (int64_t)nt < F.n_tiles) ticket_ahead = atomicAdd(F.ticket, 1u);
+    if ((int64_t)nt < F.n_tiles) {
+      const int64_t tile_start = (int64_t)nt * F.tile;
+      const int64_t tile_end = min(tile_start + (int64_t)F.tile, p.total);
+      const int64_t org = max((int64_t)0, tile_start - (int64_t)F.w16);
+      const int64_t want_end = min(p.total, tile_end + 16);
+      const int64_t bulk_end = org + ((want_end - org) & ~(int64_t)15);
+      if (lane == 0 && bulk_end > org) {
+        mbar_expect_tx(bar, (uint32_t)(bulk_end - org));
+        bulk_g2s(sbuf, p.text + org, (uint32_t)(bulk_end - org), bar);
+      }
+      for (int64_t i = bulk_end + lane; i < want_end; i += 32) sbuf[i - org] = p.text[i];
+    }
+    return nt;
+  };
+  unsigned int t = next_tile();
+#ifdef AHA_B200_PHASES
+  unsigned long long* phase_cyc = reinterpret_cast<unsigned long long*>(F.ticket + 4);
+  long long ph_t0 = clock64();
+#define AHA_PHASE(i) do { const long long _n = clock64(); if (lane == 0) atomicAdd(&phase_cyc[i], (unsigned long long)(_n - ph_t0)); ph_t0 = _n; } while (0)
+#else
+#define AHA_PHASE(i) do { } while (0)
+#endif
+
   for (;;) {
-    unsigned int t = 0;
-    if (lane == 0) t = atomicAdd(F.ticket, 1u);
-    t = __shfl_sync(0xffffffffu, t, 0);
     const bool have = (int64_t)t < F.n_tiles;
     bool bad = false, over = false;
-    WalkedTile w = {0, 0, 0, 0, 0, 0, 0};
+    WalkedTile w = {0, 0, 0, 0, 0, 0};
     uint32_t Ttile = 0, lead0[kChains] = {0, 0};
     int64_t origin = 0, a = 0, b = 0;
     CharEvent* warp_ev = P.events + ((gwarp * 2 + buf) * 32) * kEvSlots;
-    CharEvent* my_ev = warp_ev + lane * kEvSlots;
+    CharEvent* my_ev = pin_ptr(warp_ev + lane * kEvSlots);
     int2* my_mark = F.marks + ((gwarp * 2 + buf) * 32 + lane) * kMarkCap;
     if (have) {
       const int64_t tile_start = (int64_t)t * F.tile;
@@ -636,12 +685,7 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
       origin = max((int64_t)0, tile_start - (int64_t)F.w16);
       const int64_t want_end = min(p.total, tile_end + 16);
       const int64_t bulk_end = origin + ((want_end - origin) & ~(int64_t)15);
-      if (lane == 0 && bulk_end > origin) {
-        mbar_expect_tx(bar, (uint32_t)(bulk_end - origin));
-        bulk_g2s(sbuf, p.text + origin, (uint32_t)(bulk_end - origin), bar);
-      }
-      for (int64_t i = bulk_end + lane; i < want_end; i += 32) sbuf[i - origin] = p.text[i];
-      // which document is this? (overlaps the copy)
+      // which document is this?
       if (!(tile_start >= cdoc_start && tile_start < cdoc_end)) {
         cd = last_le(p.doc_off, p.n_docs, tile_start);
         cdoc_start = p.doc_off[cd];
@@ -653,11 +697,13 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
         tl = F.tile_lead[t];
         if (one_doc) dlb = p.doc_lead_base[cd];
       }
+      AHA_PHASE(1);
       if (bulk_end > origin) {
         mbar_wait(bar, parity);
         parity ^= 1u;
       }
       __syncwarp();
+      AHA_PHASE(0);
 
       a = min(tile_start + (int64_t)lane * F.chunk, tile_end);
       b = min(a + (int64_t)F.chunk, tile_end);
@@ -675,17 +721,20 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
         if (a1 < b) lead0[1] = (uint32_t)(before_a + mine0 - (one_doc ? dlb : p.doc_lead_base[last_le(p.doc_off, p.n_docs, a1)]));
       }
 
+      AHA_PHASE(1);
       // ---- walk: events to the lane's ring slots, no global loads on the chain
-      uint32_t n_ev[kChains] = {0, 0}, n_mark[kChains] = {0, 0};
+      uint32_t n_ev[kChains] = {0, 0}, n_mark[kChains] = {0, 0}, n_hit[kChains] = {0, 0};
+      bool lookup = false;
       auto on_doc = [&](int c, int64_t d, uint32_t nev) {
         if (n_mark[c] < (uint32_t)kMarkCapC) my_mark[c * kMarkCapC + n_mark[c]] = make_int2((int)d, (int)nev);
         ++n_mark[c];
       };
       const int32_t stage_end = (int32_t)(want_end - origin);
       const bool ok = chars ? char_tile_walk<true>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start, cdoc_end, lead0,
-                                                   my_ev, n_ev, w.multi_mask, on_doc)
+                                                   my_ev, n_ev, n_hit, lookup, on_doc)
                             : char_tile_walk<false>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start, cdoc_end, lead0,
-                                                    my_ev, n_ev, w.multi_mask, on_doc);
+                                                    my_ev, n_ev, n_hit, lookup, on_doc);
+      AHA_PHASE(2);
       bad = __any_sync(0xffffffffu, !ok);
       over = __any_sync(0xffffffffu, n_ev[0] > (uint32_t)kEvCapC || n_ev[1] > (uint32_t)kEvCapC || n_mark[0] > (uint32_t)kMarkCapC ||
                                          n_mark[1] > (uint32_t)kMarkCapC);
@@ -703,14 +752,15 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
         char_lane_walk(P, T, sbuf, origin, a, b, lead0[0], [&](int32_t, uint32_t ref) { c += P.t.ref_rec[ref].n; }, [&](int64_t) {});
         n_hits = c;
       } else {
-        uint32_t extra[kChains] = {0, 0};
+        if (lookup) {  // some output list is longer than the 2-bit table can say
 #pragma unroll
-        for (int c = 0; c < kChains; ++c) {
-          for (uint32_t mm = (w.multi_mask >> (c * kEvCapC)) & ((1u << kEvCapC) - 1u); mm; mm &= mm - 1)
-            extra[c] += P.t.ref_rec[my_ev[c * kEvSlotsC + __ffs(mm) - 1].ref].n - 1u;
+          for (int c = 0; c < kChains; ++c) {
+            n_hit[c] = 0;
+            for (uint32_t i = 0; i < n_ev[c]; ++i) n_hit[c] += P.t.ref_rec[my_ev[c * kEvSlotsC + i].ref].n;
+          }
         }
-        w.hits0 = n_ev[0] + extra[0];
-        n_hits = w.hits0 + n_ev[1] + extra[1];
+        w.hits0 = n_hit[0];
+        n_hits = n_hit[0] + n_hit[1];
       }
       uint32_t incl = n_hits;
       for (int o = 1; o < 32; o <<= 1) {
@@ -720,21 +770,17 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
       w.excl_lane = incl - n_hits;
       Ttile = __shfl_sync(0xffffffffu, incl, 31);
       publish_aggregate(F, t, Ttile, lane);
+      AHA_PHASE(3);
     }
 
-    // ---- deliver the previous tile: its predecessors have had a whole walk of time to publish
-    if (pend) {
-      const unsigned long long prefix = resolve_prefix(F, pend_t, lane);
-      if ((int64_t)pend_t == F.n_tiles - 1 && lane == 0) *F.total_hits = prefix + pend_T;
-      const CharEvent* pev = P.events + ((gwarp * 2 + pend_buf) * 32) * kEvSlots;
-      const int2* pmark = F.marks + ((gwarp * 2 + pend_buf) * 32 + lane) * kMarkCap;
-      deliver_events(P, prefix, pw, pev, pmark, lane);
-      pend = false;
-    }
-    if (!have) break;
-
-    if (bad || over) {
-      // needs the staged text again: resolved and delivered right away
+    if (have && (bad || over)) {
+      // needs the staged text again: the previous tile goes out first, then this one, resolved right away
+      if (pend) {
+        const CharEvent* pev = P.events + ((gwarp * 2 + pend_buf) * 32) * kEvSlots;
+        const int2* pmark = F.marks + ((gwarp * 2 + pend_buf) * 32 + lane) * kMarkCap;
+        deliver_events(P, pend_t, pend_T, pw, pev, pmark, lane);
+        pend = false;
+      }
       const unsigned long long prefix = resolve_prefix(F, t, lane);
       if ((int64_t)t == F.n_tiles - 1 && lane == 0) *F.total_hits = prefix + Ttile;
       if (lane == 0) atomicAdd(F.n_direct, 1u);
@@ -753,14 +799,32 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const Ch
             },
             [&](int64_t d) { p.doc_hit_off[d] = idx; });
       }
-    } else {
+    }
+    AHA_PHASE(6);
+    // the text buffer is free: take the next ticket and start its copy before the (latency-bound) delivery
+    unsigned int t_next = t;
+    if (have) {
+      __syncwarp();
+      fence_proxy_async();  // reads of sbuf are done before the next bulk copy overwrites it
+      t_next = next_tile();
+    }
+    AHA_PHASE(4);
+    // ---- deliver the previous tile: its predecessors have had a whole walk of time to publish
+    if (pend) {
+      const CharEvent* pev = P.events + ((gwarp * 2 + pend_buf) * 32) * kEvSlots;
+      const int2* pmark = F.marks + ((gwarp * 2 + pend_buf) * 32 + lane) * kMarkCap;
+      deliver_events(P, pend_t, pend_T, pw, pev, pmark, lane);
+      pend = false;
+    }
+    AHA_PHASE(5);
+    if (!have) break;
+    if (!(bad || over)) {
       pend = true;
       pend_t = t; pend_T = Ttile; pend_buf = buf;
       pw = w;
       buf ^= 1;
     }
-    __syncwarp();
-    fence_proxy_async();  // reads of sbuf are done before the next bulk copy overwrites it
+    t = t_next;
   }
 }
 

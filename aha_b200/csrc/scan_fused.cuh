@@ -35,9 +35,7 @@ struct FusedParams {
   int64_t n_tiles;
   unsigned long long* tile_state;  // [n_tiles] (hits of the tile << 2) | 1 once the tile has been walked
   // groups of 32 consecutive tiles (two-level look-back: 32 tiles, then 32 groups = 1024 tiles per step)
-  unsigned long long* group_acc;   // [n_groups] (tiles arrived << 40) | hits so far   (atomicAdd)
-  unsigned long long* group_agg;   // [n_groups] (hits of the group << 2) | 1, written by the last tile to arrive
-  unsigned long long* group_excl;  // [n_groups] (hits before the group << 2) | 2, written by every tile that resolves
+  unsigned long long* group_excl;  // [n_groups] (hits before the group << 2) | 2, written by the first tile of the group that resolves
   unsigned int* ticket;
   unsigned long long* total_hits;  // out: total number of hits
   int64_t hit_cap;                 // capacity of sp.hits (records); writes beyond are dropped
@@ -184,31 +182,29 @@ struct ByteGlobal {
 // part inside this tile is counted here; the caller adds the per-tile prefix.
 __device__ __forceinline__ uint32_t count_leads_smem(const uint8_t* sbuf, int64_t buf_origin, int64_t from, int64_t to) {
   uint32_t c = 0;
-  for (int64_t i = from; i < to; ++i) c += ((sbuf[i - buf_origin] & 0xC0) != 0x80);
+  int32_t i = (int32_t)(from - buf_origin);
+  const int32_t e = (int32_t)(to - buf_origin);
+  for (; i < e && (i & 3); ++i) c += ((sbuf[i] & 0xC0) != 0x80);
+  for (; i + 4 <= e; i += 4) {  // a continuation byte is 10xxxxxx
+    const uint32_t w = *reinterpret_cast<const uint32_t*>(sbuf + i);
+    c += 4u - (uint32_t)__popc(w & 0x80808080u & ~(w << 1));
+  }
+  for (; i < e; ++i) c += ((sbuf[i] & 0xC0) != 0x80);
   return c;
 }
 
 // ---- two-level decoupled look-back -------------------------------------------------------------------
 // A tile needs the number of hits in all earlier tiles.  Tickets are handed out in order, so every earlier
 // tile is already running on some warp and publishes its count without waiting for anybody.
-// publish_aggregate: called once per tile right after its walk (never blocks).
+// publish_aggregate: called once per tile right after its walk: one store, nothing to wait for.
 __device__ __forceinline__ void publish_aggregate(const FusedParams& P, unsigned int t, uint32_t T, int lane) {
-  if (lane != 0) return;
-  st_relaxed_u64(&P.tile_state[t], ((unsigned long long)T << 2) | 1ull);
-  const unsigned int g = t >> 5;
-  const long long left = P.n_tiles - ((long long)g << 5);
-  const unsigned long long size = left < 32 ? (unsigned long long)left : 32ull;
-  const unsigned long long old = atomicAdd(&P.group_acc[g], (1ull << 40) + (unsigned long long)T);
-  if ((old >> 40) + 1ull == size) {
-    const unsigned long long total = (old & ((1ull << 40) - 1ull)) + (unsigned long long)T;
-    st_relaxed_u64(&P.group_agg[g], (total << 2) | 1ull);
-  }
+  if (lane == 0) st_relaxed_u64(&P.tile_state[t], ((unsigned long long)T << 2) | 1ull);
 }
 // resolve_prefix: hits in all tiles before t.  Whole warp; waits (with back-off) only for earlier tiles that
 // have not finished their WALK yet (never for another warp's delivery).  The caller normally defers this call
 // by one tile so that it does not wait at all.  The group's exclusive prefix is computed by the first tile of the
-// group that gets here and published for the other 31 (all warps polling the same few group lines would
-// serialise in L2).
+// group that gets here (summing whole groups of 32 tile counts backwards until a published prefix is met) and
+// published for the other 31: all warps polling the same few lines would serialise in L2.
 __device__ __forceinline__ unsigned long long resolve_prefix(const FusedParams& P, unsigned int t, int lane) {
   const unsigned int g = t >> 5, j = t & 31u;
   // tiles of the same group in front of t (lanes < j); lane 31 peeks at the group's exclusive prefix
@@ -223,30 +219,23 @@ __device__ __forceinline__ unsigned long long resolve_prefix(const FusedParams& 
   for (int o = 16; o > 0; o >>= 1) in_group += __shfl_xor_sync(0xffffffffu, in_group, o);
   const unsigned long long e31 = __shfl_sync(0xffffffffu, v, 31);
   if ((e31 & 3ull) == 2ull) return (e31 >> 2) + in_group;
-  // groups in front of g, 32 per step, stopping at the first one whose exclusive prefix is known
   unsigned long long G = 0;
-  long long h = (long long)g - 1;
-  while (h >= 0) {
-    const long long idx = h - lane;
-    unsigned long long e = 2ull, a = 1ull;  // virtual group before group 0: prefix 0, 0 hits
-    if (idx >= 0) {
-      e = ld_relaxed_u64(&P.group_excl[idx]);
-      a = ld_relaxed_u64(&P.group_agg[idx]);
-    }
-    const bool have_a = (a & 3ull) == 1ull;
-    const unsigned m_incl = __ballot_sync(0xffffffffu, have_a && (e & 3ull) == 2ull);
-    const unsigned m_wait = __ballot_sync(0xffffffffu, !have_a);
-    const int first = m_incl ? (__ffs(m_incl) - 1) : 32;
-    const unsigned need = first >= 31 ? 0xffffffffu : ((2u << first) - 1u);
-    if (m_wait & need) {
+  for (long long h = (long long)g - 1; h >= 0; --h) {
+    unsigned long long e, a;
+    for (;;) {
+      a = ld_relaxed_u64(&P.tile_state[((size_t)h << 5) + lane]);  // groups in front of g are complete groups
+      e = ld_relaxed_u64(&P.group_excl[h]);
+      if (__all_sync(0xffffffffu, (a & 3ull) != 0ull)) break;
       __nanosleep(64);
-      continue;
     }
-    unsigned long long part = lane < first ? (a >> 2) : (lane == first ? (a >> 2) + (e >> 2) : 0ull);
+    unsigned long long part = a >> 2;
     for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
     G += part;
-    if (first < 32) break;
-    h -= 32;
+    e = __shfl_sync(0xffffffffu, e, 0);
+    if ((e & 3ull) == 2ull) {
+      G += e >> 2;
+      break;
+    }
   }
   if (lane == 0) st_relaxed_u64(&P.group_excl[g], (G << 2) | 2ull);
   return G + in_group;

@@ -53,8 +53,9 @@ struct HitsOwner {
   cudaStream_t stream = nullptr;
   void* dev_hits = nullptr;
   void* dev_doc_hit_off = nullptr;
-  void* host_hits = nullptr;         // pinned
+  void* host_hits = nullptr;         // pinned (recycled through PinnedPool)
   void* host_doc_hit_off = nullptr;  // pinned
+  size_t host_hits_bytes = 0, host_doc_hit_off_bytes = 0;
   void* dev_text = nullptr;          // owned copy made by aha_b200_scan
   void* dev_doc_off = nullptr;
 };

@@ -140,7 +140,9 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
   AHA_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
   FusedParams fp;
   memset(&fp, 0, sizeof(fp));
-  fused_geometry(p.warm + 1, &fp.chunk, &fp.w16, &fp.buf_bytes);
+  // character automaton in shared memory when the dictionary allows it (plain match, with or without char units)
+  const bool use_char = dd->hot.ok && !(p.mode & AHA_SEP);
+  fused_geometry(p.warm + 1, use_char, &fp.chunk, &fp.w16, &fp.buf_bytes);
   fp.tile = 32 * fp.chunk;
   fp.n_tiles = (p.total + fp.tile - 1) / fp.tile;
   const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
@@ -154,8 +156,6 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
   const size_t state_words = (size_t)(fp.n_tiles + 1) + (size_t)(n_groups + 1);
   AHA_CUDA(cudaMallocAsync(&tile_state, state_words * sizeof(unsigned long long), st));
   AHA_CUDA(cudaMallocAsync(&counters, 16 + 8 * 8, st));  // + 8 phase-cycle counters (AHA_B200_PHASES)
-  // character automaton in shared memory when the dictionary allows it (plain match, with or without char units)
-  const bool use_char = dd->hot.ok && !(p.mode & AHA_SEP);
   CharParams cp;
   memset(&cp, 0, sizeof(cp));
   if (use_char) {
@@ -355,6 +355,57 @@ int32_t aha_b200_scan_device(const aha_dfa* d, const void* dev_text, const void*
   return AHA_OK;
 }
 
+// ---- pinned host buffers: cudaMallocHost costs ~100 ms per GB, so result buffers are recycled --------------
+namespace aha {
+struct PinnedPool {
+  std::mutex mu;
+  std::vector<std::pair<void*, size_t>> free_list;
+  size_t cached = 0;
+  static constexpr size_t kMaxCached = (size_t)16 << 30;
+  void* acquire(size_t bytes, size_t* got) {
+    bytes = (bytes + 4095) & ~size_t(4095);
+    {
+      std::lock_guard<std::mutex> lk(mu);
+      size_t best = free_list.size();
+      for (size_t i = 0; i < free_list.size(); ++i)
+        if (free_list[i].second >= bytes && (best == free_list.size() || free_list[i].second < free_list[best].second)) best = i;
+      if (best != free_list.size() && free_list[best].second <= 2 * bytes + (1 << 20)) {
+        void* p = free_list[best].first;
+        *got = free_list[best].second;
+        cached -= *got;
+        free_list.erase(free_list.begin() + best);
+        return p;
+      }
+    }
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes) != cudaSuccess) return nullptr;
+    *got = bytes;
+    return p;
+  }
+  void release(void* p, size_t bytes) {
+    if (!p) return;
+    std::lock_guard<std::mutex> lk(mu);
+    if (cached + bytes > kMaxCached) {
+      cudaFreeHost(p);
+      return;
+    }
+    free_list.push_back({p, bytes});
+    cached += bytes;
+  }
+};
+static PinnedPool g_pinned;
+
+// bytes per pipeline stage of aha_b200_scan (documents are never split)
+static int64_t e2e_chunk_bytes() {
+  const char* e = getenv("AHA_B200_E2E_CHUNK_MB");
+  const int64_t mb = e ? atoll(e) : 64;
+  return (mb > 0 ? mb : 64) << 20;
+}
+}  // namespace aha
+
+// Host buffers in, host buffers out.  The batch is cut into runs of whole documents of ~64 MB; the H2D copy of
+// run k+1 and the D2H copy of the hits of run k-1 overlap the scan of run k (three streams), so that on a
+// PCIe-attached GPU the call is bound by the slower of the two copy directions, not by their sum.
 int32_t aha_b200_scan(const aha_dfa* d, const uint8_t* text, const int64_t* doc_off, int64_t n_docs, uint32_t mode,
                       const uint8_t* sep_bits, int32_t sep_size, aha_hits** out) {
   if (!d || !out || n_docs < 0 || !doc_off || (!text && n_docs > 0 && doc_off[n_docs] > 0))
@@ -373,36 +424,166 @@ int32_t aha_b200_scan(const aha_dfa* d, const uint8_t* text, const int64_t* doc_
   HitsOwner* own = new HitsOwner();
   res->opaque = own;
   res->n_docs = n_docs;
+  const bool count_only = (mode & AHA_COUNT_ONLY) != 0;
+
+  // runs of whole documents
+  std::vector<int64_t> cut(1, 0);
+  {
+    const int64_t target = e2e_chunk_bytes();
+    int64_t start = 0;
+    for (int64_t i = 0; i < n_docs; ++i) {
+      if (doc_off[i + 1] - doc_off[start] >= target) {
+        cut.push_back(i + 1);
+        start = i + 1;
+      }
+    }
+    if (cut.back() != n_docs || cut.size() == 1) cut.push_back(n_docs);
+  }
+  const size_t n_runs = cut.size() - 1;
+  int64_t max_bytes = 16, max_docs = 1;
+  for (size_t k = 0; k < n_runs; ++k) {
+    max_bytes = std::max<int64_t>(max_bytes, doc_off[cut[k + 1]] - doc_off[cut[k]]);
+    max_docs = std::max<int64_t>(max_docs, cut[k + 1] - cut[k]);
+  }
+
+  cudaStream_t s_in = nullptr, s_run = nullptr, s_out = nullptr;
+  cudaEvent_t e_in[2] = {nullptr, nullptr}, e_out = nullptr;
+  uint8_t* d_text[2] = {nullptr, nullptr};
+  int64_t* d_off[2] = {nullptr, nullptr};
+  int64_t* h_off_stage = nullptr;  // pinned, rebased doc_off of the runs in flight
+  size_t h_off_stage_bytes = 0;
+  std::vector<void*> late_free;    // device hit blocks whose D2H copy may still be running
+  size_t hits_cap = 0, hits_bytes = 0, off_bytes = 0;
+  auto cleanup = [&]() {
+    if (s_out) cudaStreamSynchronize(s_out);
+    if (s_in) cudaStreamSynchronize(s_in);
+    for (void* p : late_free) cudaFree(p);
+    for (int b = 0; b < 2; ++b) {
+      if (d_text[b]) cudaFree(d_text[b]);
+      if (d_off[b]) cudaFree(d_off[b]);
+      if (e_in[b]) cudaEventDestroy(e_in[b]);
+    }
+    if (e_out) cudaEventDestroy(e_out);
+    if (h_off_stage) g_pinned.release(h_off_stage, h_off_stage_bytes);
+    if (s_in) cudaStreamDestroy(s_in);
+    if (s_run) cudaStreamDestroy(s_run);
+    if (s_out) cudaStreamDestroy(s_out);
+  };
   auto fail = [&](int32_t code) {
+    cleanup();
     aha_b200_hits_free(res.release());
     return code;
   };
-  cudaStream_t st = nullptr;  // legacy default stream: the per-call API is synchronous like the reference
-  if (cudaMallocAsync(&own->dev_text, total > 0 ? total : 16, st) != cudaSuccess ||
-      cudaMallocAsync(&own->dev_doc_off, (n_docs + 1) * sizeof(int64_t), st) != cudaSuccess)
-    return fail(set_err(AHA_ERR_NOMEM, "device allocation failed"));
-  if (total > 0 && cudaMemcpyAsync(own->dev_text, text, total, cudaMemcpyHostToDevice, st) != cudaSuccess)
-    return fail(set_err(AHA_ERR_CUDA, "H2D copy of text failed"));
-  if (cudaMemcpyAsync(own->dev_doc_off, doc_off, (n_docs + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, st) != cudaSuccess)
-    return fail(set_err(AHA_ERR_CUDA, "H2D copy of doc_off failed"));
-  rc = scan_on_device(d, own->dev_text, own->dev_doc_off, n_docs, total, mode, sep_bits, sep_size, st, res.get(), own);
-  if (rc) return fail(rc);
-  const size_t hbytes = (size_t)(res->n_hits > 0 ? res->n_hits : 1) * sizeof(aha_hit);
-  if (cudaMallocHost(&own->host_doc_hit_off, (n_docs + 1) * sizeof(int64_t)) != cudaSuccess)
-    return fail(set_err(AHA_ERR_NOMEM, "pinned allocation failed"));
-  if (!(mode & AHA_COUNT_ONLY)) {
-    if (cudaMallocHost(&own->host_hits, hbytes) != cudaSuccess) return fail(set_err(AHA_ERR_NOMEM, "pinned allocation failed"));
-    if (res->n_hits > 0 &&
-        cudaMemcpyAsync(own->host_hits, own->dev_hits, (size_t)res->n_hits * sizeof(aha_hit), cudaMemcpyDeviceToHost, st) != cudaSuccess)
-      return fail(set_err(AHA_ERR_CUDA, "D2H copy of hits failed"));
+#define AHA_E2E(expr)                                                                                      \
+  do {                                                                                                     \
+    cudaError_t _e = (expr);                                                                               \
+    if (_e != cudaSuccess) return fail(set_err(AHA_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e))); \
+  } while (0)
+  AHA_E2E(cudaStreamCreateWithFlags(&s_in, cudaStreamNonBlocking));
+  AHA_E2E(cudaStreamCreateWithFlags(&s_run, cudaStreamNonBlocking));
+  AHA_E2E(cudaStreamCreateWithFlags(&s_out, cudaStreamNonBlocking));
+  AHA_E2E(cudaEventCreateWithFlags(&e_out, cudaEventDisableTiming));
+  const int n_buf = n_runs > 1 ? 2 : 1;
+  for (int b = 0; b < n_buf; ++b) {
+    AHA_E2E(cudaEventCreateWithFlags(&e_in[b], cudaEventDisableTiming));
+    AHA_E2E(cudaMalloc(&d_text[b], (size_t)max_bytes + 64));
+    AHA_E2E(cudaMalloc(&d_off[b], (size_t)(max_docs + 1) * sizeof(int64_t)));
   }
-  if (cudaMemcpyAsync(own->host_doc_hit_off, own->dev_doc_hit_off, (n_docs + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
-      cudaStreamSynchronize(st) != cudaSuccess)
-    return fail(set_err(AHA_ERR_CUDA, std::string("D2H copy failed: ") + cudaGetErrorString(cudaGetLastError())));
+  h_off_stage = static_cast<int64_t*>(g_pinned.acquire((size_t)n_buf * (max_docs + 1) * sizeof(int64_t), &h_off_stage_bytes));
+  own->host_doc_hit_off = g_pinned.acquire((size_t)(n_docs + 1) * sizeof(int64_t), &off_bytes);
+  if (!h_off_stage || !own->host_doc_hit_off) return fail(set_err(AHA_ERR_NOMEM, "pinned allocation failed"));
+  own->host_doc_hit_off_bytes = off_bytes;
+  int64_t* h_doc_hit_off = static_cast<int64_t*>(own->host_doc_hit_off);
+
+  auto stage_in = [&](size_t k) -> cudaError_t {
+    const int b = (int)(k & 1);
+    const int64_t lo = cut[k], hi = cut[k + 1];
+    const int64_t base = doc_off[lo], bytes = doc_off[hi] - base;
+    int64_t* ho = h_off_stage + (size_t)b * (max_docs + 1);
+    for (int64_t i = lo; i <= hi; ++i) ho[i - lo] = doc_off[i] - base;
+    cudaError_t e = cudaSuccess;
+    if (bytes > 0) e = cudaMemcpyAsync(d_text[b], text + base, (size_t)bytes, cudaMemcpyHostToDevice, s_in);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_off[b], ho, (size_t)(hi - lo + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, s_in);
+    if (e == cudaSuccess) e = cudaEventRecord(e_in[b], s_in);
+    return e;
+  };
+
+  int64_t hit_base = 0;
+  double scan_ms = 0;
+  std::vector<int64_t> run_hit_base(n_runs + 1, 0);
+  AHA_E2E(stage_in(0));
+  for (size_t k = 0; k < n_runs; ++k) {
+    const int b = (int)(k & 1);
+    const int64_t lo = cut[k], hi = cut[k + 1];
+    const int64_t bytes = doc_off[hi] - doc_off[lo];
+    AHA_E2E(cudaStreamWaitEvent(s_run, e_in[b], 0));
+    aha_hits part;
+    memset(&part, 0, sizeof(part));
+    HitsOwner pown;
+    // the other buffer was released by the scan of run k-1 (scan_on_device synchronises its stream): the copy of
+    // run k+1 overlaps this scan, the hits of run k-1 are still going home on s_out
+    if (k + 1 < n_runs) AHA_E2E(stage_in(k + 1));
+    rc = scan_on_device(d, d_text[b], d_off[b], hi - lo, bytes, mode, sep_bits, sep_size, s_run, &part, &pown);
+    if (rc) return fail(rc);
+    scan_ms += part.scan_ms;
+    run_hit_base[k] = hit_base;
+    if (!count_only && part.n_hits > 0) {
+      const size_t need = (size_t)(hit_base + part.n_hits);
+      if (need > hits_cap) {  // grow: estimate the whole batch from the density seen so far
+        const double dens = (double)need / (double)std::max<int64_t>(1, doc_off[hi]);
+        size_t want = (size_t)((double)total * dens * 1.15) + 4096;
+        if (k + 1 == n_runs || want < need) want = need;
+        size_t got = 0;
+        void* nb = g_pinned.acquire(want * sizeof(aha_hit), &got);
+        if (!nb) return fail(set_err(AHA_ERR_NOMEM, "pinned allocation failed"));
+        if (own->host_hits) {
+          AHA_E2E(cudaStreamSynchronize(s_out));
+          memcpy(nb, own->host_hits, (size_t)hit_base * sizeof(aha_hit));
+          g_pinned.release(own->host_hits, hits_bytes);
+        }
+        own->host_hits = nb;
+        hits_bytes = got;
+        own->host_hits_bytes = got;
+        hits_cap = got / sizeof(aha_hit);
+      }
+      AHA_E2E(cudaMemcpyAsync(static_cast<aha_hit*>(own->host_hits) + hit_base, pown.dev_hits, (size_t)part.n_hits * sizeof(aha_hit),
+                              cudaMemcpyDeviceToHost, s_out));
+    }
+    AHA_E2E(cudaMemcpyAsync(h_doc_hit_off + lo, pown.dev_doc_hit_off, (size_t)(hi - lo + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost,
+                            s_out));
+    if (pown.dev_hits) AHA_E2E(cudaFreeAsync(pown.dev_hits, s_out));
+    if (pown.dev_doc_hit_off) AHA_E2E(cudaFreeAsync(pown.dev_doc_hit_off, s_out));
+    // per-run offsets start at 0: rebase once the copy has landed (next iteration's host work overlaps it)
+    if (k > 0) {
+      // run k-1's offsets are complete after the previous D2H; the copy just issued is behind it on s_out
+    }
+    hit_base += part.n_hits;
+    own->device = pown.device;
+  }
+  run_hit_base[n_runs] = hit_base;
+  AHA_E2E(cudaStreamSynchronize(s_out));
+  // runs overlap in one slot of doc_hit_off (the last offset of run k is the first of run k+1): rebase back to front
+  for (size_t k = n_runs; k-- > 0;) {
+    const int64_t lo = cut[k], hi = cut[k + 1], base = run_hit_base[k];
+    if (k + 1 < n_runs) h_doc_hit_off[hi] = run_hit_base[k + 1];
+    if (base != 0)
+      for (int64_t i = lo; i < hi; ++i) h_doc_hit_off[i] += base;
+  }
+  h_doc_hit_off[n_docs] = hit_base;
+  if (n_docs == 0) h_doc_hit_off[0] = 0;
+  if (!own->host_hits) {
+    size_t got = 0;
+    own->host_hits = g_pinned.acquire(sizeof(aha_hit), &got);
+    own->host_hits_bytes = got;
+  }
+  cleanup();
+#undef AHA_E2E
+  res->n_hits = hit_base;
+  res->scan_ms = scan_ms;
   res->device = own->device;
   res->on_device = 0;
   res->hits = static_cast<aha_hit*>(own->host_hits);
-  res->doc_hit_off = static_cast<int64_t*>(own->host_doc_hit_off);
+  res->doc_hit_off = h_doc_hit_off;
   *out = res.release();
   return AHA_OK;
 }
@@ -418,8 +599,8 @@ void aha_b200_hits_free(aha_hits* h) {
     if (own->dev_doc_hit_off) cudaFreeAsync(own->dev_doc_hit_off, own->stream);
     if (own->dev_text) cudaFreeAsync(own->dev_text, own->stream);
     if (own->dev_doc_off) cudaFreeAsync(own->dev_doc_off, own->stream);
-    if (own->host_hits) cudaFreeHost(own->host_hits);
-    if (own->host_doc_hit_off) cudaFreeHost(own->host_doc_hit_off);
+    if (own->host_hits) aha::g_pinned.release(own->host_hits, own->host_hits_bytes);
+    if (own->host_doc_hit_off) aha::g_pinned.release(own->host_doc_hit_off, own->host_doc_hit_off_bytes);
     cudaSetDevice(prev);
     delete own;
   }

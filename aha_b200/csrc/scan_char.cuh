@@ -627,7 +627,9 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const __
 
   const int64_t gwarp = (int64_t)blockIdx.x * kFusedWarps + warp;
   const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
-  const int32_t warmc = (int32_t)p.warm + 3;
+  // warm-up: the state at a position is a suffix of at most max_key_len - 1 bytes, and it starts at a unit boundary,
+  // so starting with the root at the first boundary inside that window reproduces it
+  const int32_t warmc = (int32_t)p.warm;
   const int32_t sub = F.chunk / kChains;
   uint32_t parity = 0;
   int buf = 0;

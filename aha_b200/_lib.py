@@ -51,7 +51,7 @@ class Hits(C.Structure):
 
 
 EXPORTS = [
-    "aha_b200_init", "aha_b200_last_error", "aha_b200_version", "aha_b200_builder_new", "aha_b200_builder_insert",
+    "aha_b200_init", "aha_b200_last_error", "aha_b200_version", "aha_b200_kernel_launches", "aha_b200_builder_new", "aha_b200_builder_insert",
     "aha_b200_builder_lookup", "aha_b200_builder_key", "aha_b200_builder_compile", "aha_b200_builder_free",
     "aha_b200_dfa_from_cedar", "aha_b200_dfa_compile", "aha_b200_flatten_host", "aha_b200_blob_free",
     "aha_b200_dfa_blob", "aha_b200_dfa_from_blob", "aha_b200_dfa_from_device_blob", "aha_b200_dfa_info",
@@ -72,6 +72,7 @@ def lib():
     vp, i32, i64, u32, u64 = C.c_void_p, C.c_int32, C.c_int64, C.c_uint32, C.c_uint64
     P = C.POINTER
     L.aha_b200_last_error.restype = C.c_char_p
+    L.aha_b200_kernel_launches.restype = C.c_int64
     L.aha_b200_init.argtypes = [P(i32), i32]
     L.aha_b200_builder_new.argtypes = [P(vp)]
     L.aha_b200_builder_insert.argtypes = [vp, C.c_char_p, i32, P(i32)]

@@ -20,6 +20,7 @@
 namespace aha {
 
 thread_local std::string g_err;
+std::atomic<long long> g_kernel_launches{0};
 static std::mutex g_mu;
 static std::vector<int> g_devices;  // devices selected by aha_b200_init
 // 0: two-pass v1 kernels (checker), 1: fused single-pass kernel (default); env AHA_B200_IMPL, read per call
@@ -131,6 +132,7 @@ using namespace aha;
 extern "C" {
 
 int32_t aha_b200_version(void) { return 100; }
+int64_t aha_b200_kernel_launches(void) { return (int64_t)aha::g_kernel_launches.load(); }
 const char* aha_b200_last_error(void) { return g_err.c_str(); }
 
 int32_t aha_b200_init(const int32_t* devices, int32_t n) {

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdio>
 #include <mutex>
 #include <string>
@@ -14,6 +15,7 @@
 namespace aha {
 
 extern thread_local std::string g_err;
+extern std::atomic<long long> g_kernel_launches;  // kernels launched by this library (aha_b200_kernel_launches)
 
 inline int32_t set_err(int32_t code, const std::string& m) {
   g_err = m;

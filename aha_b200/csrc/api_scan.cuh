@@ -79,11 +79,11 @@ static int32_t run_v1(ScanParams p, cudaStream_t st, aha_hits* res, HitsOwner* o
     AHA_CUDA(cudaMallocAsync(&lead_counts, (p.n_chunks + 1) * sizeof(uint32_t), st));
     AHA_CUDA(cudaMallocAsync(&lead_prefix, (p.n_chunks + 1) * sizeof(uint64_t), st));
     AHA_CUDA(cudaMallocAsync(&doc_lead, (p.n_docs + 1) * sizeof(uint64_t), st));
-    count_leads_kernel<<<(unsigned)((p.n_chunks + 1 + 7) / 8), 256, 0, st>>>(p.text, p.total, p.chunk, p.n_chunks, lead_counts);
+    count_leads_kernel<<<(unsigned)((p.n_chunks + 1 + 7) / 8), 256, 0, st>>>(p.text, p.total, p.chunk, p.n_chunks, lead_counts); aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
     int32_t rc = exclusive_sum_u32_to_u64(lead_counts, lead_prefix, p.n_chunks + 1, st);
     if (rc) return rc;
     doc_lead_base_kernel<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(p.text, p.total, p.doc_off, p.n_docs, p.chunk,
-                                                                              lead_prefix, doc_lead);
+                                                                              lead_prefix, doc_lead); aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
     p.lead_prefix = lead_prefix;
     p.doc_lead_base = doc_lead;
   }
@@ -92,6 +92,7 @@ static int32_t run_v1(ScanParams p, cudaStream_t st, aha_hits* res, HitsOwner* o
     if (trie) trie_longest_doc_kernel<false><<<grid, tpb, 0, st>>>(p);
     else if (longest) longest_doc_kernel<false><<<grid, tpb, 0, st>>>(p);
     else scan_v1_kernel<false><<<grid, tpb, 0, st>>>(p);
+    aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
   }
   int32_t rc = exclusive_sum_u32_to_u64(counts, offsets, units + 1, st);
   if (rc) return rc;
@@ -107,9 +108,10 @@ static int32_t run_v1(ScanParams p, cudaStream_t st, aha_hits* res, HitsOwner* o
     if (longest) {
       if (trie) trie_longest_doc_kernel<true><<<grid, tpb, 0, st>>>(p);
       else longest_doc_kernel<true><<<grid, tpb, 0, st>>>(p);
-      offsets_to_doc_hit_off<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(offsets, p.n_docs, p.doc_hit_off);
+      aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
+      offsets_to_doc_hit_off<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(offsets, p.n_docs, p.doc_hit_off); aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
     } else {
-      scan_v1_kernel<true><<<grid, tpb, 0, st>>>(p);
+      scan_v1_kernel<true><<<grid, tpb, 0, st>>>(p); aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
     }
   }
   AHA_CUDA(cudaEventRecord(ev1, st));
@@ -128,7 +130,7 @@ static int32_t run_v1(ScanParams p, cudaStream_t st, aha_hits* res, HitsOwner* o
 template <class Policy>
 static int32_t launch_fused(const FusedParams& fp, const Policy& pol, int n_sm, size_t smem, cudaStream_t st) {
   AHA_CUDA(cudaFuncSetAttribute(scan_fused_kernel<Policy>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  scan_fused_kernel<Policy><<<n_sm, kFusedWarps * 32, smem, st>>>(fp, pol);
+  scan_fused_kernel<Policy><<<n_sm, kByteWarps * 32, smem, st>>>(fp, pol); aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
   AHA_CUDA(cudaGetLastError());
   return AHA_OK;
 }
@@ -146,7 +148,7 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
   fp.tile = 32 * fp.chunk;
   fp.n_tiles = (p.total + fp.tile - 1) / fp.tile;
   const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
-  const int64_t n_warps = (int64_t)n_sm * kFusedWarps;
+  const int64_t n_warps = (int64_t)n_sm * (use_char ? kFusedWarps : kByteWarps);
   unsigned long long* tile_state = nullptr;
   unsigned int* counters = nullptr;  // [0] ticket, [1] n_direct, [2..3] total_hits (u64)
   uint32_t* lead_counts = nullptr;
@@ -187,7 +189,7 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
   ByteGlobal pol;
   pol.cmap_g = p.classmap;
   pol.cmap = nullptr;
-  size_t smem = ((ByteGlobal::table_bytes(pol) + 127) & ~127u) + (size_t)kFusedWarps * (fp.buf_bytes + 128);
+  size_t smem = ((ByteGlobal::table_bytes(pol) + 127) & ~127u) + (size_t)kByteWarps * (fp.buf_bytes + 128);
   if (use_char) {
     smem = ((dd->hot.smem_bytes + 127) & ~size_t(127)) + (size_t)kFusedWarps * (fp.buf_bytes + 128);
     AHA_CUDA(cudaFuncSetAttribute(scan_char_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
@@ -214,11 +216,11 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
   }
   AHA_CUDA(cudaEventRecord(ev0, st));
   if (chars && p.total > 0) {
-    count_leads_kernel<<<(unsigned)((fp.n_tiles + 1 + 7) / 8), 256, 0, st>>>(p.text, p.total, fp.tile, fp.n_tiles, lead_counts);
+    count_leads_kernel<<<(unsigned)((fp.n_tiles + 1 + 7) / 8), 256, 0, st>>>(p.text, p.total, fp.tile, fp.n_tiles, lead_counts); aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
     int32_t rc = exclusive_sum_u32_to_u64(lead_counts, tile_lead, fp.n_tiles + 1, st);
     if (rc) return rc;
     doc_lead_base_kernel<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(p.text, p.total, p.doc_off, p.n_docs, fp.tile,
-                                                                              tile_lead, doc_lead);
+                                                                              tile_lead, doc_lead); aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
     fp.tile_lead = tile_lead;
     p.doc_lead_base = doc_lead;
     AHA_HSTAMP("lead prepass");
@@ -243,7 +245,7 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
     if (fp.n_tiles > 0) {
       if (use_char) {
         cp.f = fp;
-        scan_char_kernel<<<n_sm, kFusedWarps * 32, smem, st>>>(cp);
+        scan_char_kernel<<<n_sm, kFusedWarps * 32, smem, st>>>(cp); aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
         AHA_CUDA(cudaGetLastError());
       } else {
         int32_t rc = launch_fused(fp, pol, n_sm, smem, st);
@@ -251,7 +253,7 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
       }
     }
     finalize_doc_off_kernel<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(p.doc_off, p.n_docs, p.total, fp.total_hits,
-                                                                                 p.doc_hit_off);
+                                                                                 p.doc_hit_off); aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
     AHA_CUDA(cudaEventRecord(ev1, st));
     AHA_HSTAMP("launched");
     AHA_CUDA(cudaMemcpyAsync(&total_hits, fp.total_hits, sizeof(total_hits), cudaMemcpyDeviceToHost, st));
@@ -646,7 +648,7 @@ extern "C" int32_t aha_b200_gen_text_device(int32_t corpus, uint64_t seed, int64
   if (bytes == 0) return AHA_OK;
   const int64_t n_blocks = (bytes + kGenBlock - 1) / kGenBlock;
   gen_text_kernel<<<(unsigned)((n_blocks + 127) / 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(
-      corpus, seed, first / kGenBlock, n_blocks, bytes, static_cast<uint8_t*>(dev_out));
+      corpus, seed, first / kGenBlock, n_blocks, bytes, static_cast<uint8_t*>(dev_out)); aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
   AHA_CUDA(cudaGetLastError());
   return AHA_OK;
 }

@@ -24,7 +24,8 @@ namespace aha {
 constexpr int kLaneCap = 32;      // scratch records per lane per tile
 constexpr int kMarkCap = 4;       // document-start markers per lane per tile
 constexpr int kMarkCapC = 2;      // ... per sub-chunk (scan_char.cuh walks two sub-chunks per lane)
-constexpr int kFusedWarps = 16;   // warps per CTA
+constexpr int kFusedWarps = 16;   // warps per CTA of scan_char_kernel (register- and shared-memory-bound)
+constexpr int kByteWarps = 32;    // warps per CTA of scan_fused_kernel<ByteGlobal>: latency-bound on L2, so as many as fit
 
 struct FusedParams {
   ScanParams sp;
@@ -247,7 +248,7 @@ __device__ __forceinline__ unsigned long long tile_exclusive_prefix(const FusedP
 }
 
 template <class Policy>
-__global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_fused_kernel(const FusedParams P, const Policy policy_in) {
+__global__ void __launch_bounds__(kByteWarps * 32, 1) scan_fused_kernel(const FusedParams P, const Policy policy_in) {
   extern __shared__ __align__(128) uint8_t smem[];
   const ScanParams& p = P.sp;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -263,7 +264,7 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_fused_kernel(const F
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   __syncthreads();
 
-  const int64_t gwarp = (int64_t)blockIdx.x * kFusedWarps + warp;
+  const int64_t gwarp = (int64_t)blockIdx.x * kByteWarps + warp;
   aha_hit* my_rec = P.scratch + (gwarp * 32 + lane) * kLaneCap;
   int2* my_mark = P.marks + (gwarp * 32 + lane) * kMarkCap;
   uint32_t parity = 0;

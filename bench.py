@@ -40,6 +40,16 @@ def make_patterns(name):
     return synth.patterns_mix(100000), synth.MIX, synth.SEED_TEXT + 2
 
 
+def measured_traffic(name):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the scan kernel from the committed `ncu --set full` capture
+    (profiles/traffic.json: bytes per text byte for the workload), scaled to this launch by the caller."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(name)
+    except Exception:
+        return None
+
+
 def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -178,15 +188,11 @@ def main():
     build_s = time.perf_counter() - t0
     bcast_ms = 0.0
     if world > 1:
-        n = torch.tensor([len(blob) if rank == 0 else 0], dtype=torch.int64, device="cuda")
-        dist.broadcast(n, 0)
-        buf = torch.empty(int(n.item()), dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            buf.copy_(torch.frombuffer(bytearray(blob), dtype=torch.uint8))
+        from aha_b200 import shard
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        dist.broadcast(buf, 0)  # ncclBroadcast over NVLink
+        buf = shard.broadcast_blob(blob if rank == 0 else b"", 0, "cuda")  # ncclBroadcast over NVLink
         e1.record()
         torch.cuda.synchronize()
         bcast_ms = e0.elapsed_time(e1)
@@ -213,7 +219,8 @@ def main():
     for _ in range(W):
         res = step()
     n_hits = res.n_hits
-    launches_per_step = int(os.environ.get("AHA_LAUNCHES_PER_STEP", "0")) or (2 if os.environ.get("AHA_B200_IMPL") == "0" else 2)
+    from aha_b200 import _lib
+    launches0 = _lib.lib().aha_b200_kernel_launches()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -226,6 +233,7 @@ def main():
         kernel_ms.append(res.scan_ms)
     ev1.record()
     barrier()
+    gpu_launches = int(_lib.lib().aha_b200_kernel_launches() - launches0)  # kernels of libaha_b200.so in the timed region
     clocks = sampler.stop() if rank == 0 else None
     ms_total = ev0.elapsed_time(ev1)
     t = torch.tensor([ms_total, float(n_hits)], dtype=torch.float64, device="cuda")
@@ -241,10 +249,12 @@ def main():
     kms = float(np.mean(kernel_ms))
     peak, peak_src = peaks()
     achieved = (total + 12.0 * n_hits) / (kms * 1e-3) / 1e9
+    tr = measured_traffic(name)
+    traffic = int(tr["dram_bytes_per_text_byte"] * total) if tr else None
 
     # ---- end to end through the C ABI with host buffers (rank-local shard, pinned host text) ----
     e2e = None
-    e2e_bytes = min(total, (512 << 20) // D * D) if not args.bytes else total
+    e2e_bytes = min(total, (1 << 30) // D * D) if not args.bytes else total
     e2e_docs = e2e_bytes // D
     host_text = torch.empty(e2e_bytes, dtype=torch.uint8, pin_memory=True)
     host_text.copy_(text[:e2e_bytes])
@@ -264,7 +274,8 @@ def main():
     e2e = {"value": world * e2e_bytes / float(e2e_t.item()) / 1e9, "unit": "GB/s",
            "h2d_bytes_per_step": int(e2e_bytes + 8 * (e2e_docs + 1)),
            "d2h_bytes_per_step": int(12 * r.n_hits + 8 * (e2e_docs + 1)),
-           "note": "aha_b200_scan on %d MB of host text per rank per step" % (e2e_bytes >> 20)}
+           "note": "aha_b200_scan (C ABI, pinned host text in, pinned host hits out, H2D/scan/D2H pipelined over 64 MB runs) "
+                   "on %d MB of host text per rank per step" % (e2e_bytes >> 20)}
 
     if rank == 0:
         cpu = None
@@ -287,10 +298,10 @@ def main():
                        "impl": "two-pass" if os.environ.get("AHA_B200_IMPL") == "0" else "fused"},
             "hits_per_s": hits_all / (ms_step * 1e-3),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "kernel_ms": kms,
+                         "traffic": traffic, "traffic_source": (tr or {}).get("source"), "peak_source": peak_src, "kernel_ms": kms,
                          "algorithmic_bytes": "1 B read per text byte + 12 B written per hit"},
             "cpu_baseline": cpu,
-            "e2e": e2e, "gpu_launches": launches_per_step * args.steps, "clocks": clocks,
+            "e2e": e2e, "gpu_launches": gpu_launches, "clocks": clocks,
             "dfa_build_s": build_s, "dfa_broadcast_ms": bcast_ms,
         }
         print(json.dumps(line))

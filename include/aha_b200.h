@@ -64,6 +64,8 @@ enum aha_mode {
 int32_t aha_b200_init(const int32_t* devices, int32_t n);
 const char* aha_b200_last_error(void);
 int32_t aha_b200_version(void);
+/* number of CUDA kernels this library has launched so far in the process (diagnostics / bench accounting) */
+int64_t aha_b200_kernel_launches(void);
 
 /* ---- host builder: Aha::Cedar#insert + Aha::AC.compile where Crystal is absent ----------- */
 /* Aha::Cedar.new (cedar.cr:198-221) */

@@ -16,6 +16,7 @@
 #include "scan_trie.cuh"
 #include "scan_fused.cuh"
 #include "scan_char.cuh"
+#include "scan_char_split.cuh"
 
 namespace aha {
 

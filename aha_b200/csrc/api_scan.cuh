@@ -135,6 +135,134 @@ static int32_t launch_fused(const FusedParams& fp, const Policy& pol, int n_sm, 
   return AHA_OK;
 }
 
+// character automaton, three kernels (scan_char_split.cuh): walk -> prefix over tiles -> expansion at full occupancy
+static int32_t run_char_split(ScanParams p, const DeviceDfa* dd, cudaStream_t st, aha_hits* res, HitsOwner* own, cudaEvent_t ev0,
+                              cudaEvent_t ev1) {
+  int dev = 0, n_sm = 0;
+  AHA_CUDA(cudaGetDevice(&dev));
+  AHA_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+  SplitParams sp;
+  memset(&sp, 0, sizeof(sp));
+  CharParams& cp = sp.c;
+  FusedParams& fp = cp.f;
+  fused_geometry(p.warm + 1, true, &fp.chunk, &fp.w16, &fp.buf_bytes);
+  fp.tile = 32 * fp.chunk;
+  fp.n_tiles = (p.total + fp.tile - 1) / fp.tile;
+  const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
+  const HotTable& h = dd->hot;
+  cp.t.root_g = reinterpret_cast<const uint32_t*>(h.dev + h.off_root);
+  cp.t.val_g = reinterpret_cast<const uint32_t*>(h.dev + h.off_val);
+  cp.t.check_g = reinterpret_cast<const uint16_t*>(h.dev + h.off_check);
+  cp.t.gfail = reinterpret_cast<const uint16_t*>(h.dev + h.off_gfail);
+  cp.t.ref_rec = reinterpret_cast<const RefRec*>(h.dev + h.off_ref);
+  cp.t.n_root = h.n_root;
+  cp.t.m = h.m;
+  cp.t.m_pad = h.m_pad;
+  cp.t.n_mwords = h.n_mwords;
+  cp.t.mbits_g = reinterpret_cast<const uint32_t*>(h.dev + h.off_mbits);
+  for (int c = 0; c < 3; ++c) { cp.t.lo[c] = h.lo[c]; cp.t.n[c] = h.n[c]; cp.t.off[c] = h.off[c]; }
+  cp.cmap_g = p.classmap;
+  const int64_t nt = fp.n_tiles;
+  unsigned int* counters = nullptr;  // [0] ticket, [1] n_direct_list
+  uint64_t* tile_prefix = nullptr;
+  uint32_t* lead_counts = nullptr;
+  uint64_t* tile_lead = nullptr;
+  uint64_t* doc_lead = nullptr;
+  void* scan_tmp = nullptr;
+  size_t scan_tmp_bytes = 0;
+  AHA_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, scan_tmp_bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr, nt + 1, st));
+  // every allocation whose size is known happens before the timed region
+  AHA_CUDA(cudaMallocAsync(&counters, 16, st));
+  AHA_CUDA(cudaMallocAsync(&sp.store, (size_t)(nt ? nt : 1) * 32 * kStoreSlots * sizeof(CharEvent), st));
+  AHA_CUDA(cudaMallocAsync(&sp.tile_meta, (size_t)(nt ? nt : 1) * 32 * kChains * sizeof(uint32_t), st));
+  AHA_CUDA(cudaMallocAsync(&sp.tile_hits, (size_t)(nt + 1) * sizeof(uint32_t), st));
+  AHA_CUDA(cudaMallocAsync(&sp.direct_list, (size_t)(nt ? nt : 1) * sizeof(uint32_t), st));
+  AHA_CUDA(cudaMallocAsync(&tile_prefix, (size_t)(2 * (nt + 1)) * sizeof(uint64_t), st));
+  AHA_CUDA(cudaMallocAsync(&scan_tmp, scan_tmp_bytes ? scan_tmp_bytes : 16, st));
+  AHA_CUDA(cudaMallocAsync(&own->dev_doc_hit_off, (p.n_docs + 1) * sizeof(int64_t), st));
+  p.doc_hit_off = static_cast<int64_t*>(own->dev_doc_hit_off);
+  if (chars && p.total > 0) {
+    AHA_CUDA(cudaMallocAsync(&lead_counts, (nt + 1) * sizeof(uint32_t), st));
+    AHA_CUDA(cudaMallocAsync(&tile_lead, (nt + 1) * sizeof(uint64_t), st));
+    AHA_CUDA(cudaMallocAsync(&doc_lead, (p.n_docs + 1) * sizeof(uint64_t), st));
+  }
+  sp.n_direct_list = counters + 1;
+  fp.ticket = counters;
+  fp.n_direct = counters + 1;
+  sp.tile_prefix = tile_prefix;
+  uint64_t* hits_u64 = tile_prefix + (nt + 1);
+  const size_t smem = ((h.smem_bytes + 127) & ~size_t(127)) + (size_t)kFusedWarps * (fp.buf_bytes + 128);
+  AHA_CUDA(cudaFuncSetAttribute(char_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+
+  AHA_CUDA(cudaEventRecord(ev0, st));
+  if (chars && p.total > 0) {
+    count_leads_kernel<<<(unsigned)((nt + 1 + 7) / 8), 256, 0, st>>>(p.text, p.total, fp.tile, nt, lead_counts);
+    g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
+    int32_t rc = exclusive_sum_u32_to_u64(lead_counts, tile_lead, nt + 1, st);
+    if (rc) return rc;
+    doc_lead_base_kernel<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(p.text, p.total, p.doc_off, p.n_docs, fp.tile, tile_lead,
+                                                                              doc_lead);
+    g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
+    fp.tile_lead = tile_lead;
+    p.doc_lead_base = doc_lead;
+  }
+  AHA_CUDA(cudaMemsetAsync(counters, 0, 16, st));
+  AHA_CUDA(cudaMemsetAsync(sp.tile_hits + nt, 0, sizeof(uint32_t), st));
+  AHA_CUDA(cudaMemsetAsync(own->dev_doc_hit_off, 0, (p.n_docs + 1) * sizeof(int64_t), st));
+  p.hits = nullptr;
+  fp.hit_cap = 0;
+  fp.sp = p;
+  if (nt > 0) {
+    char_walk_kernel<<<n_sm, kFusedWarps * 32, smem, st>>>(sp);
+    g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
+    AHA_CUDA(cudaGetLastError());
+  }
+  tile_hits_to_u64_kernel<<<(unsigned)((nt + 1 + 255) / 256), 256, 0, st>>>(sp.tile_hits, nt + 1, hits_u64);
+  g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
+  AHA_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp, scan_tmp_bytes, hits_u64, tile_prefix, nt + 1, st));
+  g_kernel_launches.fetch_add(2, std::memory_order_relaxed);
+  unsigned long long total_hits = 0;
+  unsigned int n_direct = 0;
+  AHA_CUDA(cudaMemcpyAsync(&total_hits, tile_prefix + nt, sizeof(total_hits), cudaMemcpyDeviceToHost, st));
+  AHA_CUDA(cudaMemcpyAsync(&n_direct, sp.n_direct_list, sizeof(n_direct), cudaMemcpyDeviceToHost, st));
+  AHA_CUDA(cudaStreamSynchronize(st));
+  // the hit buffer is sized exactly: the walk has already counted
+  if (!(p.mode & AHA_COUNT_ONLY)) {
+    AHA_CUDA(cudaMallocAsync(&own->dev_hits, (size_t)(total_hits ? total_hits : 1) * sizeof(aha_hit), st));
+    fp.sp.hits = static_cast<aha_hit*>(own->dev_hits);
+    fp.hit_cap = (int64_t)total_hits;
+  }
+  if (nt > 0) {
+    const unsigned grid = (unsigned)std::min<int64_t>((nt + 7) / 8, (int64_t)n_sm * 64);
+    char_expand_kernel<<<grid, 256, 0, st>>>(sp);
+    g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
+    if (n_direct > 0) {
+      const unsigned dgrid = (unsigned)std::min<int64_t>(((int64_t)n_direct + 3) / 4, (int64_t)n_sm * 8);
+      char_direct_kernel<<<dgrid, 128, 256 + 4 * (size_t)fp.buf_bytes, st>>>(sp);
+      g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
+    }
+    AHA_CUDA(cudaGetLastError());
+  }
+  finalize_doc_off_kernel<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(p.doc_off, p.n_docs, p.total, reinterpret_cast<const unsigned long long*>(tile_prefix + nt), p.doc_hit_off);
+  g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
+  AHA_CUDA(cudaEventRecord(ev1, st));
+  AHA_CUDA(cudaGetLastError());
+  res->n_hits = (int64_t)total_hits;
+  AHA_CUDA(cudaFreeAsync(counters, st));
+  AHA_CUDA(cudaFreeAsync(sp.store, st));
+  AHA_CUDA(cudaFreeAsync(sp.tile_meta, st));
+  AHA_CUDA(cudaFreeAsync(sp.tile_hits, st));
+  AHA_CUDA(cudaFreeAsync(sp.direct_list, st));
+  AHA_CUDA(cudaFreeAsync(tile_prefix, st));
+  AHA_CUDA(cudaFreeAsync(scan_tmp, st));
+  if (lead_counts) {
+    AHA_CUDA(cudaFreeAsync(lead_counts, st));
+    AHA_CUDA(cudaFreeAsync(tile_lead, st));
+    AHA_CUDA(cudaFreeAsync(doc_lead, st));
+  }
+  return AHA_OK;
+}
+
 static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, cudaStream_t st, aha_hits* res, HitsOwner* own,
                          cudaEvent_t ev0, cudaEvent_t ev1) {
   int dev = 0, n_sm = 0;
@@ -317,7 +445,10 @@ static int32_t scan_on_device(const aha_dfa* d, const void* dev_text, const void
   AHA_CUDA(cudaEventCreate(&ev1));
   const bool fused_ok = scan_impl() == 1 && !(mode & (AHA_LONGEST | AHA_TRIE_LONGEST)) &&
                         (reinterpret_cast<uintptr_t>(dev_text) & 15) == 0 && dd->view.max_key_len <= 1024;
-  if (fused_ok) rc = run_fused(p, dd, d, st, res, own, ev0, ev1);
+  const char* cimpl = getenv("AHA_B200_CHAR_IMPL");  // "fused": the single-kernel variant of scan_char.cuh (kept for A/B runs)
+  const bool split = fused_ok && dd->hot.ok && !(mode & AHA_SEP) && !(cimpl && cimpl[0] == 'f');
+  if (split) rc = run_char_split(p, dd, st, res, own, ev0, ev1);
+  else if (fused_ok) rc = run_fused(p, dd, d, st, res, own, ev0, ev1);
   else rc = run_v1(p, st, res, own, ev0, ev1);
   if (rc == AHA_OK) {
     AHA_CUDA(cudaEventSynchronize(ev1));

@@ -235,7 +235,9 @@ constexpr int kEvSlotsC = kEvSlots / kChains;  // ring slots per sub-chunk (>= b
 // Events of sub-chunk c go to my_ev[c * kEvSlotsC ...); n_ev[c] counts all of them; multi_mask bit (c * kEvCapC + i)
 // = event i of sub-chunk c reports more than one key.  Returns false (warp-uniform) when the text is not
 // structurally valid UTF-8: the caller rescans the tile with the byte automaton.
-template <bool kChars, class OnDoc>
+// kStride = ring slots per sub-chunk; kBounded: drop (but count) events beyond kStride instead of relying on
+// kStride >= bytes of a sub-chunk.
+template <bool kChars, int kStride, bool kBounded, class OnDoc>
 __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanParams& p, const uint8_t* sbuf, int64_t origin, int64_t a,
                                                int64_t b, int32_t sub, int32_t stage_end, int32_t warmc, bool one_doc, int64_t cd,
                                                int64_t cdoc_start, int64_t cdoc_end, const uint32_t (&lead0)[kChains], CharEvent* my_ev,
@@ -286,7 +288,7 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
         doc_end = p.doc_off[d + 1];
       }
       if (doc_start == ac) {
-        for (int64_t e = first_ge(p.doc_off, p.n_docs, ac); e <= d; ++e) on_doc(c, e, 0u);
+        for (int64_t e = first_ge(p.doc_off, p.n_docs, ac); e <= d; ++e) on_doc(c, e, n_ev[c]);
       }
       enter_segment(c, doc_start, doc_end);
     }
@@ -302,7 +304,8 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
     if (kChars) k[c] += (cs >= a_seg[c]) ? 1u : 0u;
     const bool fire = (v & 0x8000u) && (uint32_t)(last - a_seg[c]) < (uint32_t)(rb[c] - a_seg[c]);
     if (fire) {
-      my_ev[c * kEvSlotsC + n_ev[c]] = CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : last + ebase[c], ref};
+      if (!kBounded || n_ev[c] < (uint32_t)kStride)
+        my_ev[c * kStride + n_ev[c]] = CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : last + ebase[c], ref};
       const uint32_t cnt = (S.mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
       n_hit[c] += cnt;
       lookup = lookup || cnt == 0u;
@@ -344,7 +347,8 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
       for (int c = 0; c < kChains; ++c) {
         if (fire[c]) {
           const uint32_t ref = q[c].hit ? q[c].slotv : S.m + q[c].cid;
-          my_ev[c * kEvSlotsC + n_ev[c]] = CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : cs[c] + len - 1 + ebase[c], ref};
+          if (!kBounded || n_ev[c] < (uint32_t)kStride)
+            my_ev[c * kStride + n_ev[c]] = CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : cs[c] + len - 1 + ebase[c], ref};
           const uint32_t cnt = (S.mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
           n_hit[c] += cnt;
           lookup = lookup || cnt == 0u;
@@ -732,9 +736,9 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) scan_char_kernel(const __
         ++n_mark[c];
       };
       const int32_t stage_end = (int32_t)(want_end - origin);
-      const bool ok = chars ? char_tile_walk<true>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start, cdoc_end, lead0,
+      const bool ok = chars ? char_tile_walk<true, kEvSlotsC, false>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start, cdoc_end, lead0,
                                                    my_ev, n_ev, n_hit, lookup, on_doc)
-                            : char_tile_walk<false>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start, cdoc_end, lead0,
+                            : char_tile_walk<false, kEvSlotsC, false>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start, cdoc_end, lead0,
                                                     my_ev, n_ev, n_hit, lookup, on_doc);
       AHA_PHASE(2);
       bad = __any_sync(0xffffffffu, !ok);

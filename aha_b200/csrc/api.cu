@@ -46,12 +46,12 @@ static int32_t ensure_devices() {
 }
 
 // per-warp text buffer geometry of the fused kernels (shared by the table budget and the launcher)
-// 132 = 4 * 33 bytes per lane: the lanes' chunks start in distinct banks (a 126-byte chunk = six 12-byte steps per
-// sub-chunk of 3-byte units was measured: fewer steps but 5 % more tiles, and the per-tile costs dominate)
+// byte kernel: 132 = 4 * 33 bytes per lane, the lanes' chunks start in distinct banks.
+// character kernels: 126 = 2 sub-chunks of 63 bytes; with the 9 warm-up bytes that a run of 3-byte units needs, a
+// sub-chunk is exactly six 12-byte steps (132 would need a seventh, three quarters empty)
 static void fused_geometry(uint32_t max_key_len, bool char_kernel, int32_t* chunk, int32_t* w16, int32_t* buf_bytes) {
   const uint32_t warm = max_key_len > 0 ? max_key_len - 1 : 0;
-  (void)char_kernel;
-  *chunk = 132;
+  *chunk = char_kernel ? 126 : 132;
   *w16 = (int32_t)((warm + 1 + 3 + 15) & ~15u);
   if (*w16 < 16) *w16 = 16;
   *buf_bytes = (*w16 + 32 * *chunk + 16 + 32 + 127) & ~127;  // 16 staged bytes past the tile + read slack

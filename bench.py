@@ -153,7 +153,7 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--bytes", type=int, default=0, help="override bytes per GPU (testing)")
-    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -260,12 +260,16 @@ def main():
     host_text.copy_(text[:e2e_bytes])
     host_np = host_text.numpy()
     host_off = np.arange(e2e_docs + 1, dtype=np.int64) * D
-    r = ac.scan_batch((host_np, host_off))
+    for _ in range(2):  # warm-up: pinned result buffers and the device pool reach their steady size
+        r = ac.scan_batch((host_np, host_off))
+        e2e_hits = r.n_hits
+        r = None  # a caller releases one result before asking for the next (aha_b200_hits_free)
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.e2e_steps):
         r = ac.scan_batch((host_np, host_off))
-        _ = r.n_hits
+        e2e_hits = r.n_hits  # hits and doc_hit_off are in pinned host memory when the call returns
+        r = None
     torch.cuda.synchronize()
     e2e_s = (time.perf_counter() - t0) / args.e2e_steps
     e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
@@ -273,7 +277,7 @@ def main():
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
     e2e = {"value": world * e2e_bytes / float(e2e_t.item()) / 1e9, "unit": "GB/s",
            "h2d_bytes_per_step": int(e2e_bytes + 8 * (e2e_docs + 1)),
-           "d2h_bytes_per_step": int(12 * r.n_hits + 8 * (e2e_docs + 1)),
+           "d2h_bytes_per_step": int(12 * e2e_hits + 8 * (e2e_docs + 1)),
            "note": "aha_b200_scan (C ABI, pinned host text in, pinned host hits out, H2D/scan/D2H pipelined over 64 MB runs) "
                    "on %d MB of host text per rank per step" % (e2e_bytes >> 20)}
 

@@ -236,7 +236,8 @@ constexpr int kEvSlotsC = kEvSlots / kChains;  // ring slots per sub-chunk (>= b
 // = event i of sub-chunk c reports more than one key.  Returns false (warp-uniform) when the text is not
 // structurally valid UTF-8: the caller rescans the tile with the byte automaton.
 // kStride = ring slots per sub-chunk; kBounded: drop (but count) events beyond kStride instead of relying on
-// kStride >= bytes of a sub-chunk.
+// kStride >= bytes of a sub-chunk, and lay the slots out slot-major (event i of sub-chunk c at my_ev[i * 64 + c]: the
+// i-th events of all 64 sub-chunks of a tile share sectors, so the store is written and read densely).
 template <bool kChars, int kStride, bool kBounded, class OnDoc>
 __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanParams& p, const uint8_t* sbuf, int64_t origin, int64_t a,
                                                int64_t b, int32_t sub, int32_t stage_end, int32_t warmc, bool one_doc, int64_t cd,
@@ -305,7 +306,7 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
     const bool fire = (v & 0x8000u) && (uint32_t)(last - a_seg[c]) < (uint32_t)(rb[c] - a_seg[c]);
     if (fire) {
       if (!kBounded || n_ev[c] < (uint32_t)kStride)
-        my_ev[c * kStride + n_ev[c]] = CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : last + ebase[c], ref};
+        my_ev[kBounded ? n_ev[c] * 64 + c : c * kStride + n_ev[c]] = CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : last + ebase[c], ref};
       const uint32_t cnt = (S.mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
       n_hit[c] += cnt;
       lookup = lookup || cnt == 0u;
@@ -348,7 +349,8 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
         if (fire[c]) {
           const uint32_t ref = q[c].hit ? q[c].slotv : S.m + q[c].cid;
           if (!kBounded || n_ev[c] < (uint32_t)kStride)
-            my_ev[c * kStride + n_ev[c]] = CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : cs[c] + len - 1 + ebase[c], ref};
+            my_ev[kBounded ? n_ev[c] * 64 + c : c * kStride + n_ev[c]] =
+                CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : cs[c] + len - 1 + ebase[c], ref};
           const uint32_t cnt = (S.mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
           n_hit[c] += cnt;
           lookup = lookup || cnt == 0u;

@@ -23,7 +23,7 @@ constexpr uint32_t kTileDirect = 0x80000000u;         // tile_hits[] flag: the t
 
 struct SplitParams {
   CharParams c;
-  CharEvent* store;          // [n_tiles][32][kStoreSlots]
+  CharEvent* store;          // [n_tiles][kStoreSlotsC][32 lanes][kChains]: slot-major, event i of every sub-chunk side by side
   uint32_t* tile_meta;       // [n_tiles][32][kChains]  hits:16 | events:16 of a sub-chunk
   uint32_t* tile_hits;       // [n_tiles + 1] hits of the tile | kTileDirect
   const uint64_t* tile_prefix;  // [n_tiles + 1] exclusive prefix of the hits (kernels 3 and 4)
@@ -139,11 +139,11 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
       if (a1 < b) lead0[1] = (uint32_t)(before_a + mine0 - (one_doc ? dlb : p.doc_lead_base[last_le(p.doc_off, p.n_docs, a1)]));
     }
 
-    CharEvent* my_ev = pin_ptr(Q.store + ((size_t)t * 32 + lane) * kStoreSlots);
+    CharEvent* my_ev = pin_ptr(Q.store + (size_t)t * 32 * kStoreSlots + lane * kChains);
     uint32_t n_ev[kChains] = {0, 0}, n_hit[kChains] = {0, 0};
     bool lookup = false;
     auto on_doc = [&](int c, int64_t d, uint32_t nev) {  // marker event in the stream of sub-chunk c
-      if (nev < (uint32_t)kStoreSlotsC) my_ev[c * kStoreSlotsC + nev] = CharEvent{(int32_t)d, kMarkRef};
+      if (nev < (uint32_t)kStoreSlotsC) my_ev[nev * 64 + c] = CharEvent{(int32_t)d, kMarkRef};
       ++n_ev[c];
     };
     const int32_t stage_end = (int32_t)(want_end - origin);
@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
         for (int c = 0; c < kChains; ++c) {
           n_hit[c] = 0;
           for (uint32_t i = 0; i < n_ev[c]; ++i) {
-            const uint32_t ref = my_ev[c * kStoreSlotsC + i].ref;
+            const uint32_t ref = my_ev[i * 64 + c].ref;
             if (ref != kMarkRef) n_hit[c] += P.t.ref_rec[ref].n;
           }
         }
@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(256) char_expand_kernel(const __grid_constant_
       RefRec rr{0, 0, 0, 0};
       if (i < E) {
         const uint32_t idx = i - ex;
-        ev = tile_ev[lo * kStoreSlots + (idx < n0 ? idx : kStoreSlotsC + (idx - n0))];
+        ev = idx < n0 ? tile_ev[idx * 64 + lo * kChains] : tile_ev[(idx - n0) * 64 + lo * kChains + 1];
         if (ev.ref != kMarkRef) rr = P.t.ref_rec[ev.ref];
       }
       uint32_t len_incl = rr.n;

@@ -46,7 +46,7 @@ class Hit(C.Structure):
 class Hits(C.Structure):
     _fields_ = [
         ("hits", C.c_void_p), ("n_hits", C.c_int64), ("doc_hit_off", C.c_void_p), ("n_docs", C.c_int64),
-        ("on_device", C.c_int32), ("device", C.c_int32), ("scan_ms", C.c_double), ("opaque", C.c_void_p),
+        ("on_device", C.c_int32), ("device", C.c_int32), ("scan_ms", C.c_double), ("walk_ms", C.c_double), ("opaque", C.c_void_p),
     ]
 
 

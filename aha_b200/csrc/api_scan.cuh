@@ -212,9 +212,14 @@ static int32_t run_char_split(ScanParams p, const DeviceDfa* dd, cudaStream_t st
   p.hits = nullptr;
   fp.hit_cap = 0;
   fp.sp = p;
+  cudaEvent_t evw0 = nullptr, evw1 = nullptr;
   if (nt > 0) {
+    AHA_CUDA(cudaEventCreate(&evw0));
+    AHA_CUDA(cudaEventCreate(&evw1));
+    AHA_CUDA(cudaEventRecord(evw0, st));
     char_walk_kernel<<<n_sm, kFusedWarps * 32, smem, st>>>(sp);
     g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
+    AHA_CUDA(cudaEventRecord(evw1, st));
     AHA_CUDA(cudaGetLastError());
   }
   tile_hits_to_u64_kernel<<<(unsigned)((nt + 1 + 255) / 256), 256, 0, st>>>(sp.tile_hits, nt + 1, hits_u64);
@@ -226,6 +231,13 @@ static int32_t run_char_split(ScanParams p, const DeviceDfa* dd, cudaStream_t st
   AHA_CUDA(cudaMemcpyAsync(&total_hits, tile_prefix + nt, sizeof(total_hits), cudaMemcpyDeviceToHost, st));
   AHA_CUDA(cudaMemcpyAsync(&n_direct, sp.n_direct_list, sizeof(n_direct), cudaMemcpyDeviceToHost, st));
   AHA_CUDA(cudaStreamSynchronize(st));
+  if (evw0) {
+    float wms = 0;
+    AHA_CUDA(cudaEventElapsedTime(&wms, evw0, evw1));
+    res->walk_ms = wms;
+    cudaEventDestroy(evw0);
+    cudaEventDestroy(evw1);
+  }
   // the hit buffer is sized exactly: the walk has already counted
   if (!(p.mode & AHA_COUNT_ONLY)) {
     AHA_CUDA(cudaMallocAsync(&own->dev_hits, (size_t)(total_hits ? total_hits : 1) * sizeof(aha_hit), st));
@@ -642,7 +654,7 @@ int32_t aha_b200_scan(const aha_dfa* d, const uint8_t* text, const int64_t* doc_
   };
 
   int64_t hit_base = 0;
-  double scan_ms = 0;
+  double scan_ms = 0, walk_ms = 0;
   std::vector<int64_t> run_hit_base(n_runs + 1, 0);
   AHA_E2E(stage_in(0));
   for (size_t k = 0; k < n_runs; ++k) {
@@ -659,6 +671,7 @@ int32_t aha_b200_scan(const aha_dfa* d, const uint8_t* text, const int64_t* doc_
     rc = scan_on_device(d, d_text[b], d_off[b], hi - lo, bytes, mode, sep_bits, sep_size, s_run, &part, &pown);
     if (rc) return fail(rc);
     scan_ms += part.scan_ms;
+    walk_ms += part.walk_ms;
     run_hit_base[k] = hit_base;
     if (!count_only && part.n_hits > 0) {
       const size_t need = (size_t)(hit_base + part.n_hits);
@@ -713,6 +726,7 @@ int32_t aha_b200_scan(const aha_dfa* d, const uint8_t* text, const int64_t* doc_
 #undef AHA_E2E
   res->n_hits = hit_base;
   res->scan_ms = scan_ms;
+  res->walk_ms = walk_ms;
   res->device = own->device;
   res->on_device = 0;
   res->hits = static_cast<aha_hit*>(own->host_hits);

@@ -35,6 +35,7 @@ typedef struct aha_hits {
   int32_t on_device;      /* 1: hits/doc_hit_off are device pointers (aha_b200_scan_device)  */
   int32_t device;
   double scan_ms;         /* device time of the scan kernels only (CUDA events)              */
+  double walk_ms;         /* of which the dominant kernel (char_walk_kernel); 0 on other paths */
   void* opaque;
 } aha_hits;
 

@@ -26,6 +26,7 @@ lib LibAhaB200
     on_device : Int32
     device : Int32
     scan_ms : Float64
+    walk_ms : Float64
     opaque : Void*
   end
 

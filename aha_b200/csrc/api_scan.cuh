@@ -176,6 +176,9 @@ static int32_t run_char_split(ScanParams p, const DeviceDfa* dd, cudaStream_t st
   AHA_CUDA(cudaMallocAsync(&sp.store, (size_t)(nt ? nt : 1) * 32 * kStoreSlots * sizeof(CharEvent), st));
   AHA_CUDA(cudaMallocAsync(&sp.tile_meta, (size_t)(nt ? nt : 1) * 32 * kChains * sizeof(uint32_t), st));
   AHA_CUDA(cudaMallocAsync(&sp.tile_hits, (size_t)(nt + 1) * sizeof(uint32_t), st));
+  TileDoc* tile_doc = nullptr;
+  AHA_CUDA(cudaMallocAsync(&tile_doc, (size_t)(nt ? nt : 1) * sizeof(TileDoc), st));
+  sp.tile_doc = tile_doc;
   AHA_CUDA(cudaMallocAsync(&sp.direct_list, (size_t)(nt ? nt : 1) * sizeof(uint32_t), st));
   AHA_CUDA(cudaMallocAsync(&tile_prefix, (size_t)(2 * (nt + 1)) * sizeof(uint64_t), st));
   AHA_CUDA(cudaMallocAsync(&scan_tmp, scan_tmp_bytes ? scan_tmp_bytes : 16, st));
@@ -214,6 +217,8 @@ static int32_t run_char_split(ScanParams p, const DeviceDfa* dd, cudaStream_t st
   fp.sp = p;
   cudaEvent_t evw0 = nullptr, evw1 = nullptr;
   if (nt > 0) {
+    tile_doc_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(p.doc_off, p.n_docs, fp.tile, nt, tile_doc);
+    g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
     AHA_CUDA(cudaEventCreate(&evw0));
     AHA_CUDA(cudaEventCreate(&evw1));
     AHA_CUDA(cudaEventRecord(evw0, st));
@@ -264,6 +269,7 @@ static int32_t run_char_split(ScanParams p, const DeviceDfa* dd, cudaStream_t st
   AHA_CUDA(cudaFreeAsync(sp.store, st));
   AHA_CUDA(cudaFreeAsync(sp.tile_meta, st));
   AHA_CUDA(cudaFreeAsync(sp.tile_hits, st));
+  AHA_CUDA(cudaFreeAsync(tile_doc, st));
   AHA_CUDA(cudaFreeAsync(sp.direct_list, st));
   AHA_CUDA(cudaFreeAsync(tile_prefix, st));
   AHA_CUDA(cudaFreeAsync(scan_tmp, st));

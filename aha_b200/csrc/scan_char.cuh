@@ -203,9 +203,10 @@ __device__ __forceinline__ ProbeResult char_probe(const CharSmem& S, uint32_t r,
   const uint32_t c1 = S.check[slot1], c2 = S.check[slot2];
   const bool hit1 = c1 == s, hit2 = c2 == f1;
   q.hit = hit1 || hit2;
-  q.slotv = hit1 ? slot1 : slot2;
+  const uint32_t slot12 = hit1 ? slot1 : slot2;
   q.v = r & 0xFFFFu;  // the root entry in val[] format (fail = 0)
-  if (q.hit) q.v = S.val[q.slotv];
+  if (q.hit) q.v = S.val[slot12];
+  q.slotv = q.hit ? slot12 : S.m + q.cid;  // what fires, as a ref_rec[] index
   q.rare = !q.hit && deep && q.cid != 0;
   return q;
 }
@@ -238,7 +239,7 @@ constexpr int kEvSlotsC = kEvSlots / kChains;  // ring slots per sub-chunk (>= b
 // kStride = ring slots per sub-chunk; kBounded: drop (but count) events beyond kStride instead of relying on
 // kStride >= bytes of a sub-chunk, and lay the slots out slot-major (event i of sub-chunk c at my_ev[i * 64 + c]: the
 // i-th events of all 64 sub-chunks of a tile share sectors, so the store is written and read densely).
-template <bool kChars, int kStride, bool kBounded, class OnDoc>
+template <bool kChars, int kStride, bool kBounded, bool kLean = false, class OnDoc>
 __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanParams& p, const uint8_t* sbuf, int64_t origin, int64_t a,
                                                int64_t b, int32_t sub, int32_t stage_end, int32_t warmc, bool one_doc, int64_t cd,
                                                int64_t cdoc_start, int64_t cdoc_end, const uint32_t (&lead0)[kChains], CharEvent* my_ev,
@@ -307,16 +308,20 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
     if (fire) {
       if (!kBounded || n_ev[c] < (uint32_t)kStride)
         my_ev[kBounded ? n_ev[c] * 64 + c : c * kStride + n_ev[c]] = CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : last + ebase[c], ref};
-      const uint32_t cnt = (S.mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
-      n_hit[c] += cnt;
-      lookup = lookup || cnt == 0u;
+      if (!kLean) {
+        const uint32_t cnt = (S.mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
+        n_hit[c] += cnt;
+        lookup = lookup || cnt == 0u;
+      }
       ++n_ev[c];
     }
   };
 
   // one character of EVERY sub-chunk (warp converged): probes first, then the rare continuation behind a single
   // vote, then the state update, then the events behind a single branch
-  auto multi_step = [&](const uint32_t (&r)[kChains], const int32_t (&cs)[kChains], int32_t len) {
+  // rl[c] = offset of the character's last byte relative to a_seg[c], span[c] = rb[c] - a_seg[c] (hoisted by the caller)
+  auto multi_step = [&](const uint32_t (&r)[kChains], const int32_t (&cs)[kChains], int32_t len, const int32_t (&rl)[kChains],
+                        const uint32_t (&span)[kChains]) {
     ProbeResult q[kChains];
     bool any_rare = false;
 #pragma unroll
@@ -339,21 +344,23 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
       s[c] = v & 0x7FFFu;
       f1[c] = (v >> 16) & 0x7FFFu;
       deep[c] = (v >> 31) != 0u;
-      if (kChars) k[c] += (cs[c] >= a_seg[c]) ? 1u : 0u;
-      fire[c] = (v & 0x8000u) && (uint32_t)(cs[c] + len - 1 - a_seg[c]) < (uint32_t)(rb[c] - a_seg[c]);
+      if (kChars) k[c] += (rl[c] >= len - 1) ? 1u : 0u;
+      fire[c] = (uint32_t)rl[c] < span[c] && (v & 0x8000u) != 0u;
       any_fire = any_fire || fire[c];
     }
     if (any_fire) {
 #pragma unroll
       for (int c = 0; c < kChains; ++c) {
         if (fire[c]) {
-          const uint32_t ref = q[c].hit ? q[c].slotv : S.m + q[c].cid;
+          const uint32_t ref = q[c].slotv;
           if (!kBounded || n_ev[c] < (uint32_t)kStride)
             my_ev[kBounded ? n_ev[c] * 64 + c : c * kStride + n_ev[c]] =
                 CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : cs[c] + len - 1 + ebase[c], ref};
-          const uint32_t cnt = (S.mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
-          n_hit[c] += cnt;
-          lookup = lookup || cnt == 0u;
+          if (!kLean) {
+            const uint32_t cnt = (S.mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
+            n_hit[c] += cnt;
+            lookup = lookup || cnt == 0u;
+          }
           ++n_ev[c];
         }
       }
@@ -391,38 +398,50 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
         return rel < S.n3 ? S.root3[rel] : 0u;
       };
       // rolled on purpose: A:B:C is a 96-bit shift register, one copy of the step keeps the loop in the instruction cache
+      int32_t rl0[kChains];
+      uint32_t span[kChains];
+#pragma unroll
+      for (int c = 0; c < kChains; ++c) {
+        rl0[c] = pos[c] + 2 - a_seg[c];
+        span[c] = (uint32_t)(rb[c] - a_seg[c]);
+      }
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         uint32_t r[kChains];
-        int32_t cs[kChains];
+        int32_t cs[kChains], rl[kChains];
 #pragma unroll
         for (int c = 0; c < kChains; ++c) {
           r[c] = root3(A[c]);
           cs[c] = pos[c] + 3 * u;
+          rl[c] = rl0[c] + 3 * u;
           A[c] = __funnelshift_r(A[c], B[c], 24);
           B[c] = __funnelshift_r(B[c], C[c], 24);
           C[c] >>= 24;
         }
-        multi_step(r, cs, 3);
+        multi_step(r, cs, 3, rl, span);
       }
 #pragma unroll
       for (int c = 0; c < kChains; ++c)
         if (!done[c]) pos[c] += 12;
     } else if (__all_sync(kFull, can1)) {
       // twelve ASCII characters per sub-chunk
+      uint32_t span[kChains];
+#pragma unroll
+      for (int c = 0; c < kChains; ++c) span[c] = (uint32_t)(rb[c] - a_seg[c]);
 #pragma unroll 1
       for (int i = 0; i < 12; ++i) {
         uint32_t r[kChains];
-        int32_t cs[kChains];
+        int32_t cs[kChains], rl[kChains];
 #pragma unroll
         for (int c = 0; c < kChains; ++c) {
           r[c] = S.root[A[c] & 0xFFu];
           cs[c] = pos[c] + i;
+          rl[c] = cs[c] - a_seg[c];
           A[c] = __funnelshift_r(A[c], B[c], 8);
           B[c] = __funnelshift_r(B[c], C[c], 8);
           C[c] >>= 8;
         }
-        multi_step(r, cs, 1);
+        multi_step(r, cs, 1, rl, span);
       }
 #pragma unroll
       for (int c = 0; c < kChains; ++c)

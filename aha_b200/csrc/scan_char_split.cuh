@@ -21,8 +21,17 @@ constexpr int kStoreSlots = kStoreSlotsC * kChains;   // per lane
 constexpr uint32_t kMarkRef = 0xFFFFFFFFu;            // marker event: `end` holds a document index
 constexpr uint32_t kTileDirect = 0x80000000u;         // tile_hits[] flag: the tile is delivered by char_direct_kernel
 
+// which document a tile starts in: looked up once per tile by tile_doc_kernel, so that the walkers (whose
+// consecutive tiles are megabytes apart) load one record a tile ahead instead of running a binary search
+struct alignas(16) TileDoc {
+  int64_t doc_start;
+  int32_t doc_len;   // documents are < 2^31 bytes
+  int32_t doc;
+};
+
 struct SplitParams {
   CharParams c;
+  const TileDoc* tile_doc;   // [n_tiles]
   CharEvent* store;          // [n_tiles][kStoreSlotsC][32 lanes][kChains]: slot-major, event i of every sub-chunk side by side
   uint32_t* tile_meta;       // [n_tiles][32][kChains]  hits:16 | events:16 of a sub-chunk
   uint32_t* tile_hits;       // [n_tiles + 1] hits of the tile | kTileDirect
@@ -30,6 +39,14 @@ struct SplitParams {
   uint32_t* direct_list;     // [n_tiles] tiles for char_direct_kernel
   unsigned int* n_direct_list;
 };
+
+__global__ void tile_doc_kernel(const int64_t* doc_off, int64_t n_docs, int64_t tile, int64_t n_tiles, TileDoc* out) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_tiles) return;
+  const int64_t d = last_le(doc_off, n_docs, t * tile);
+  const int64_t ds = doc_off[d];
+  out[t] = TileDoc{ds, (int32_t)(doc_off[d + 1] - ds), (int32_t)d};
+}
 
 __global__ void tile_hits_to_u64_kernel(const uint32_t* tile_hits, int64_t n, uint64_t* out) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -77,15 +94,13 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
   const int32_t warmc = (int32_t)p.warm;
   const int32_t sub = F.chunk / kChains;
   uint32_t parity = 0;
-  int64_t cd = 0, cdoc_start = 0, cdoc_end = -1;
 
-  unsigned int ticket_ahead = 0;  // lane 0: requested one tile early, the atomic's latency is never waited for
-  if (lane == 0) ticket_ahead = atomicAdd(F.ticket, 1u);
-  auto next_tile = [&]() -> unsigned int {
-    unsigned int nt = __shfl_sync(0xffffffffu, ticket_ahead, 0);
-    if (lane == 0 && (int64_t)nt < F.n_tiles) ticket_ahead = atomicAdd(F.ticket, 1u);
-    if ((int64_t)nt < F.n_tiles) {
-      const int64_t tile_start = (int64_t)nt * F.tile;
+  // Tiles are dealt round-robin (tile t -> warp t mod W): every tile costs about the same, nothing orders them, and
+  // a warp knows its next tile early enough to have that tile's document record in registers before it needs it.
+  const int64_t W = (int64_t)gridDim.x * kFusedWarps;
+  auto stage_tile = [&](int64_t nt) {
+    if (nt < F.n_tiles) {
+      const int64_t tile_start = nt * F.tile;
       const int64_t tile_end = min(tile_start + (int64_t)F.tile, p.total);
       const int64_t org = max((int64_t)0, tile_start - (int64_t)F.w16);
       const int64_t want_end = min(p.total, tile_end + 16);
@@ -96,20 +111,20 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
       }
       for (int64_t i = bulk_end + lane; i < want_end; i += 32) sbuf[i - org] = p.text[i];
     }
-    return nt;
   };
+  int64_t t = (int64_t)blockIdx.x * kFusedWarps + warp;
+  TileDoc td_next = TileDoc{0, 0, 0};
+  if (t < F.n_tiles) td_next = Q.tile_doc[t];
+  stage_tile(t);
 
-  for (unsigned int t = next_tile(); (int64_t)t < F.n_tiles;) {
-    const int64_t tile_start = (int64_t)t * F.tile;
+  while (t < F.n_tiles) {
+    const int64_t tile_start = t * F.tile;
     const int64_t tile_end = min(tile_start + (int64_t)F.tile, p.total);
     const int64_t origin = max((int64_t)0, tile_start - (int64_t)F.w16);
     const int64_t want_end = min(p.total, tile_end + 16);
     const int64_t bulk_end = origin + ((want_end - origin) & ~(int64_t)15);
-    if (!(tile_start >= cdoc_start && tile_start < cdoc_end)) {
-      cd = last_le(p.doc_off, p.n_docs, tile_start);
-      cdoc_start = p.doc_off[cd];
-      cdoc_end = p.doc_off[cd + 1];
-    }
+    const int64_t cd = td_next.doc, cdoc_start = td_next.doc_start, cdoc_end = td_next.doc_start + td_next.doc_len;
+    if (t + W < F.n_tiles) td_next = Q.tile_doc[t + W];  // used a whole tile later
     const bool one_doc = cdoc_start <= tile_start && cdoc_end >= tile_end;
     uint64_t tl = 0, dlb = 0;
     if (chars) {
@@ -147,13 +162,13 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
       ++n_ev[c];
     };
     const int32_t stage_end = (int32_t)(want_end - origin);
-    const bool ok = chars ? char_tile_walk<true, kStoreSlotsC, true>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start,
+    const bool ok = chars ? char_tile_walk<true, kStoreSlotsC, true, true>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start,
                                                                      cdoc_end, lead0, my_ev, n_ev, n_hit, lookup, on_doc)
-                          : char_tile_walk<false, kStoreSlotsC, true>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start,
+                          : char_tile_walk<false, kStoreSlotsC, true, true>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start,
                                                                       cdoc_end, lead0, my_ev, n_ev, n_hit, lookup, on_doc);
     const bool bad = __any_sync(0xffffffffu, !ok);
     const bool over = __any_sync(0xffffffffu, n_ev[0] > (uint32_t)kStoreSlotsC || n_ev[1] > (uint32_t)kStoreSlotsC);
-    uint32_t n_hits;
+    uint32_t n_hits = 0;
     if (bad || over) {
       // the expansion cannot use this tile's events: count with the byte automaton, deliver in char_direct_kernel
       CountSink cs;
@@ -161,7 +176,35 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
       n_hits = cs.n;
       n_hit[0] = cs.n;
       n_hit[1] = 0;
-    } else {
+    }
+    // the staged text is not needed any more: the next tile's bulk copy flies while this tile's counts are settled
+    __syncwarp();
+    fence_proxy_async();  // reads of sbuf are done before the bulk copy overwrites it
+    stage_tile(t + W);
+    if (!(bad || over)) {
+      // hits per sub-chunk: the walk only stored events; the lane reads its own back (both sub-chunks of a slot share
+      // 16 bytes) and looks the hit counts up in the 2-bit table -- a few batched loads per tile instead of a table
+      // lookup inside the walk at every event
+      const uint32_t mx = max(n_ev[0], n_ev[1]);
+      for (uint32_t i0 = 0; i0 < mx; i0 += 4) {
+        uint4 e[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (i0 + j < mx) e[j] = *reinterpret_cast<const uint4*>(my_ev + (size_t)(i0 + j) * 64);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (i0 + j < n_ev[0] && e[j].y != kMarkRef) {
+            const uint32_t cnt = (S.mbits[e[j].y >> 4] >> ((e[j].y & 15u) * 2u)) & 3u;
+            n_hit[0] += cnt;
+            lookup = lookup || cnt == 0u;
+          }
+          if (i0 + j < n_ev[1] && e[j].w != kMarkRef) {
+            const uint32_t cnt = (S.mbits[e[j].w >> 4] >> ((e[j].w & 15u) * 2u)) & 3u;
+            n_hit[1] += cnt;
+            lookup = lookup || cnt == 0u;
+          }
+        }
+      }
       if (lookup) {  // some output list is longer than the 2-bit table can say
 #pragma unroll
         for (int c = 0; c < kChains; ++c) {
@@ -184,9 +227,7 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
       Q.tile_hits[t] = T | ((bad || over) ? kTileDirect : 0u);
       if (bad || over) Q.direct_list[atomicAdd(Q.n_direct_list, 1u)] = t;
     }
-    __syncwarp();
-    fence_proxy_async();  // reads of sbuf are done before the next bulk copy overwrites it
-    t = next_tile();
+    t += W;
   }
 }
 

@@ -348,7 +348,15 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
       fire[c] = (uint32_t)rl[c] < span[c] && (v & 0x8000u) != 0u;
       any_fire = any_fire || fire[c];
     }
-    if (any_fire) {
+    if (kLean) {
+      // branch-free: a handful of predicated instructions per sub-chunk cost less than the divergent branches around them
+#pragma unroll
+      for (int c = 0; c < kChains; ++c) {
+        if (fire[c] && n_ev[c] < (uint32_t)kStride)
+          my_ev[n_ev[c] * 64 + c] = CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : cs[c] + len - 1 + ebase[c], q[c].slotv};
+        n_ev[c] += fire[c] ? 1u : 0u;
+      }
+    } else if (any_fire) {
 #pragma unroll
       for (int c = 0; c < kChains; ++c) {
         if (fire[c]) {

@@ -267,11 +267,12 @@ inline CharTableHost build_char_table(const BlobHeader& h, const uint8_t* blob, 
   T.n_root = 256;
   for (int c = 0; c < 3; ++c) {
     T.off[c] = T.n_root;
-    if (lo[c] == 0xFFFFFFFFu) continue;
-    T.lo[c] = lo[c] & ~63u;  // multiple of 64: the kernel folds it into the decode (scan_char.cuh)
-    T.n[c] = hi[c] - T.lo[c] + 1;
-    if (T.n[c] > (1u << 20)) { T.why = "character range too wide for the root table"; return T; }
-    T.n_root += T.n[c];
+    if (lo[c] != 0xFFFFFFFFu) {
+      T.lo[c] = lo[c] & ~63u;  // multiple of 64: the kernel folds it into the decode (scan_char.cuh)
+      T.n[c] = hi[c] - T.lo[c] + 1;
+      if (T.n[c] > (1u << 20)) { T.why = "character range too wide for the root table"; return T; }
+    }
+    T.n_root += T.n[c] + 1;  // one zero entry behind every range: the kernel clamps an out-of-range index to it
   }
   if ((size_t)T.n_root * 4 > smem_budget / 2) { T.why = "character range too wide for the root table"; return T; }
   // 4. effective state: nearest fail-ancestor (self included) that has children; 0 = root

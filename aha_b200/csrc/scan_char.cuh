@@ -403,9 +403,9 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
         const uint32_t wm = w & 0x3F3F0Fu;
         const uint32_t h = __dp4a(wm, 0x00000140u, S.neg_lo3_64);
         const uint32_t rel = h * 64u + (wm >> 16);
-        return rel < S.n3 ? S.root3[rel] : 0u;
+        return S.root3[min(rel, S.n3)];  // root3[n3] = 0 (char_table.hpp)
       };
-      // rolled on purpose: A:B:C is a 96-bit shift register, one copy of the step keeps the loop in the instruction cache
+      // twelve bytes = three words: character u sits at a fixed place in A:B:C, one funnel shift each
       int32_t rl0[kChains];
       uint32_t span[kChains];
 #pragma unroll
@@ -419,12 +419,10 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
         int32_t cs[kChains], rl[kChains];
 #pragma unroll
         for (int c = 0; c < kChains; ++c) {
-          r[c] = root3(A[c]);
+          const uint32_t w = u == 0 ? A[c] : (u == 1 ? __funnelshift_r(A[c], B[c], 24) : (u == 2 ? __funnelshift_r(B[c], C[c], 16) : C[c] >> 8));
+          r[c] = root3(w);
           cs[c] = pos[c] + 3 * u;
           rl[c] = rl0[c] + 3 * u;
-          A[c] = __funnelshift_r(A[c], B[c], 24);
-          B[c] = __funnelshift_r(B[c], C[c], 24);
-          C[c] >>= 24;
         }
         multi_step(r, cs, 3, rl, span);
       }

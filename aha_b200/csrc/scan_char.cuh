@@ -375,12 +375,15 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
     }
   };
 
-  for (;;) {
-    if (__any_sync(kFull, !ok)) return false;
+  if (__any_sync(kFull, !ok)) return false;
+  {
     bool all_done = true;
 #pragma unroll
     for (int c = 0; c < kChains; ++c) all_done = all_done && done[c];
-    if (__all_sync(kFull, all_done)) break;
+    if (__all_sync(kFull, all_done)) { lookup_out = lookup; return true; }
+  }
+  // (ok and done[] only change in the one-unit branch below: that is where they are voted on)
+  for (;;) {
     uint32_t A[kChains], B[kChains], C[kChains];
     bool can3 = true, can1 = true;
 #pragma unroll
@@ -519,6 +522,11 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
         }
         if (done[c]) pos[c] = rb[c];
       }
+      if (__any_sync(kFull, !ok)) return false;
+      bool all_done = true;
+#pragma unroll
+      for (int c = 0; c < kChains; ++c) all_done = all_done && done[c];
+      if (__all_sync(kFull, all_done)) break;
     }
   }
   lookup_out = lookup;

@@ -236,6 +236,8 @@ constexpr int kEvSlotsC = kEvSlots / kChains;  // ring slots per sub-chunk (>= b
 // Events of sub-chunk c go to my_ev[c * kEvSlotsC ...); n_ev[c] counts all of them; multi_mask bit (c * kEvCapC + i)
 // = event i of sub-chunk c reports more than one key.  Returns false (warp-uniform) when the text is not
 // structurally valid UTF-8: the caller rescans the tile with the byte automaton.
+// kLean (the split pipeline): events only -- no hit counting in the walk -- and n_ev[] counts in steps of 64 (the
+// slot-major element stride), on_doc included; the caller divides when the walk returns.
 // kStride = ring slots per sub-chunk; kBounded: drop (but count) events beyond kStride instead of relying on
 // kStride >= bytes of a sub-chunk, and lay the slots out slot-major (event i of sub-chunk c at my_ev[i * 64 + c]: the
 // i-th events of all 64 sub-chunks of a tile share sectors, so the store is written and read densely).
@@ -306,14 +308,17 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
     if (kChars) k[c] += (cs >= a_seg[c]) ? 1u : 0u;
     const bool fire = (v & 0x8000u) && (uint32_t)(last - a_seg[c]) < (uint32_t)(rb[c] - a_seg[c]);
     if (fire) {
-      if (!kBounded || n_ev[c] < (uint32_t)kStride)
-        my_ev[kBounded ? n_ev[c] * 64 + c : c * kStride + n_ev[c]] = CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : last + ebase[c], ref};
-      if (!kLean) {
+      if (kLean) {  // n_ev[c] counts in steps of 64 = the slot-major element stride (see multi_step)
+        if (n_ev[c] < (uint32_t)kStride * 64u) my_ev[n_ev[c] + c] = CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : last + ebase[c], ref};
+        n_ev[c] += 64u;
+      } else {
+        if (!kBounded || n_ev[c] < (uint32_t)kStride)
+          my_ev[kBounded ? n_ev[c] * 64 + c : c * kStride + n_ev[c]] = CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : last + ebase[c], ref};
         const uint32_t cnt = (S.mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
         n_hit[c] += cnt;
         lookup = lookup || cnt == 0u;
+        ++n_ev[c];
       }
-      ++n_ev[c];
     }
   };
 
@@ -345,16 +350,20 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
       f1[c] = (v >> 16) & 0x7FFFu;
       deep[c] = (v >> 31) != 0u;
       if (kChars) k[c] += (rl[c] >= len - 1) ? 1u : 0u;
-      fire[c] = (uint32_t)rl[c] < span[c] && (v & 0x8000u) != 0u;
+      // the fires bit as a sign test of v << 16: the shift can run on the multiply pipe, the test folds into the range compare
+      int32_t vs;
+      asm("shl.b32 %0, %1, 16;" : "=r"(vs) : "r"(v));
+      fire[c] = (uint32_t)rl[c] < span[c] && vs < 0;
       any_fire = any_fire || fire[c];
     }
     if (kLean) {
       // branch-free: a handful of predicated instructions per sub-chunk cost less than the divergent branches around them
 #pragma unroll
       for (int c = 0; c < kChains; ++c) {
-        if (fire[c] && n_ev[c] < (uint32_t)kStride)
-          my_ev[n_ev[c] * 64 + c] = CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : cs[c] + len - 1 + ebase[c], q[c].slotv};
-        n_ev[c] += fire[c] ? 1u : 0u;
+        // n_ev[c] is kept pre-multiplied by the slot-major element stride: the address is one multiply-add away
+        if (fire[c] && n_ev[c] < (uint32_t)kStride * 64u)
+          my_ev[n_ev[c] + c] = CharEvent{kChars ? (int32_t)(lead[c] + k[c]) : cs[c] + len - 1 + ebase[c], q[c].slotv};
+        if (fire[c]) n_ev[c] += 64u;
       }
     } else if (any_fire) {
 #pragma unroll

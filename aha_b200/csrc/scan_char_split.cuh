@@ -158,14 +158,16 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
     uint32_t n_ev[kChains] = {0, 0}, n_hit[kChains] = {0, 0};
     bool lookup = false;
     auto on_doc = [&](int c, int64_t d, uint32_t nev) {  // marker event in the stream of sub-chunk c
-      if (nev < (uint32_t)kStoreSlotsC) my_ev[nev * 64 + c] = CharEvent{(int32_t)d, kMarkRef};
-      ++n_ev[c];
+      if (nev < (uint32_t)kStoreSlotsC * 64u) my_ev[nev + c] = CharEvent{(int32_t)d, kMarkRef};  // nev in steps of 64 (kLean)
+      n_ev[c] += 64u;
     };
     const int32_t stage_end = (int32_t)(want_end - origin);
     const bool ok = chars ? char_tile_walk<true, kStoreSlotsC, true, true>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start,
                                                                      cdoc_end, lead0, my_ev, n_ev, n_hit, lookup, on_doc)
                           : char_tile_walk<false, kStoreSlotsC, true, true>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start,
                                                                       cdoc_end, lead0, my_ev, n_ev, n_hit, lookup, on_doc);
+    n_ev[0] >>= 6;
+    n_ev[1] >>= 6;
     const bool bad = __any_sync(0xffffffffu, !ok);
     const bool over = __any_sync(0xffffffffu, n_ev[0] > (uint32_t)kStoreSlotsC || n_ev[1] > (uint32_t)kStoreSlotsC);
     uint32_t n_hits = 0;

@@ -90,6 +90,32 @@ class Cedar:
             self._ac = AC.compile(self)
         return self._ac.scan_batch(docs, TRIE_LONGEST | (IGNORE_CASE if ignore_case else 0), sep)
 
+    def gsub(self, text, ignore_case=False, sep=None, block=None):
+        """CedarX#gsub(String, ignore_case, sep) { |hit| replacement } (cedar.cr:1123-1177).
+
+        The reference's gsub loop is its match_longest loop (cedar.cr:1098-1121) with `sb <<` on every branch: each
+        character is copied once, except inside a hit, where the block's return value goes instead.  So the string
+        is rebuilt on the host from the GPU's TRIE_LONGEST hit stream.  `block` receives (start, end, value)."""
+        return self.gsub_batch([text], ignore_case, sep, block)[0]
+
+    def gsub_batch(self, docs, ignore_case=False, sep=None, block=None):
+        if block is None:
+            raise TypeError("gsub needs a block: hit -> replacement")
+        res = self.match_longest_batch(docs, ignore_case, sep)
+        hits, off = res.hits(), res.doc_hit_off()
+        out = []
+        for d, doc in enumerate(docs):
+            s = doc if isinstance(doc, str) else bytes(doc).decode("utf-8")
+            sb, pos = [], 0
+            for h in hits[int(off[d]):int(off[d + 1])]:
+                start, end = int(h["start"]), int(h["end"])
+                sb.append(s[pos:start])
+                sb.append(str(block((start, end, int(h["value"])))))
+                pos = end
+            sb.append(s[pos:])
+            out.append("".join(sb))
+        return out
+
     def compiled_arrays(self):
         """Runs ACX.compile(da) (ac.cr:71-112); returns copies of (nodes, fails, output, key_lens)."""
         nodes, fails, output, kl = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()

@@ -18,6 +18,7 @@ namespace aha {
 
 constexpr int kStoreSlotsC = 16;                      // event slots per sub-chunk in the store (more: direct pass)
 constexpr int kStoreSlots = kStoreSlotsC * kChains;   // per lane
+constexpr int kExpandRounds = 4;                     // rounds of 32 events a warp of char_expand_kernel keeps in flight
 constexpr uint32_t kMarkRef = 0xFFFFFFFFu;            // marker event: `end` holds a document index
 constexpr uint32_t kTileDirect = 0x80000000u;         // tile_hits[] flag: the tile is delivered by char_direct_kernel
 
@@ -256,35 +257,51 @@ __global__ void __launch_bounds__(256) char_expand_kernel(const __grid_constant_
     const unsigned long long prefix = Q.tile_prefix[t];
     const CharEvent* tile_ev = Q.store + (size_t)t * 32 * kStoreSlots;
     uint32_t run = 0;
-    for (uint32_t base = 0; base < E; base += 32) {
-      const uint32_t i = base + lane;
-      uint32_t lo = 0;
+    // kExpandRounds rounds of 32 events in flight: all event loads first, then all ref_rec loads, then the ordered stores
+    for (uint32_t base = 0; base < E; base += 32 * kExpandRounds) {
+      CharEvent ev[kExpandRounds];
+      RefRec rr[kExpandRounds];
 #pragma unroll
-      for (int step = 16; step > 0; step >>= 1) {
-        const uint32_t cand = lo + step;
-        const uint32_t ex = __shfl_sync(0xffffffffu, ev_excl, cand & 31);
-        if (cand < 32 && ex <= i) lo = cand;
+      for (int r = 0; r < kExpandRounds; ++r) {
+        ev[r] = CharEvent{0, kMarkRef};
+        if (base + r * 32 < E) {  // warp-uniform
+          const uint32_t i = base + r * 32 + lane;
+          uint32_t lo = 0;
+#pragma unroll
+          for (int step = 16; step > 0; step >>= 1) {
+            const uint32_t cand = lo + step;
+            const uint32_t ex = __shfl_sync(0xffffffffu, ev_excl, cand & 31);
+            if (cand < 32 && ex <= i) lo = cand;
+          }
+          const uint32_t ex = __shfl_sync(0xffffffffu, ev_excl, lo);
+          const uint32_t n0 = __shfl_sync(0xffffffffu, n_ev0, lo);
+          if (i < E) {
+            const uint32_t idx = i - ex;
+            ev[r] = idx < n0 ? tile_ev[idx * 64 + lo * kChains] : tile_ev[(idx - n0) * 64 + lo * kChains + 1];
+          }
+        }
       }
-      const uint32_t ex = __shfl_sync(0xffffffffu, ev_excl, lo);
-      const uint32_t n0 = __shfl_sync(0xffffffffu, n_ev0, lo);
-      CharEvent ev{0, kMarkRef};
-      RefRec rr{0, 0, 0, 0};
-      if (i < E) {
-        const uint32_t idx = i - ex;
-        ev = idx < n0 ? tile_ev[idx * 64 + lo * kChains] : tile_ev[(idx - n0) * 64 + lo * kChains + 1];
-        if (ev.ref != kMarkRef) rr = P.t.ref_rec[ev.ref];
+#pragma unroll
+      for (int r = 0; r < kExpandRounds; ++r) {
+        rr[r] = RefRec{0, 0, 0, 0};
+        if (ev[r].ref != kMarkRef) rr[r] = P.t.ref_rec[ev[r].ref];
       }
-      uint32_t len_incl = rr.n;
-      for (int o = 1; o < 32; o <<= 1) {
-        uint32_t v = __shfl_up_sync(0xffffffffu, len_incl, o);
-        if (lane >= o) len_incl += v;
+#pragma unroll
+      for (int r = 0; r < kExpandRounds; ++r) {
+        if (base + r * 32 < E) {  // warp-uniform
+          uint32_t len_incl = rr[r].n;
+          for (int o = 1; o < 32; o <<= 1) {
+            uint32_t v = __shfl_up_sync(0xffffffffu, len_incl, o);
+            if (lane >= o) len_incl += v;
+          }
+          const int64_t at = (int64_t)prefix + run + (len_incl - rr[r].n);
+          if (base + r * 32 + lane < E) {
+            if (ev[r].ref == kMarkRef) p.doc_hit_off[ev[r].end] = at;
+            else if (p.hits) expand_event(p, rr[r], ev[r].end, chars, p.hits, at, P.f.hit_cap);
+          }
+          run += __shfl_sync(0xffffffffu, len_incl, 31);
+        }
       }
-      const int64_t at = (int64_t)prefix + run + (len_incl - rr.n);
-      if (i < E) {
-        if (ev.ref == kMarkRef) p.doc_hit_off[ev.end] = at;
-        else if (p.hits) expand_event(p, rr, ev.end, chars, p.hits, at, P.f.hit_cap);
-      }
-      run += __shfl_sync(0xffffffffu, len_incl, 31);
     }
   }
 }

@@ -160,6 +160,36 @@ class Cedar:
         buf = C.string_at(self._L.orc_trie_hits(), n * 12) if n else b""
         return np.frombuffer(buf, dtype=HIT_DTYPE).copy()
 
+    def gsub(self, text, ignore_case=False, sep=None, block=None):
+        """CedarX#gsub(String, ignore_case, sep) { |hit| ... } (cedar.cr:1123-1177), restated loop by loop.
+
+        `prefix(s + offset, ...)` with the longest-wins rule of cedar.cr:1153-1160 is played by the C restatement of
+        match_longest (cedar.cr:1098-1121) run on the suffix: at a non-separator offset its first iteration is that
+        very computation, so the longest prefix match is its first hit iff that hit starts at 0.  O(n^2): tests only."""
+        s = text if isinstance(text, str) else bytes(text).decode("utf-8")
+        seps = None if sep is None else set(c if isinstance(c, str) else chr(c) for c in sep)
+        sb, offset = [], 0
+        while offset < len(s):
+            if seps is not None:
+                while offset < len(s) and s[offset] in seps:  # cedar.cr:1148-1151
+                    sb.append(s[offset])
+                    offset += 1
+                if offset >= len(s):
+                    break
+            h = self.match_longest(s[offset:], ignore_case, sep)
+            last_vk, last_char_num = (int(h[0]["value"]), int(h[0]["end"])) if len(h) and h[0]["start"] == 0 else (0, 0)
+            if last_char_num == 0:  # cedar.cr:1161-1171
+                sb.append(s[offset])
+                offset += 1
+                if seps is not None:
+                    while offset < len(s) and s[offset] not in seps:
+                        sb.append(s[offset])
+                        offset += 1
+            else:  # cedar.cr:1172-1176
+                sb.append(str(block((offset, offset + last_char_num, last_vk))))
+                offset += last_char_num
+        return "".join(sb)
+
 
 class AC:
     """Aha::AC (ac.cr)."""

@@ -129,6 +129,21 @@ module Aha
       m = LibAhaB200::TRIE_LONGEST | (ignore_case ? LibAhaB200::IGNORE_CASE : 0_u32)
       scan_batch([seq.to_slice], m, sep) { |_, h| yield h }
     end
+
+    # CedarX#gsub(String, ignore_case, sep) { |hit| replacement } (cedar.cr:1123-1177): the reference loop is the
+    # match_longest loop with `sb <<` on every branch, so the string is rebuilt from the GPU's hit stream.
+    def trie_gsub(seq : String, ignore_case = false, sep : BitArray? = nil, &block)
+      chars = seq.chars
+      String.build do |sb|
+        pos = 0
+        trie_match_longest(seq, ignore_case, sep) do |h|
+          (pos...h.start).each { |i| sb << chars[i] }
+          sb << (yield h)
+          pos = h.end
+        end
+        (pos...chars.size).each { |i| sb << chars[i] }
+      end
+    end
   end
 
   # Reopened: the ivars of ac.cr:35-39 and the protected getters of cedar.cr:147-148 are reachable from inside.

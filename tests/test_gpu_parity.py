@@ -190,6 +190,31 @@ def test_cedar_match_longest_spec_vectors():  # spec/cedar_match_spec.cr:4-30, 5
     assert got == [(0, 4, "Ruby"), (20, 24, "ruby")]
 
 
+def test_cedar_gsub_spec_vectors():  # spec/cedar_match_spec.cr:32-49, 65-81
+    t = _trie3()
+    names = {"ruby": "crystal", "Ruby": "Crystal"}
+    block = lambda m: names.get(t[m[2]], "Unknown")  # noqa: E731
+    assert t.gsub("Ruby on ruby rub", True, block=block) == "Crystal on crystal Unknown"
+    assert t.gsub("Ruby rRuby on rubyx ruby", True, sep=[" "], block=block) == "Crystal rRuby on rubyx crystal"
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_cedar_gsub_random(seed):
+    rng = random.Random(100 + seed)
+    letters = "abAB cCdé日本Я" if seed % 2 else "abAB "
+    words = list(dict.fromkeys("".join(rng.choice(letters.replace(" ", "")) for _ in range(rng.randint(1, 4))) for _ in range(60)))
+    gt, ot = aha_b200.Cedar(), O.Cedar()
+    for w in words:
+        assert gt.insert(w) == ot.insert(w)
+    docs = ["".join(rng.choice(letters) for _ in range(rng.randint(0, 120))) for _ in range(12)] + ["", " ", "a", "  a  "]
+    block = lambda m: "<%d:%d>" % (m[2], m[1] - m[0])  # noqa: E731
+    for icase in (False, True):
+        for sep in (None, [" "]):
+            got = gt.gsub_batch(docs, icase, sep, block)
+            want = [ot.gsub(d, icase, sep, block) for d in docs]
+            assert got == want
+
+
 @pytest.mark.parametrize("seed", range(6))
 def test_cedar_match_longest_random(seed):
     rng = random.Random(seed)

@@ -72,6 +72,21 @@ def test_cedar_match_sep():  # spec/cedar_match_spec.cr:51-63
         assert got == [(0, 4, "Ruby"), (20, 24, "ruby")]
 
 
+def _crystal_block(t):
+    names = {"ruby": "crystal", "Ruby": "Crystal"}
+    return lambda m: names.get(t[m[2]], "Unknown")
+
+
+def test_cedar_gsub():  # spec/cedar_match_spec.cr:32-49
+    t = _trie()
+    assert t.gsub("Ruby on ruby rub", True, block=_crystal_block(t)) == "Crystal on crystal Unknown"
+
+
+def test_cedar_gsub_sep():  # spec/cedar_match_spec.cr:65-81
+    t = _trie()
+    assert t.gsub("Ruby rRuby on rubyx ruby", True, sep=[" "], block=_crystal_block(t)) == "Crystal rRuby on rubyx crystal"
+
+
 def test_cedar_insert_ids():  # spec/cedar_spec.cr:4-13 (insert part)
     t = O.Cedar()
     assert [t.insert(s) for s in ["Ruby", "ruby", "rb"]] == [0, 1, 2]

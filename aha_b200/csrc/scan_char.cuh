@@ -247,6 +247,7 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
                                                int64_t cdoc_start, int64_t cdoc_end, const uint32_t (&lead0)[kChains], CharEvent* my_ev,
                                                uint32_t (&n_ev)[kChains], uint32_t (&n_hit)[kChains], bool& lookup_out, OnDoc on_doc) {
   constexpr unsigned kFull = 0xffffffffu;
+  const uint32_t sbuf_s = pin_u32((uint32_t)__cvta_generic_to_shared(sbuf));
   bool ok = true;
   bool lookup = false;  // an event reports more than 3 keys: n_hit is a lower bound, the caller counts through ref_rec
   // per sub-chunk state (all offsets relative to sbuf)
@@ -394,21 +395,26 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
   // (ok and done[] only change in the one-unit branch below: that is where they are voted on)
   for (;;) {
     uint32_t A[kChains], B[kChains], C[kChains];
-    bool can3 = true, can1 = true;
+    // straight-line integer logic (no short-circuit branches): bad3 / bad1 = 0 iff the sub-chunk is done, or has twelve
+    // bytes of room and they are four well-formed 3-byte units / twelve ASCII bytes
+    uint32_t bad3 = 0, bad1 = 0;
 #pragma unroll
     for (int c = 0; c < kChains; ++c) {
-      const uint32_t* wp = reinterpret_cast<const uint32_t*>(sbuf + (pos[c] & ~3));
-      const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3];
+      const uint32_t wa = sbuf_s + ((uint32_t)pos[c] & ~3u);
+      const uint32_t w0 = lds_u32(wa), w1 = lds_u32(wa + 4), w2 = lds_u32(wa + 8), w3 = lds_u32(wa + 12);
       const uint32_t sh = ((uint32_t)pos[c] & 3u) * 8u;
       A[c] = __funnelshift_r(w0, w1, sh);
       B[c] = __funnelshift_r(w1, w2, sh);
       C[c] = __funnelshift_r(w2, w3, sh);
-      const bool room = pos[c] < seg_end[c] && pos[c] + 12 <= min(de[c], stage_end);
-      const uint32_t bad3 =
+      // sign bit set when there is no room: pos >= seg_end, or pos + 12 > min(de, stage_end)
+      const uint32_t noroom = (uint32_t)((seg_end[c] - 1 - pos[c]) | (min(de[c], stage_end) - 12 - pos[c])) & 0x80000000u;
+      const uint32_t live = done[c] ? 0u : 0xFFFFFFFFu;
+      const uint32_t x3 =
           ((A[c] ^ 0xE08080E0u) & 0xF0C0C0F0u) | ((B[c] ^ 0x80E08080u) & 0xC0F0C0C0u) | ((C[c] ^ 0x8080E080u) & 0xC0C0F0C0u);
-      can3 = can3 && (done[c] || (room && bad3 == 0u));
-      can1 = can1 && (done[c] || (room && ((A[c] | B[c] | C[c]) & 0x80808080u) == 0u));
+      bad3 |= live & (noroom | x3);
+      bad1 |= live & (noroom | ((A[c] | B[c] | C[c]) & 0x80808080u));
     }
+    const bool can3 = bad3 == 0u, can1 = bad1 == 0u;
     if (__all_sync(kFull, can3)) {
       // four 3-byte units per sub-chunk: payload = (b0 & 0xF) << 12 | (b1 & 0x3F) << 6 | (b2 & 0x3F), root index = payload - lo
       auto root3 = [&](uint32_t w) {

@@ -18,7 +18,11 @@ namespace aha {
 
 constexpr int kStoreSlotsC = 16;                      // event slots per sub-chunk in the store (more: direct pass)
 constexpr int kStoreSlots = kStoreSlotsC * kChains;   // per lane
-constexpr int kExpandRounds = 4;                     // rounds of 32 events a warp of char_expand_kernel keeps in flight
+#ifndef AHA_B200_EXPAND_ROUNDS
+#define AHA_B200_EXPAND_ROUNDS 1
+#endif
+constexpr int kExpandRounds = AHA_B200_EXPAND_ROUNDS;  // rounds of 32 events a warp of char_expand_kernel keeps in flight
+                                                       // (measured on C2: 1 -> 0.91 ms, 4 -> 1.03 ms: occupancy wins)
 constexpr uint32_t kMarkRef = 0xFFFFFFFFu;            // marker event: `end` holds a document index
 constexpr uint32_t kTileDirect = 0x80000000u;         // tile_hits[] flag: the tile is delivered by char_direct_kernel
 

@@ -1,5 +1,6 @@
 """GPU parity tests: the CUDA path, called through the C ABI (aha_b200.AC -> libaha_b200.so), against the
 CPU oracle on the same inputs.  Bit-exact: integer/byte work, no tolerance."""
+import os
 import random
 
 import numpy as np
@@ -271,3 +272,51 @@ def test_char_automaton_dense_hits_and_many_tiny_docs():
     keys = ["的", "的的", "的的的", "一", "的一", "一的"]
     check_batch(keys, ["的" * 5000, "的一" * 3000, ("一的的" * 700)])
     check_batch(keys, ["的一"] * 3000 + [""] * 50 + ["的"] * 500, aha_b200.UNITS_CHAR)
+
+
+def _stream_hash(hits_i32, base=0):
+    """Order-sensitive 64-bit checksum of a hit stream on the device: sum_i mix(i + base, start, end, value) mod 2^64."""
+    import torch
+    h = hits_i32.view(-1, 3).to(torch.int64)
+    idx = torch.arange(h.shape[0], dtype=torch.int64, device=h.device) + base
+    x = h[:, 0] * -7046029254386353131 + h[:, 1] * -4417276706812531889 + h[:, 2] * 1609587929392839161 + idx * -8796714831421723037
+    x = (x ^ (x >> 29)) * -4658895280553007687
+    return int(x.sum().item())
+
+
+def test_full_size_c2_properties():
+    """BASELINE config C2 at full size (10 k CJK patterns, 2 048 documents of 1 MiB = 2.1 GB resident in HBM).  The oracle
+    cannot replay 80 M hits record by record in test time, so the full-size run is checked through size-independent
+    properties: total hit count against the oracle's multi-threaded counting walk over ALL the text, every 97th
+    document hit for hit, offsets monotone and consistent, and the stream of the whole batch equal (order-sensitive
+    checksum) to the streams of its two halves scanned separately."""
+    import torch
+    keys = synth.patterns_zh_ngrams(10000)
+    g = aha_b200.AC.compile(keys)
+    o = O.AC.compile(keys)
+    D = synth.doc_bytes(1 << 20)
+    n_docs = 2048
+    dev = synth.gen_device(synth.ZH, synth.SEED_TEXT + 1, 0, n_docs * D)
+    doc_off = torch.arange(0, n_docs + 1, dtype=torch.int64, device="cuda") * D
+    res = g.scan_device(dev, doc_off)
+    off = res.doc_hit_off_tensor().cpu().numpy()
+    assert off[0] == 0 and off[-1] == res.n_hits and np.all(np.diff(off) >= 0)
+    host = dev.cpu().numpy()
+    total = o.scan_count_mt(host, np.arange(n_docs + 1, dtype=np.int64) * D, os.cpu_count() or 4)
+    assert total == res.n_hits
+    hits = res.hits_tensor()
+    for d in range(0, n_docs, 97):
+        want = o.scan(host[d * D:(d + 1) * D])
+        got = hits[int(off[d]):int(off[d + 1])].cpu().numpy().astype("<i4")
+        assert got.tobytes() == want.tobytes(), "document %d" % d
+    whole = _stream_hash(hits)
+    half = n_docs // 2
+    a = g.scan_device(dev[:half * D], doc_off[:half + 1])
+    ha = _stream_hash(a.hits_tensor())
+    na = a.n_hits
+    assert na == off[half]
+    a = None
+    b = g.scan_device(dev[half * D:], doc_off[:n_docs - half + 1])
+    assert na + b.n_hits == res.n_hits
+    hb = _stream_hash(b.hits_tensor(), na)
+    assert (ha + hb) % (1 << 64) == whole % (1 << 64)

@@ -320,3 +320,19 @@ def test_full_size_c2_properties():
     assert na + b.n_hits == res.n_hits
     hb = _stream_hash(b.hits_tensor(), na)
     assert (ha + hb) % (1 << 64) == whole % (1 << 64)
+
+
+def test_hit_density_swings_between_calls():
+    """One dictionary, batches whose hit density swings by orders of magnitude between calls: the hit buffer is sized
+    per call after the walk has counted, whatever the previous call looked like."""
+    keys = ["ab", "b", "日本", "本"]
+    g = aha_b200.AC.compile(keys)
+    o = O.AC.compile(keys)
+    batches = [["x" * 100000], ["ab日本" * 30000, "b" * 50000], ["ab" * 10, "", "x" * 5000], ["本" * 200000]]
+    for docs in batches:
+        for mode in (0, aha_b200.UNITS_CHAR):
+            res = g.scan_batch(docs, mode)
+            want, want_off = oracle_batch(o, docs, mode)
+            assert res.n_hits == len(want)
+            assert np.array_equal(res.doc_hit_off(), want_off)
+            assert res.hits().tobytes() == want.tobytes()

@@ -51,7 +51,7 @@ static int32_t ensure_devices() {
 // sub-chunk is exactly six 12-byte steps (132 would need a seventh, three quarters empty)
 static void fused_geometry(uint32_t max_key_len, bool char_kernel, int32_t* chunk, int32_t* w16, int32_t* buf_bytes) {
   const uint32_t warm = max_key_len > 0 ? max_key_len - 1 : 0;
-  *chunk = char_kernel ? 126 : 132;
+  *chunk = char_kernel ? AHA_B200_CHAR_CHUNK : 132;
   *w16 = (int32_t)((warm + 1 + 3 + 15) & ~15u);
   if (*w16 < 16) *w16 = 16;
   *buf_bytes = (*w16 + 32 * *chunk + 16 + 32 + 127) & ~127;  // 16 staged bytes past the tile + read slack

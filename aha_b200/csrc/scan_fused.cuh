@@ -24,7 +24,13 @@ namespace aha {
 constexpr int kLaneCap = 32;      // scratch records per lane per tile
 constexpr int kMarkCap = 4;       // document-start markers per lane per tile
 constexpr int kMarkCapC = 2;      // ... per sub-chunk (scan_char.cuh walks two sub-chunks per lane)
-constexpr int kFusedWarps = 16;   // warps per CTA of scan_char_kernel (register- and shared-memory-bound)
+#ifndef AHA_B200_CHAR_WARPS
+#define AHA_B200_CHAR_WARPS 16
+#endif
+#ifndef AHA_B200_CHAR_CHUNK
+#define AHA_B200_CHAR_CHUNK 126
+#endif
+constexpr int kFusedWarps = AHA_B200_CHAR_WARPS;   // warps per CTA of scan_char_kernel (register- and shared-memory-bound)
 constexpr int kByteWarps = 32;    // warps per CTA of scan_fused_kernel<ByteGlobal>: latency-bound on L2, so as many as fit
 
 struct FusedParams {

@@ -233,9 +233,10 @@ constexpr int kEvSlotsC = kEvSlots / kChains;  // ring slots per sub-chunk (>= b
 // twelve ASCII characters) the warp takes a branch-free unrolled step; near a boundary (region end, document
 // end, mixed unit lengths) the warp falls back to one unit per iteration.
 // one_doc: the whole tile lies in document cd = [cdoc_start, cdoc_end).
-// Events of sub-chunk c go to my_ev[c * kEvSlotsC ...); n_ev[c] counts all of them; multi_mask bit (c * kEvCapC + i)
-// = event i of sub-chunk c reports more than one key.  Returns false (warp-uniform) when the text is not
-// structurally valid UTF-8: the caller rescans the tile with the byte automaton.
+// Events of sub-chunk c go to my_ev[c * kStride ...) (slot-major when kBounded, see below); n_ev[c] counts all of them,
+// n_hit[c] the hits they expand to as far as the 2-bit table knows (lookup_out = some event needs ref_rec[] for its
+// count).  Returns false (warp-uniform) when the text is not structurally valid UTF-8: the caller rescans the tile
+// with the byte automaton.
 // kLean (the split pipeline): events only -- no hit counting in the walk -- and n_ev[] counts in steps of 64 (the
 // slot-major element stride), on_doc included; the caller divides when the walk returns.
 // kStride = ring slots per sub-chunk; kBounded: drop (but count) events beyond kStride instead of relying on

@@ -413,9 +413,9 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
       const uint32_t x3 =
           ((A[c] ^ 0xE08080E0u) & 0xF0C0C0F0u) | ((B[c] ^ 0x80E08080u) & 0xC0F0C0C0u) | ((C[c] ^ 0x8080E080u) & 0xC0C0F0C0u);
       bad3 |= live & (noroom | x3);
-      bad1 |= live & (noroom | ((A[c] | B[c] | C[c]) & 0x80808080u));
+      bad1 |= live & noroom;  // the ASCII test itself is only made when the 3-byte step is not taken
     }
-    const bool can3 = bad3 == 0u, can1 = bad1 == 0u;
+    const bool can3 = bad3 == 0u;
     if (__all_sync(kFull, can3)) {
       // four 3-byte units per sub-chunk: payload = (b0 & 0xF) << 12 | (b1 & 0x3F) << 6 | (b2 & 0x3F), root index = payload - lo
       auto root3 = [&](uint32_t w) {
@@ -448,7 +448,11 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
 #pragma unroll
       for (int c = 0; c < kChains; ++c)
         if (!done[c]) pos[c] += 12;
-    } else if (__all_sync(kFull, can1)) {
+    } else if (__all_sync(kFull, [&] {
+#pragma unroll
+                 for (int c = 0; c < kChains; ++c) bad1 |= (done[c] ? 0u : 0xFFFFFFFFu) & ((A[c] | B[c] | C[c]) & 0x80808080u);
+                 return bad1 == 0u;
+               }())) {
       // twelve ASCII characters per sub-chunk
       uint32_t span[kChains];
 #pragma unroll

@@ -336,3 +336,46 @@ def test_hit_density_swings_between_calls():
             assert res.n_hits == len(want)
             assert np.array_equal(res.doc_hit_off(), want_off)
             assert res.hits().tobytes() == want.tobytes()
+
+
+def test_large_c3_properties():
+    """BASELINE config C3's dictionary (100 k mixed patterns: the byte automaton in global memory) over 1 GiB of MIX
+    text, checked like the full-size C2 run: oracle total count over all text, every 61st document hit for hit,
+    both offset units, and halves against the whole."""
+    import torch
+    keys = synth.patterns_mix(100000)
+    g = aha_b200.AC.compile(keys)
+    o = O.AC.compile(keys)
+    D = synth.doc_bytes(1 << 20)
+    n_docs = 1024
+    dev = synth.gen_device(synth.MIX, synth.SEED_TEXT + 2, 0, n_docs * D)
+    doc_off = torch.arange(0, n_docs + 1, dtype=torch.int64, device="cuda") * D
+    res = g.scan_device(dev, doc_off)
+    off = res.doc_hit_off_tensor().cpu().numpy()
+    assert off[0] == 0 and off[-1] == res.n_hits and np.all(np.diff(off) >= 0)
+    host = dev.cpu().numpy()
+    total = o.scan_count_mt(host, np.arange(n_docs + 1, dtype=np.int64) * D, os.cpu_count() or 4)
+    assert total == res.n_hits
+    hits = res.hits_tensor()
+    for d in range(0, n_docs, 61):
+        want = o.scan(host[d * D:(d + 1) * D])
+        got = hits[int(off[d]):int(off[d + 1])].cpu().numpy().astype("<i4")
+        assert got.tobytes() == want.tobytes(), "document %d" % d
+    whole = _stream_hash(hits)
+    n_all = res.n_hits
+    hits = None
+    res = None
+    half = n_docs // 2
+    a = g.scan_device(dev[:half * D], doc_off[:half + 1])
+    ha, na = _stream_hash(a.hits_tensor()), a.n_hits
+    assert na == off[half]
+    a = None
+    b = g.scan_device(dev[half * D:], doc_off[:n_docs - half + 1])
+    assert na + b.n_hits == n_all
+    assert (ha + _stream_hash(b.hits_tensor(), na)) % (1 << 64) == whole % (1 << 64)
+    b = None
+    # character offsets (String overloads) on a slice: every hit, against the oracle
+    docs = [host[d * D:(d + 1) * D].tobytes() for d in (0, 511)]
+    r = g.scan_batch(docs, aha_b200.UNITS_CHAR)
+    want, want_off = oracle_batch(o, docs, aha_b200.UNITS_CHAR)
+    assert np.array_equal(r.doc_hit_off(), want_off) and r.hits().tobytes() == want.tobytes()

@@ -14,13 +14,14 @@ from tests.test_oracle_kat import _rand_keys
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(autouse=True, params=["fused", "fused-byte", "two-pass"])
+@pytest.fixture(autouse=True, params=["fused", "char-fused", "fused-byte", "two-pass"])
 def scan_impl(request, monkeypatch):
-    """every parity test runs against all device paths: the fused single-pass kernel (character automaton in
-    shared memory where the dictionary allows), the fused kernel forced to the byte automaton, and the
-    two-pass baseline"""
+    """every parity test runs against all device paths: the default (character automaton in shared memory where the
+    dictionary allows: walk / scan / expand kernels, else the fused byte-automaton kernel), the single-kernel variant
+    of the character path, the fused kernel forced to the byte automaton, and the two-pass baseline"""
     monkeypatch.setenv("AHA_B200_IMPL", "0" if request.param == "two-pass" else "1")
     monkeypatch.setenv("AHA_B200_NO_CHAR", "1" if request.param == "fused-byte" else "0")
+    monkeypatch.setenv("AHA_B200_CHAR_IMPL", "fused" if request.param == "char-fused" else "split")
     return request.param
 
 

@@ -196,15 +196,15 @@ struct ProbeResult {
   uint32_t v, slotv, cid;
   bool hit, rare;
 };
-__device__ __forceinline__ ProbeResult char_probe(const CharSmem& S, uint32_t r, uint32_t s, uint32_t f1, bool deep) {
+__device__ __forceinline__ ProbeResult char_probe(const CharSmem& S, uint32_t vroot, uint32_t cid, uint32_t s, uint32_t f1, bool deep) {
   ProbeResult q;
-  q.cid = r >> 16;
+  q.cid = cid;
   const uint32_t slot1 = s + q.cid, slot2 = f1 + q.cid;
   const uint32_t c1 = S.check[slot1], c2 = S.check[slot2];
   const bool hit1 = c1 == s, hit2 = c2 == f1;
   q.hit = hit1 || hit2;
   const uint32_t slot12 = hit1 ? slot1 : slot2;
-  q.v = r & 0xFFFFu;  // the root entry in val[] format (fail = 0)
+  q.v = vroot;  // the root entry in val[] format (fail = 0)
   if (q.hit) q.v = S.val[slot12];
   q.slotv = q.hit ? slot12 : S.m + q.cid;  // what fires, as a ref_rec[] index
   q.rare = !q.hit && deep && q.cid != 0;
@@ -327,13 +327,13 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
   // one character of EVERY sub-chunk (warp converged): probes first, then the rare continuation behind a single
   // vote, then the state update, then the events behind a single branch
   // rl[c] = offset of the character's last byte relative to a_seg[c], span[c] = rb[c] - a_seg[c] (hoisted by the caller)
-  auto multi_step = [&](const uint32_t (&r)[kChains], const int32_t (&cs)[kChains], int32_t len, const int32_t (&rl)[kChains],
-                        const uint32_t (&span)[kChains]) {
+  auto multi_step = [&](const uint32_t (&vr)[kChains], const uint32_t (&ci)[kChains], const int32_t (&cs)[kChains], int32_t len,
+                        const int32_t (&rl)[kChains], const uint32_t (&span)[kChains]) {
     ProbeResult q[kChains];
     bool any_rare = false;
 #pragma unroll
     for (int c = 0; c < kChains; ++c) {
-      q[c] = char_probe(S, r[c], s[c], f1[c], deep[c]);
+      q[c] = char_probe(S, vr[c], ci[c], s[c], f1[c], deep[c]);
       any_rare = any_rare || q[c].rare;
     }
     if (__any_sync(kFull, any_rare)) {
@@ -422,7 +422,7 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
         const uint32_t wm = w & 0x3F3F0Fu;
         const uint32_t h = __dp4a(wm, 0x00000140u, S.neg_lo3_64);
         const uint32_t rel = h * 64u + (wm >> 16);
-        return S.root3[min(rel, S.n3)];  // root3[n3] = 0 (char_table.hpp)
+        return S.root3.base + min(rel, S.n3) * 4u;  // address of the entry; root3[n3] = 0 (char_table.hpp)
       };
       // twelve bytes = three words: character u sits at a fixed place in A:B:C, one funnel shift each
       int32_t rl0[kChains];
@@ -434,16 +434,18 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        uint32_t r[kChains];
+        uint32_t vr[kChains], ci[kChains];
         int32_t cs[kChains], rl[kChains];
 #pragma unroll
         for (int c = 0; c < kChains; ++c) {
           const uint32_t w = u == 0 ? A[c] : (u == 1 ? __funnelshift_r(A[c], B[c], 24) : (u == 2 ? __funnelshift_r(B[c], C[c], 16) : C[c] >> 8));
-          r[c] = root3(w);
+          const uint32_t ra = root3(w);
+          vr[c] = lds_u16(ra);      // the two halves of the entry as two loads: the load pipe has room, the integer pipe has not
+          ci[c] = lds_u16(ra + 2);
           cs[c] = pos[c] + 3 * u;
           rl[c] = rl0[c] + 3 * u;
         }
-        multi_step(r, cs, 3, rl, span);
+        multi_step(vr, ci, cs, 3, rl, span);
       }
 #pragma unroll
       for (int c = 0; c < kChains; ++c)
@@ -470,7 +472,13 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
           B[c] = __funnelshift_r(B[c], C[c], 8);
           C[c] >>= 8;
         }
-        multi_step(r, cs, 1, rl, span);
+        uint32_t vr[kChains], ci[kChains];
+#pragma unroll
+        for (int c = 0; c < kChains; ++c) {
+          vr[c] = r[c] & 0xFFFFu;
+          ci[c] = r[c] >> 16;
+        }
+        multi_step(vr, ci, cs, 1, rl, span);
       }
 #pragma unroll
       for (int c = 0; c < kChains; ++c)

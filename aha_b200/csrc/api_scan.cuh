@@ -82,7 +82,7 @@ static int32_t run_v1(ScanParams p, cudaStream_t st, aha_hits* res, HitsOwner* o
     count_leads_kernel<<<(unsigned)((p.n_chunks + 1 + 7) / 8), 256, 0, st>>>(p.text, p.total, p.chunk, p.n_chunks, lead_counts); aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
     int32_t rc = exclusive_sum_u32_to_u64(lead_counts, lead_prefix, p.n_chunks + 1, st);
     if (rc) return rc;
-    doc_lead_base_kernel<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(p.text, p.total, p.doc_off, p.n_docs, p.chunk,
+    doc_lead_base_kernel<<<(unsigned)((p.n_docs + 1 + 7) / 8), 256, 0, st>>>(p.text, p.total, p.doc_off, p.n_docs, p.chunk,
                                                                               lead_prefix, doc_lead); aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
     p.lead_prefix = lead_prefix;
     p.doc_lead_base = doc_lead;
@@ -203,7 +203,7 @@ static int32_t run_char_split(ScanParams p, const DeviceDfa* dd, cudaStream_t st
     g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
     int32_t rc = exclusive_sum_u32_to_u64(lead_counts, tile_lead, nt + 1, st);
     if (rc) return rc;
-    doc_lead_base_kernel<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(p.text, p.total, p.doc_off, p.n_docs, fp.tile, tile_lead,
+    doc_lead_base_kernel<<<(unsigned)((p.n_docs + 1 + 7) / 8), 256, 0, st>>>(p.text, p.total, p.doc_off, p.n_docs, fp.tile, tile_lead,
                                                                               doc_lead);
     g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
     fp.tile_lead = tile_lead;
@@ -365,7 +365,7 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
     count_leads_kernel<<<(unsigned)((fp.n_tiles + 1 + 7) / 8), 256, 0, st>>>(p.text, p.total, fp.tile, fp.n_tiles, lead_counts); aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
     int32_t rc = exclusive_sum_u32_to_u64(lead_counts, tile_lead, fp.n_tiles + 1, st);
     if (rc) return rc;
-    doc_lead_base_kernel<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(p.text, p.total, p.doc_off, p.n_docs, fp.tile,
+    doc_lead_base_kernel<<<(unsigned)((p.n_docs + 1 + 7) / 8), 256, 0, st>>>(p.text, p.total, p.doc_off, p.n_docs, fp.tile,
                                                                               tile_lead, doc_lead); aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
     fp.tile_lead = tile_lead;
     p.doc_lead_base = doc_lead;

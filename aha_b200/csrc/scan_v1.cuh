@@ -124,13 +124,16 @@ __global__ void count_leads_kernel(const uint8_t* text, int64_t total, int32_t c
 
 __global__ void doc_lead_base_kernel(const uint8_t* text, int64_t total, const int64_t* doc_off, int64_t n_docs,
                                      int32_t chunk, const uint64_t* lead_prefix, uint64_t* doc_lead_base) {
-  const int64_t d = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  // one warp per document boundary: the bytes between the tile start and the boundary, 32 at a time
+  const int64_t d = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
   if (d > n_docs) return;
   const int64_t pos = doc_off[d];
   const int64_t g = pos / chunk;
-  uint64_t c = lead_prefix[g];
-  for (int64_t i = g * chunk; i < pos; ++i) c += ((text[i] & 0xC0) != 0x80);
-  doc_lead_base[d] = c;
+  uint32_t c = 0;
+  for (int64_t i = g * chunk + lane; i < pos; i += 32) c += ((text[i] & 0xC0) != 0x80);
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if (lane == 0) doc_lead_base[d] = lead_prefix[g] + c;
 }
 
 // ---- ACX#match_longest (ac.cr:118-143, 249-263): sequential machine, one thread per document ----

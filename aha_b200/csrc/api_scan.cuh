@@ -74,6 +74,12 @@ static int32_t run_v1(ScanParams p, cudaStream_t st, aha_hits* res, HitsOwner* o
   p.offsets = offsets;
   p.doc_hit_off = static_cast<int64_t*>(own->dev_doc_hit_off);
   const int tpb = 128;
+  // trie path: the count pass keeps its hits in a scratch slice per document (3 bytes of scratch per byte of text), so
+  // that the walk runs once; not for inputs whose scratch would not be reasonable to ask for
+  aha_hit* doc_scratch = nullptr;
+  if (trie && !(p.mode & AHA_COUNT_ONLY) && p.total > 0 && p.total <= ((int64_t)16 << 30))
+    AHA_CUDA(cudaMallocAsync(&doc_scratch, (size_t)((p.total >> 2) + 1) * sizeof(aha_hit), st));
+  p.doc_scratch = doc_scratch;
   AHA_CUDA(cudaEventRecord(ev0, st));
   if (chars && !longest && p.total > 0) {
     AHA_CUDA(cudaMallocAsync(&lead_counts, (p.n_chunks + 1) * sizeof(uint32_t), st));
@@ -106,7 +112,11 @@ static int32_t run_v1(ScanParams p, cudaStream_t st, aha_hits* res, HitsOwner* o
   }
   if (units > 0) {
     if (longest) {
-      if (trie) trie_longest_doc_kernel<true><<<grid, tpb, 0, st>>>(p);
+      if (trie && p.doc_scratch && p.hits) {
+        trie_compact_kernel<<<(unsigned)((p.n_docs + 7) / 8), 256, 0, st>>>(p);
+        aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
+      }
+      if (trie) trie_longest_doc_kernel<true><<<grid, tpb, 0, st>>>(p);  // with a scratch: only documents that overflowed it
       else longest_doc_kernel<true><<<grid, tpb, 0, st>>>(p);
       aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
       offsets_to_doc_hit_off<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(offsets, p.n_docs, p.doc_hit_off); aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
@@ -118,6 +128,7 @@ static int32_t run_v1(ScanParams p, cudaStream_t st, aha_hits* res, HitsOwner* o
   AHA_CUDA(cudaGetLastError());
   AHA_CUDA(cudaFreeAsync(counts, st));
   AHA_CUDA(cudaFreeAsync(offsets, st));
+  if (doc_scratch) AHA_CUDA(cudaFreeAsync(doc_scratch, st));
   if (lead_counts) {
     AHA_CUDA(cudaFreeAsync(lead_counts, st));
     AHA_CUDA(cudaFreeAsync(lead_prefix, st));

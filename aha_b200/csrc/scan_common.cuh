@@ -34,6 +34,7 @@ struct ScanParams {
   int64_t* doc_hit_off;          // [n_docs + 1]
   const uint64_t* lead_prefix;   // [n_chunks + 1] non-continuation bytes before each chunk (AHA_UNITS_CHAR)
   const uint64_t* doc_lead_base; // [n_docs + 1]  non-continuation bytes before each document
+  aha_hit* doc_scratch;          // trie path: hits of document d at [doc_off[d] / 4, doc_off[d + 1] / 4) during the count pass
 };
 
 // "chr < sep.size && !sep[chr]" (ac.cr:326,333): neighbour byte vetoes the hit

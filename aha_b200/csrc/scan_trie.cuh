@@ -25,7 +25,10 @@ __host__ __device__ __forceinline__ bool cp_lower(uint32_t c) {
          (c >= 0x430 && c <= 0x44F);
 }
 // chr.uppercase? ? chr.downcase : chr.upcase   (cedar.cr:995-996)
-__host__ __device__ __forceinline__ uint32_t cp_other(uint32_t c) { return cp_upper(c) ? c + 32 : (cp_lower(c) ? c - 32 : c); }
+__host__ __device__ __forceinline__ uint32_t cp_other(uint32_t c) {
+  if (c < 0x80) return (c - 'A' < 26u) ? c + 32 : ((c - 'a' < 26u) ? c - 32 : c);  // ASCII: the common case, two compares
+  return cp_upper(c) ? c + 32 : (cp_lower(c) ? c - 32 : c);
+}
 
 __device__ __forceinline__ int utf8_decode(const uint8_t* s, int64_t i, int64_t n, uint32_t* cp) {
   const uint32_t b = s[i];
@@ -56,12 +59,21 @@ __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams 
   if (d >= p.n_docs) return;
   const uint8_t* s = p.text + p.doc_off[d];
   const int64_t n = p.doc_off[d + 1] - p.doc_off[d];
+  // The count pass also records: a document keeps one scratch slot per four bytes of text, which holds every hit
+  // unless the matches are shorter than that on average; trie_compact_kernel then moves the slice to its final place
+  // and only documents that overflowed are walked again (EMIT).
+  const int64_t sc_base = p.doc_off[d] >> 2, sc_cap = p.doc_scratch ? (p.doc_off[d + 1] >> 2) - sc_base : 0;
+  if (EMIT && p.doc_scratch && (int64_t)p.counts[d] <= sc_cap) return;
   const bool icase = (p.mode & AHA_IGNORE_CASE) != 0;
   const bool use_sep = (p.mode & AHA_SEP) != 0;
   const uint32_t C = p.C;
   uint64_t run = EMIT ? p.offsets[d] : 0;
   // jump(chr, from): walk the character's UTF-8 bytes over goto edges only; -1 == no path
   auto jump = [&](uint32_t cp, uint32_t from) -> int64_t {
+    if (cp < 0x80) {  // one byte, one edge
+      const uint32_t e = p.delta[(uint64_t)from * C + cmap[cp]];
+      return (!(e & kGoto) || cp == 0) ? -1 : (int64_t)(e & kStateMask);
+    }
     uint8_t buf[4];
     const int k = utf8_encode(cp, buf);
     uint32_t st = from;
@@ -144,13 +156,30 @@ __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams 
         }
       }
     } else {
-      if (EMIT && p.hits) p.hits[run] = aha_hit{cidx, cidx + best_n, best_v};
+      if (EMIT) {
+        if (p.hits) p.hits[run] = aha_hit{cidx, cidx + best_n, best_v};
+      } else if ((int64_t)run < sc_cap) {
+        p.doc_scratch[sc_base + (int64_t)run] = aha_hit{cidx, cidx + best_n, best_v};
+      }
       ++run;
       pos += best_bytes;
       cidx += best_n;
     }
   }
   if (!EMIT) p.counts[d] = (uint32_t)run;
+}
+
+// scratch slices -> final positions: one warp per document, 12-byte records copied as words
+__global__ void __launch_bounds__(256) trie_compact_kernel(const ScanParams p) {
+  const int64_t d = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (d >= p.n_docs || !p.hits) return;
+  const int64_t sc_base = p.doc_off[d] >> 2, sc_cap = (p.doc_off[d + 1] >> 2) - sc_base;
+  const int64_t cnt = p.counts[d];
+  if (cnt > sc_cap) return;  // walked again by the EMIT pass
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(p.doc_scratch + sc_base);
+  uint32_t* dst = reinterpret_cast<uint32_t*>(p.hits + p.offsets[d]);
+  for (int64_t i = lane; i < cnt * 3; i += 32) dst[i] = src[i];
 }
 
 }  // namespace aha

@@ -89,3 +89,28 @@ def patterns_mix(n, seed_text=SEED_TEXT + 2, seed=SEED_PAT + 2, en_frac=0.6):
     out = out_en + [z for z in out_zh if z not in seen]
     perm = rng.permutation(len(out))
     return [out[i] for i in perm]
+
+
+def patterns_en_phrases(n, seed_text=SEED_TEXT + 3, seed=SEED_PAT + 3):
+    """Config C4: n distinct EN words and two-word phrases sampled from the EN stream, every third one
+    with its case changed (upper / capitalised), for the ignore_case + sep scan of CedarX#match_longest."""
+    toks = _sample_text(EN, seed_text, 16 << 20).split()
+    rng = np.random.default_rng(seed)
+    seen, out = set(), []
+    while len(out) < n:
+        pos = rng.integers(0, len(toks) - 2, size=4 * n)
+        two = rng.random(4 * n) < 0.4
+        style = rng.integers(0, 6, size=4 * n)
+        for p, t, st in zip(pos, two, style):
+            w = toks[p] + (b" " + toks[p + 1] if t else b"")
+            if st == 0:
+                w = w.upper()
+            elif st == 1:
+                w = w.capitalize()
+            if len(w) < 3 or len(w) > 60 or w in seen:
+                continue
+            seen.add(w)
+            out.append(w)
+            if len(out) == n:
+                break
+    return out

@@ -380,3 +380,22 @@ def test_large_c3_properties():
     r = g.scan_batch(docs, aha_b200.UNITS_CHAR)
     want, want_off = oracle_batch(o, docs, aha_b200.UNITS_CHAR)
     assert np.array_equal(r.doc_hit_off(), want_off) and r.hits().tobytes() == want.tobytes()
+
+
+def test_scaled_c4_trie_longest():
+    """BASELINE config C4 scaled down: 20 k EN words and phrases in mixed case, 3 MB of EN text as 4 KiB documents,
+    CedarX#match_longest with ignore_case and sep = [' '] (character offsets), every hit against the oracle."""
+    keys = synth.patterns_en_phrases(20000)
+    gt, ot = aha_b200.Cedar(), O.Cedar()
+    for k in keys:
+        assert gt.insert(k) == ot.insert(k)
+    D = 4096 // synth.BLOCK * synth.BLOCK
+    text = synth.gen_host(synth.EN, synth.SEED_TEXT + 3, 0, 768 * D)
+    docs = [text[i:i + D].tobytes().decode("ascii") for i in range(0, len(text), D)]
+    for icase, sep in ((True, [" "]), (False, None)):
+        res = gt.match_longest_batch(docs, icase, sep)
+        want = [ot.match_longest(d, icase, sep) for d in docs]
+        off = np.cumsum([0] + [len(w) for w in want])
+        assert res.n_hits > 1000
+        assert np.array_equal(res.doc_hit_off(), off)
+        assert res.hits().tobytes() == np.concatenate(want).tobytes()

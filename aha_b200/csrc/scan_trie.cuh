@@ -100,31 +100,35 @@ __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams 
       }
     }
     int32_t best_n = 0, best_v = 0, best_bytes = 0;
+    // depth-first walk; the level being tried lives in registers (c_*), the arrays only hold the levels above it:
+    // they are written on the way down and read on the way back, not at every candidate
     int depth = 0;
-    node[0] = 0;
-    bpos[0] = (int32_t)pos;
-    var[0] = 0;
+    uint32_t c_node = 0, c_var = 0;
+    int32_t c_bpos = (int32_t)pos;
     while (depth >= 0) {
-      const int lv = depth;
-      if (var[lv] >= 2 || bpos[lv] >= n || lv >= kTrieMaxChars) {
-        --depth;
+      if (c_var >= 2 || c_bpos >= n || depth >= kTrieMaxChars) {
+        if (--depth >= 0) {
+          c_node = node[depth];
+          c_bpos = bpos[depth];
+          c_var = var[depth];
+        }
         continue;
       }
-      const int l = utf8_decode(s, bpos[lv], n, &cp);
-      const int v = var[lv]++;
+      const int l = utf8_decode(s, c_bpos, n, &cp);
+      const uint32_t v = c_var++;
       uint32_t cc = cp;
       if (v == 1) {
-        if (!icase) { var[lv] = 2; continue; }
+        if (!icase) { c_var = 2; continue; }
         cc = cp_other(cp);
         if (cc == cp) continue;
       }
-      const int64_t nn = jump(cc, node[lv]);
+      const int64_t nn = jump(cc, c_node);
       if (nn < 0) continue;
       const uint32_t j = p.out_off[nn];
-      if (j < p.out_off[nn + 1] && lv + 1 > best_n) {
+      if (j < p.out_off[nn + 1] && depth + 1 > best_n) {
         bool ok = true;
         if (use_sep) {
-          const int64_t after = bpos[lv] + l;
+          const int64_t after = c_bpos + l;
           if (after < n) {
             uint32_t ncp;
             utf8_decode(s, after, n, &ncp);
@@ -132,14 +136,17 @@ __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams 
           }
         }
         if (ok) {
-          best_n = lv + 1;
+          best_n = depth + 1;
           best_v = p.out_val[j];
-          best_bytes = bpos[lv] + l - (int32_t)pos;
+          best_bytes = c_bpos + l - (int32_t)pos;
         }
       }
-      node[lv + 1] = (uint32_t)nn;
-      bpos[lv + 1] = bpos[lv] + l;
-      var[lv + 1] = 0;
+      node[depth] = c_node;
+      bpos[depth] = c_bpos;
+      var[depth] = (uint8_t)c_var;
+      c_node = (uint32_t)nn;
+      c_bpos += l;
+      c_var = 0;
       ++depth;
     }
     if (best_n == 0) {

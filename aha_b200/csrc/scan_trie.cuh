@@ -68,21 +68,21 @@ __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams 
   const bool use_sep = (p.mode & AHA_SEP) != 0;
   const uint32_t C = p.C;
   uint64_t run = EMIT ? p.offsets[d] : 0;
-  // jump(chr, from): walk the character's UTF-8 bytes over goto edges only; -1 == no path
+  // jump(chr, from): walk the character's UTF-8 bytes over goto edges only; -1 == no path, else the table entry of the
+  // last edge (target state | flags: kOut tells whether the target has an output list, so out_off[] is only read then)
   auto jump = [&](uint32_t cp, uint32_t from) -> int64_t {
     if (cp < 0x80) {  // one byte, one edge
       const uint32_t e = p.delta[(uint64_t)from * C + cmap[cp]];
-      return (!(e & kGoto) || cp == 0) ? -1 : (int64_t)(e & kStateMask);
+      return (!(e & kGoto) || cp == 0) ? -1 : (int64_t)e;
     }
     uint8_t buf[4];
     const int k = utf8_encode(cp, buf);
-    uint32_t st = from;
+    uint32_t e = from;
     for (int j = 0; j < k; ++j) {
-      const uint32_t e = p.delta[(uint64_t)st * C + cmap[buf[j]]];
+      e = p.delta[(uint64_t)(e & kStateMask) * C + cmap[buf[j]]];
       if (!(e & kGoto) || buf[j] == 0) return -1;
-      st = e & kStateMask;
     }
-    return (int64_t)st;
+    return (int64_t)e;
   };
   uint32_t node[kTrieMaxChars + 1];
   int32_t bpos[kTrieMaxChars + 1];
@@ -122,10 +122,11 @@ __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams 
         cc = cp_other(cp);
         if (cc == cp) continue;
       }
-      const int64_t nn = jump(cc, c_node);
-      if (nn < 0) continue;
-      const uint32_t j = p.out_off[nn];
-      if (j < p.out_off[nn + 1] && depth + 1 > best_n) {
+      const int64_t je = jump(cc, c_node);
+      if (je < 0) continue;
+      const uint32_t nn = (uint32_t)je & kStateMask;
+      if (((uint32_t)je & kOut) && depth + 1 > best_n) {
+        const uint32_t j = p.out_off[nn];
         bool ok = true;
         if (use_sep) {
           const int64_t after = c_bpos + l;
@@ -144,7 +145,7 @@ __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams 
       node[depth] = c_node;
       bpos[depth] = c_bpos;
       var[depth] = (uint8_t)c_var;
-      c_node = (uint32_t)nn;
+      c_node = nn;
       c_bpos += l;
       c_var = 0;
       ++depth;

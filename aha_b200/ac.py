@@ -230,10 +230,17 @@ class AC:
         check(lib().aha_b200_dfa_from_device_blob(tensor.data_ptr(), tensor.numel(), C.byref(h)))
         return cls(h)
 
-    def blob(self):
+    def blob_view(self):
+        """The serialised DFA as a uint8 array over library-owned memory (valid while this object lives); no copy,
+        so a multi-GB automaton (1 M patterns: 3.2 GB) can be handed to the broadcast as it is."""
         p, n = C.c_void_p(), C.c_int64()
         check(lib().aha_b200_dfa_blob(self._dfa, C.byref(p), C.byref(n)))
-        return C.string_at(p.value, n.value)
+        a = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(n.value,))
+        a.flags.writeable = False
+        return a
+
+    def blob(self):
+        return self.blob_view().tobytes()
 
     def info(self):
         names = ["n_states", "n_classes", "n_keys", "max_key_len", "n_out", "blob_bytes", "hot_states", "entry_bytes"]

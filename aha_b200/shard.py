@@ -12,6 +12,7 @@ document order.  Two collectives only, both over `torch.distributed` (NCCL on GP
 Nothing here touches the scan itself: a rank scans its shard with `AC.scan_batch` / `AC.scan_device`.
 """
 import numpy as np
+import warnings
 
 
 def partition_docs(doc_sizes, world):
@@ -52,7 +53,10 @@ def broadcast_blob(blob, src=0, device=None):
     dist.broadcast(n, src)
     buf = torch.empty(int(n.item()), dtype=torch.uint8, device=dev)
     if rank == src:
-        buf.copy_(torch.frombuffer(bytearray(blob), dtype=torch.uint8))
+        src_arr = np.frombuffer(blob, dtype=np.uint8) if isinstance(blob, (bytes, bytearray, memoryview)) else np.asarray(blob)
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")  # read-only view of the library's blob: only read from
+            buf.copy_(torch.from_numpy(src_arr))
     dist.broadcast(buf, src)
     return buf
 

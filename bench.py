@@ -6,7 +6,7 @@ per GPU (2048 documents of ~1 MiB), dictionary sampled from the same stream.  On
 the scan over the whole batch.  `value` times the scan with text resident in HBM; `e2e` times the
 C-ABI call aha_b200_scan() on HOST buffers (H2D text, scan, D2H hits inside the timed region).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c1|c2|c3]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c1|c2|c3|c5]
 N > 1 is launched by torchrun (one rank per GPU): the corpus shards by document (weak scaling), the DFA
 is built on rank 0 and broadcast over NCCL, hit counts are all-gathered.
 """
@@ -28,7 +28,10 @@ WORKLOADS = {
     "c1": ("EN", 1000, 100 << 20, 1 << 20, "C1: 1k ASCII word patterns / 100 MB EN text"),
     "c2": ("ZH", 10000, 2 << 30, 1 << 20, "C2: 10k CJK patterns / 2 GB ZH text"),
     "c3": ("MIX", 100000, 10 << 30, 1 << 20, "C3: 100k patterns / 10 GB MIX text"),
+    # configs[4]: 100 GB over 8 GPUs = 12.5 GB per GPU, the 3.2 GB byte DFA broadcast over NCCL
+    "c5": ("MIX", 1000000, 12500 << 20, 1 << 20, "C5: 1M patterns / 100 GB MIX text document-sharded over 8 GPUs (12.5 GB per GPU)"),
 }
+CORPUS = {"c1": ("EN", 0), "c2": ("ZH", 1), "c3": ("MIX", 2), "c5": ("MIX", 2)}  # corpus, seed offset
 
 
 def make_patterns(name):
@@ -37,7 +40,7 @@ def make_patterns(name):
         return synth.patterns_en_words(1000), synth.EN, synth.SEED_TEXT
     if name == "c2":
         return synth.patterns_zh_ngrams(10000), synth.ZH, synth.SEED_TEXT + 1
-    return synth.patterns_mix(100000), synth.MIX, synth.SEED_TEXT + 2
+    return synth.patterns_mix(WORKLOADS[name][1]), synth.MIX, synth.SEED_TEXT + 2
 
 
 def measured_traffic(name):
@@ -184,7 +187,7 @@ def main():
     if rank == 0:
         keys, corpus, seed = make_patterns(name)
         ac = aha_b200.AC.compile(keys)
-        blob = ac.blob()
+        blob = ac.blob_view() if world > 1 else None
     build_s = time.perf_counter() - t0
     bcast_ms = 0.0
     if world > 1:
@@ -198,8 +201,7 @@ def main():
         bcast_ms = e0.elapsed_time(e1)
         if rank != 0:
             ac = aha_b200.AC.from_device_blob(buf)
-            _, corpus, seed = {"c1": (None, synth.EN, synth.SEED_TEXT), "c2": (None, synth.ZH, synth.SEED_TEXT + 1),
-                               "c3": (None, synth.MIX, synth.SEED_TEXT + 2)}[name]
+            corpus, seed = getattr(synth, CORPUS[name][0]), synth.SEED_TEXT + CORPUS[name][1]
     info = ac.info()
 
     # ---- corpus shard of this rank: documents [rank*n_docs, (rank+1)*n_docs) of the stream ----

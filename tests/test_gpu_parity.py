@@ -382,6 +382,46 @@ def test_large_c3_properties():
     assert np.array_equal(r.doc_hit_off(), want_off) and r.hits().tobytes() == want.tobytes()
 
 
+def test_scaled_c5_million_patterns():
+    """BASELINE config C5's dictionary (1 M mixed patterns: a 3.2 GB byte automaton, far beyond L2) over 256 MiB of
+    MIX text: oracle total count over all text, every 37th document hit for hit, halves against the whole, and the
+    same automaton rebuilt from its device blob (what a rank does after the ncclBroadcast) giving the same stream."""
+    import torch
+    keys = synth.patterns_mix(1000000)
+    g = aha_b200.AC.compile(keys)
+    o = O.AC.compile(keys)
+    info = g.info()
+    assert info["n_keys"] == 1000000 and info["n_states"] > 3000000
+    D = synth.doc_bytes(1 << 20)
+    n_docs = 256
+    dev = synth.gen_device(synth.MIX, synth.SEED_TEXT + 2, 0, n_docs * D)
+    doc_off = torch.arange(0, n_docs + 1, dtype=torch.int64, device="cuda") * D
+    res = g.scan_device(dev, doc_off)
+    off = res.doc_hit_off_tensor().cpu().numpy()
+    assert off[0] == 0 and off[-1] == res.n_hits and np.all(np.diff(off) >= 0)
+    host = dev.cpu().numpy()
+    total = o.scan_count_mt(host, np.arange(n_docs + 1, dtype=np.int64) * D, os.cpu_count() or 4)
+    assert total == res.n_hits
+    hits = res.hits_tensor()
+    for d in range(0, n_docs, 37):
+        want = o.scan(host[d * D:(d + 1) * D])
+        got = hits[int(off[d]):int(off[d + 1])].cpu().numpy().astype("<i4")
+        assert got.tobytes() == want.tobytes(), "document %d" % d
+    whole, n_all = _stream_hash(hits), res.n_hits
+    hits = res = None
+    # a second rank's view: the blob arrives in device memory, the automaton is rebuilt from it
+    blob = torch.from_numpy(g.blob_view().copy()).cuda()
+    g2 = aha_b200.AC.from_device_blob(blob)
+    half = n_docs // 2
+    a = g2.scan_device(dev[:half * D], doc_off[:half + 1])
+    ha, na = _stream_hash(a.hits_tensor()), a.n_hits
+    assert na == off[half]
+    a = None
+    b = g2.scan_device(dev[half * D:], doc_off[:n_docs - half + 1])
+    assert na + b.n_hits == n_all
+    assert (ha + _stream_hash(b.hits_tensor(), na)) % (1 << 64) == whole % (1 << 64)
+
+
 def test_scaled_c4_trie_longest():
     """BASELINE config C4 scaled down: 20 k EN words and phrases in mixed case, 3 MB of EN text as 4 KiB documents,
     CedarX#match_longest with ignore_case and sep = [' '] (character offsets), every hit against the oracle."""

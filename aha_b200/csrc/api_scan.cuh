@@ -140,8 +140,16 @@ static int32_t run_v1(ScanParams p, cudaStream_t st, aha_hits* res, HitsOwner* o
 // single-pass fused kernel: see scan_fused.cuh
 template <class Policy>
 static int32_t launch_fused(const FusedParams& fp, const Policy& pol, int n_sm, size_t smem, cudaStream_t st) {
-  AHA_CUDA(cudaFuncSetAttribute(scan_fused_kernel<Policy>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  scan_fused_kernel<Policy><<<n_sm, kByteWarps * 32, smem, st>>>(fp, pol); aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
+  // event mode (lists expanded after the walk) for everything but sep scans, whose neighbour tests sit in emit_list
+  const char* fr = getenv("AHA_B200_BYTE_RECORDS");
+  const bool force_records = fr && fr[0] == '1';  // in-product cross-check of the older delivery
+  if ((fp.sp.mode & AHA_SEP) || force_records || !fp.ev_scratch) {
+    AHA_CUDA(cudaFuncSetAttribute(scan_fused_kernel<Policy, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    scan_fused_kernel<Policy, false><<<n_sm, kByteWarps * 32, smem, st>>>(fp, pol); aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
+  } else {
+    AHA_CUDA(cudaFuncSetAttribute(scan_fused_kernel<Policy, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    scan_fused_kernel<Policy, true><<<n_sm, kByteWarps * 32, smem, st>>>(fp, pol); aha::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
+  }
   AHA_CUDA(cudaGetLastError());
   return AHA_OK;
 }
@@ -334,6 +342,7 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
     AHA_CUDA(cudaMallocAsync(&cp.events, (size_t)n_warps * 2 * 32 * kEvSlots * sizeof(CharEvent), st));
   } else {
     AHA_CUDA(cudaMallocAsync(&fp.scratch, (size_t)n_warps * 32 * kLaneCap * sizeof(aha_hit), st));
+    if (!(p.mode & AHA_SEP)) AHA_CUDA(cudaMallocAsync(&fp.ev_scratch, (size_t)n_warps * 32 * kByteEvCap * sizeof(uint2), st));
   }
   AHA_CUDA(cudaMallocAsync(&fp.marks, (size_t)n_warps * 2 * 32 * kMarkCap * sizeof(int2), st));
   AHA_CUDA(cudaMallocAsync(&own->dev_doc_hit_off, (p.n_docs + 1) * sizeof(int64_t), st));
@@ -442,6 +451,7 @@ static int32_t run_fused(ScanParams p, const DeviceDfa* dd, const aha_dfa* dfa, 
   AHA_CUDA(cudaFreeAsync(tile_state, st));
   AHA_CUDA(cudaFreeAsync(counters, st));
   if (fp.scratch) AHA_CUDA(cudaFreeAsync(fp.scratch, st));
+  if (fp.ev_scratch) AHA_CUDA(cudaFreeAsync(fp.ev_scratch, st));
   if (cp.events) AHA_CUDA(cudaFreeAsync(cp.events, st));
   AHA_CUDA(cudaFreeAsync(fp.marks, st));
   if (lead_counts) {

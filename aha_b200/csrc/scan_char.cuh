@@ -46,6 +46,7 @@ struct CharParams {
 
 // counts only (fallback / overflow paths)
 struct CountSink {
+  static constexpr bool kEvents = false;
   uint32_t n = 0;
   __device__ __forceinline__ void hit(int32_t, int32_t, int32_t) { ++n; }
   __device__ __forceinline__ void doc_start(int64_t) {}

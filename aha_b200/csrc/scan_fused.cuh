@@ -21,7 +21,8 @@
 
 namespace aha {
 
-constexpr int kLaneCap = 32;      // scratch records per lane per tile
+constexpr int kLaneCap = 32;      // scratch records per lane per tile (record mode: sep scans)
+constexpr int kByteEvCap = 64;        // events (end position, state) per lane per tile (event mode: everything else)
 constexpr int kMarkCap = 4;       // document-start markers per lane per tile
 constexpr int kMarkCapC = 2;      // ... per sub-chunk (scan_char.cuh walks two sub-chunks per lane)
 #ifndef AHA_B200_CHAR_WARPS
@@ -47,6 +48,7 @@ struct FusedParams {
   unsigned long long* total_hits;  // out: total number of hits
   int64_t hit_cap;                 // capacity of sp.hits (records); writes beyond are dropped
   aha_hit* scratch;                // [n_warps_total][32][kLaneCap]
+  uint2* ev_scratch;               // [n_warps_total][32][kByteEvCap] {state, end} (event mode)
   int2* marks;                     // [n_warps_total][32][kMarkCap] (doc index low/high packed, seq)
   unsigned int* n_direct;          // diagnostics: tiles that took the direct pass
   const uint64_t* tile_lead;       // [n_tiles + 1] non-continuation bytes before each tile (AHA_UNITS_CHAR)
@@ -86,6 +88,7 @@ __device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned l
 // ---- sinks ---------------------------------------------------------------------------------------
 // ScratchSink: first pass; lane-private records + markers, counts everything.
 struct ScratchSink {
+  static constexpr bool kEvents = false;
   aha_hit* rec;   // lane slot [kLaneCap]
   int2* mark;     // lane slot [kMarkCap]
   uint32_t n = 0, n_mark = 0;
@@ -101,6 +104,7 @@ struct ScratchSink {
 };
 // DirectSink: offsets known; writes final positions.
 struct DirectSink {
+  static constexpr bool kEvents = false;
   aha_hit* out;
   int64_t* doc_hit_off;
   int64_t idx, cap;
@@ -110,6 +114,32 @@ struct DirectSink {
   }
   __device__ __forceinline__ void doc_start(int64_t d) { doc_hit_off[d] = idx; }
   __device__ __forceinline__ bool want_records() const { return true; }
+};
+
+// EventSink: the walk only notes where an output state was entered ({state, end}); the lists are expanded after the
+// walk by all lanes at once.  With the expansion inside the walk a lane that fires holds its 31 neighbours for
+// four dependent loads, and at one hit per 5-10 bytes some lane fires at nearly every step.
+struct EventSink {
+  static constexpr bool kEvents = true;
+  uint2* ev;      // lane slot [kByteEvCap]
+  int2* mark;     // lane slot [kMarkCap]: {document, events before it}
+  uint32_t n = 0, n_mark = 0;
+  __device__ __forceinline__ void event(uint32_t state, int32_t end) {
+    if (n < (uint32_t)kByteEvCap) ev[n] = make_uint2(state, (uint32_t)end);
+    ++n;
+  }
+  __device__ __forceinline__ void hit(int32_t, int32_t, int32_t) {}
+  __device__ __forceinline__ void doc_start(int64_t d) {
+    if (n_mark < (uint32_t)kMarkCap) mark[n_mark] = make_int2((int)d, (int)n);
+    ++n_mark;
+  }
+};
+// TallySink: counts hits only (a tile whose events did not fit is counted, then delivered by the direct pass)
+struct TallySink {
+  static constexpr bool kEvents = false;
+  uint32_t n = 0;
+  __device__ __forceinline__ void hit(int32_t, int32_t, int32_t) { ++n; }
+  __device__ __forceinline__ void doc_start(int64_t) {}
 };
 
 // expands the output list of `state` for a match whose last byte is absolute position `pos`
@@ -166,7 +196,10 @@ struct ByteGlobal {
         if (chars) lead += ((byte & 0xC0) != 0x80);
         const uint32_t e = __ldg(&p.delta[(uint64_t)s * C + cmap[byte]]);
         s = e & kStateMask;
-        if (e & kOut) emit_list(p, sink, s, pos, doc_start, doc_end, lead);
+        if (e & kOut) {
+          if constexpr (Sink::kEvents) sink.event(s, chars ? (int32_t)lead : (int32_t)(pos - doc_start + 1));
+          else emit_list(p, sink, s, pos, doc_start, doc_end, lead);
+        }
       }
       if (pos == doc_end && (pos < b || b == p.total)) {
         s = 0;
@@ -253,7 +286,7 @@ __device__ __forceinline__ unsigned long long tile_exclusive_prefix(const FusedP
   return resolve_prefix(P, t, lane);
 }
 
-template <class Policy>
+template <class Policy, bool EV>
 __global__ void __launch_bounds__(kByteWarps * 32, 1) scan_fused_kernel(const FusedParams P, const Policy policy_in) {
   extern __shared__ __align__(128) uint8_t smem[];
   const ScanParams& p = P.sp;
@@ -318,55 +351,148 @@ __global__ void __launch_bounds__(kByteWarps * 32, 1) scan_fused_kernel(const Fu
       }
     }
 
-    ScratchSink ss;
-    ss.rec = my_rec;
-    ss.mark = my_mark;
-    policy.walk(P, sbuf, origin, a, b, lead0, ss);
-
-    // ---- warp prefix of lane counts, tile aggregate
-    uint32_t incl = ss.n;
-    for (int o = 1; o < 32; o <<= 1) {
-      uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += v;
-    }
-    const uint32_t excl_lane = incl - ss.n;
-    const uint32_t T = __shfl_sync(0xffffffffu, incl, 31);
-    // ---- decoupled look-back
-    const unsigned long long prefix = tile_exclusive_prefix(P, t, T, lane);
-    if ((int64_t)t == P.n_tiles - 1 && lane == 0) *P.total_hits = prefix + T;
-
-    // ---- deliver
-    const bool over = (ss.n > (uint32_t)kLaneCap) || (ss.n_mark > (uint32_t)kMarkCap);
-    const bool any_over = __any_sync(0xffffffffu, over);
-    if (!any_over) {
-      // markers first (they only need the lane base)
-      for (uint32_t k = 0; k < ss.n_mark; ++k) p.doc_hit_off[my_mark[k].x] = (int64_t)(prefix + excl_lane + (uint32_t)my_mark[k].y);
-      if (p.hits && T > 0) {
-        // cooperative copy: output index i -> (lane l, record k) by binary search over the lane prefix
-        __syncwarp();
-        for (uint32_t i = lane; i < ((T + 31u) & ~31u); i += 32) {
-          uint32_t lo = 0;
+    if constexpr (EV) {
+      // ---- event mode: walk (one dependent table load per byte, nothing else), count, look-back, expand in place
+      const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
+      uint2* my_ev = P.ev_scratch + (gwarp * 32 + lane) * kByteEvCap;
+      EventSink es;
+      es.ev = my_ev;
+      es.mark = my_mark;
+      policy.walk(P, sbuf, origin, a, b, lead0, es);
+      const uint32_t ne = es.n, nm = es.n_mark;
+      const bool any_over = __any_sync(0xffffffffu, ne > (uint32_t)kByteEvCap || nm > (uint32_t)kMarkCap);
+      uint32_t n_lane = 0;
+      if (!any_over) {
+        for (uint32_t k0 = 0; k0 < ne; k0 += 4) {  // list lengths of four events at a time: independent loads
+          uint32_t c[4];
 #pragma unroll
-          for (int step = 16; step > 0; step >>= 1) {
-            const uint32_t cand = lo + step;
-            const uint32_t ex = __shfl_sync(0xffffffffu, excl_lane, cand & 31);
-            if (cand < 32 && ex <= i) lo = cand;
+          for (int u = 0; u < 4; ++u) {
+            c[u] = 0;
+            if (k0 + u < ne) {
+              const uint32_t st = my_ev[k0 + u].x;
+              c[u] = __ldg(p.out_off + st + 1) - __ldg(p.out_off + st);
+            }
           }
-          const uint32_t ex = __shfl_sync(0xffffffffu, excl_lane, lo);
-          if (i < T) {
-            const int64_t dst = (int64_t)prefix + i;
-            if (dst < P.hit_cap) p.hits[dst] = P.scratch[(gwarp * 32 + lo) * kLaneCap + (i - ex)];
+          n_lane += (c[0] + c[1]) + (c[2] + c[3]);
+        }
+      } else {
+        TallySink ts;
+        policy.walk(P, sbuf, origin, a, b, lead0, ts);
+        n_lane = ts.n;
+      }
+      uint32_t incl = n_lane;
+      for (int o = 1; o < 32; o <<= 1) {
+        uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+      }
+      const uint32_t excl_lane = incl - n_lane;
+      const uint32_t T = __shfl_sync(0xffffffffu, incl, 31);
+      const unsigned long long prefix = tile_exclusive_prefix(P, t, T, lane);
+      if ((int64_t)t == P.n_tiles - 1 && lane == 0) *P.total_hits = prefix + T;
+      if (!any_over) {
+        // every lane expands its own events to their final positions (a lane's hits are consecutive in the stream)
+        int64_t idx = (int64_t)(prefix + excl_lane);
+        uint32_t m = 0;
+        aha_hit* const out = p.hits;
+        for (uint32_t k0 = 0; k0 < ne; k0 += 4) {
+          uint2 e[4];
+          uint32_t j0[4], cnt[4], kl[4];
+          int32_t v0[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) e[u] = (k0 + u < ne) ? my_ev[k0 + u] : make_uint2(0u, 0u);
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            j0[u] = 0;
+            cnt[u] = 0;
+            if (k0 + u < ne) {
+              j0[u] = __ldg(p.out_off + e[u].x);
+              cnt[u] = __ldg(p.out_off + e[u].x + 1) - j0[u];
+            }
+          }
+          if (out) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v0[u] = cnt[u] ? __ldg(p.out_val + j0[u]) : 0;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) kl[u] = cnt[u] ? (chars ? __ldg(p.key_tail + v0[u]) : __ldg(p.key_len + v0[u])) : 0u;
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            if (k0 + u < ne) {
+              while (m < nm && (uint32_t)my_mark[m].y == k0 + u) p.doc_hit_off[my_mark[m++].x] = idx;
+              if (out && cnt[u]) {
+                const int32_t end = (int32_t)e[u].y;
+                if (idx < P.hit_cap) out[idx] = chars ? aha_hit{end - 1 - (int32_t)kl[u], end, v0[u]} : aha_hit{end - (int32_t)kl[u], end, v0[u]};
+                for (uint32_t j = 1; j < cnt[u]; ++j) {
+                  const int32_t v = __ldg(p.out_val + j0[u] + j);
+                  const int32_t l = (int32_t)(chars ? __ldg(p.key_tail + v) : __ldg(p.key_len + v));
+                  if (idx + j < P.hit_cap) out[idx + j] = chars ? aha_hit{end - 1 - l, end, v} : aha_hit{end - l, end, v};
+                }
+              }
+              idx += cnt[u];
+            }
           }
         }
+        while (m < nm) p.doc_hit_off[my_mark[m++].x] = idx;
+      } else {
+        if (lane == 0) atomicAdd(P.n_direct, 1u);
+        DirectSink ds;
+        ds.out = p.hits;
+        ds.doc_hit_off = p.doc_hit_off;
+        ds.idx = (int64_t)(prefix + excl_lane);
+        ds.cap = P.hit_cap;
+        policy.walk(P, sbuf, origin, a, b, lead0, ds);
       }
     } else {
-      if (lane == 0) atomicAdd(P.n_direct, 1u);
-      DirectSink ds;
-      ds.out = p.hits;
-      ds.doc_hit_off = p.doc_hit_off;
-      ds.idx = (int64_t)(prefix + excl_lane);
-      ds.cap = P.hit_cap;
-      policy.walk(P, sbuf, origin, a, b, lead0, ds);
+      ScratchSink ss;
+      ss.rec = my_rec;
+      ss.mark = my_mark;
+      policy.walk(P, sbuf, origin, a, b, lead0, ss);
+
+      // ---- warp prefix of lane counts, tile aggregate
+      uint32_t incl = ss.n;
+      for (int o = 1; o < 32; o <<= 1) {
+        uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+      }
+      const uint32_t excl_lane = incl - ss.n;
+      const uint32_t T = __shfl_sync(0xffffffffu, incl, 31);
+      // ---- decoupled look-back
+      const unsigned long long prefix = tile_exclusive_prefix(P, t, T, lane);
+      if ((int64_t)t == P.n_tiles - 1 && lane == 0) *P.total_hits = prefix + T;
+
+      // ---- deliver
+      const bool over = (ss.n > (uint32_t)kLaneCap) || (ss.n_mark > (uint32_t)kMarkCap);
+      const bool any_over = __any_sync(0xffffffffu, over);
+      if (!any_over) {
+        // markers first (they only need the lane base)
+        for (uint32_t k = 0; k < ss.n_mark; ++k) p.doc_hit_off[my_mark[k].x] = (int64_t)(prefix + excl_lane + (uint32_t)my_mark[k].y);
+        if (p.hits && T > 0) {
+          // cooperative copy: output index i -> (lane l, record k) by binary search over the lane prefix
+          __syncwarp();
+          for (uint32_t i = lane; i < ((T + 31u) & ~31u); i += 32) {
+            uint32_t lo = 0;
+  #pragma unroll
+            for (int step = 16; step > 0; step >>= 1) {
+              const uint32_t cand = lo + step;
+              const uint32_t ex = __shfl_sync(0xffffffffu, excl_lane, cand & 31);
+              if (cand < 32 && ex <= i) lo = cand;
+            }
+            const uint32_t ex = __shfl_sync(0xffffffffu, excl_lane, lo);
+            if (i < T) {
+              const int64_t dst = (int64_t)prefix + i;
+              if (dst < P.hit_cap) p.hits[dst] = P.scratch[(gwarp * 32 + lo) * kLaneCap + (i - ex)];
+            }
+          }
+        }
+      } else {
+        if (lane == 0) atomicAdd(P.n_direct, 1u);
+        DirectSink ds;
+        ds.out = p.hits;
+        ds.doc_hit_off = p.doc_hit_off;
+        ds.idx = (int64_t)(prefix + excl_lane);
+        ds.cap = P.hit_cap;
+        policy.walk(P, sbuf, origin, a, b, lead0, ds);
+      }
     }
     __syncwarp();
     fence_proxy_async();  // reads of sbuf are done before the next bulk copy overwrites it

@@ -14,13 +14,16 @@ from tests.test_oracle_kat import _rand_keys
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(autouse=True, params=["fused", "char-fused", "fused-byte", "two-pass"])
+@pytest.fixture(autouse=True, params=["fused", "char-fused", "fused-byte", "fused-byte-records", "two-pass"])
 def scan_impl(request, monkeypatch):
     """every parity test runs against all device paths: the default (character automaton in shared memory where the
     dictionary allows: walk / scan / expand kernels, else the fused byte-automaton kernel), the single-kernel variant
-    of the character path, the fused kernel forced to the byte automaton, and the two-pass baseline"""
+    of the character path, the fused kernel forced to the byte automaton (both deliveries), and the two-pass baseline"""
     monkeypatch.setenv("AHA_B200_IMPL", "0" if request.param == "two-pass" else "1")
-    monkeypatch.setenv("AHA_B200_NO_CHAR", "1" if request.param == "fused-byte" else "0")
+    monkeypatch.setenv("AHA_B200_NO_CHAR", "1" if request.param.startswith("fused-byte") else "0")
+    # the byte kernel delivers from {state, end} events expanded after the walk; "records" is its older delivery
+    # (lists expanded inside the walk into a lane-private ring), still the path of sep scans
+    monkeypatch.setenv("AHA_B200_BYTE_RECORDS", "1" if request.param == "fused-byte-records" else "0")
     monkeypatch.setenv("AHA_B200_CHAR_IMPL", "fused" if request.param == "char-fused" else "split")
     return request.param
 

@@ -218,7 +218,12 @@ def main():
     def step():
         return ac.scan_device(text, doc_off)
 
+    # a caller keeps one result in flight: the previous one is released before the next scan (with both alive the
+    # stream-ordered pool keeps growing through the first calls, which would put cudaMallocAsync's mapping of
+    # multi-GB hit buffers into the timed steps of C3 / C5; tools/gap_probe.py shows call = scan_ms once it is settled)
+    res = None
     for _ in range(W):
+        res = None
         res = step()
     n_hits = res.n_hits
     from aha_b200 import _lib
@@ -231,6 +236,7 @@ def main():
     kernel_ms, walk_ms = [], []
     ev0.record()
     for _ in range(args.steps):
+        res = None
         res = step()
         kernel_ms.append(res.scan_ms)
         walk_ms.append(res.walk_ms)

@@ -51,10 +51,20 @@ static int32_t ensure_devices() {
 // sub-chunk is exactly six 12-byte steps (132 would need a seventh, three quarters empty)
 static void fused_geometry(uint32_t max_key_len, bool char_kernel, int32_t* chunk, int32_t* w16, int32_t* buf_bytes) {
   const uint32_t warm = max_key_len > 0 ? max_key_len - 1 : 0;
-  *chunk = char_kernel ? AHA_B200_CHAR_CHUNK : 132;
   *w16 = (int32_t)((warm + 1 + 3 + 15) & ~15u);
   if (*w16 < 16) *w16 = 16;
-  *buf_bytes = (*w16 + 32 * *chunk + 16 + 32 + 127) & ~127;  // 16 staged bytes past the tile + read slack
+  auto buf_for = [&](int32_t c) { return (*w16 + 32 * c + 16 + 32 + 127) & ~127; };  // 16 staged bytes past the tile + read slack
+  *chunk = char_kernel ? AHA_B200_CHAR_CHUNK : 132;
+  if (!char_kernel) {
+    // byte kernel: bound by table lookups per second, and every lane repeats max_key_len - 1 of them as warm-up, so the
+    // longest chunk (chunk / 4 odd: lanes in distinct banks) whose 32 per-warp buffers still fit next to the class map
+    int32_t want = kByteChunkDefault;
+    if (const char* e = getenv("AHA_B200_BYTE_CHUNK")) want = atoi(e);
+    if (want >= 36 && want <= 1024 && want % 4 == 0 && (want / 4) % 2 == 1 &&
+        (size_t)kByteWarps * (size_t)(buf_for(want) + 128) + 512 <= (size_t)227 * 1024)
+      *chunk = want;
+  }
+  *buf_bytes = buf_for(*chunk);
 }
 
 static int32_t build_hot_table(const aha_dfa* d, DeviceDfa* dd) {

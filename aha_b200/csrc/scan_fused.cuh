@@ -32,6 +32,7 @@ constexpr int kMarkCapC = 2;      // ... per sub-chunk (scan_char.cuh walks two 
 #define AHA_B200_CHAR_CHUNK 126
 #endif
 constexpr int kFusedWarps = AHA_B200_CHAR_WARPS;   // warps per CTA of scan_char_kernel (register- and shared-memory-bound)
+constexpr int kByteChunkDefault = 132;  // bytes per lane of the byte kernel (AHA_B200_BYTE_CHUNK overrides; see fused_geometry)
 constexpr int kByteWarps = 32;    // warps per CTA of scan_fused_kernel<ByteGlobal>: latency-bound on L2, so as many as fit
 
 struct FusedParams {

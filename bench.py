@@ -222,8 +222,10 @@ def main():
     # stream-ordered pool keeps growing through the first calls, which would put cudaMallocAsync's mapping of
     # multi-GB hit buffers into the timed steps of C3 / C5; tools/gap_probe.py shows call = scan_ms once it is settled)
     res = None
+    keep_prev = os.environ.get("AHA_BENCH_KEEP_PREV") == "1"  # A/B: previous result still alive during the next scan
     for _ in range(W):
-        res = None
+        if not keep_prev:
+            res = None
         res = step()
     n_hits = res.n_hits
     from aha_b200 import _lib
@@ -236,7 +238,8 @@ def main():
     kernel_ms, walk_ms = [], []
     ev0.record()
     for _ in range(args.steps):
-        res = None
+        if not keep_prev:
+            res = None
         res = step()
         kernel_ms.append(res.scan_ms)
         walk_ms.append(res.walk_ms)

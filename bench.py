@@ -218,12 +218,16 @@ def main():
     def step():
         return ac.scan_device(text, doc_off)
 
-    # a caller keeps one result in flight: the previous one is released before the next scan (with both alive the
-    # stream-ordered pool keeps growing through the first calls, which would put cudaMallocAsync's mapping of
-    # multi-GB hit buffers into the timed steps of C3 / C5; tools/gap_probe.py shows call = scan_ms once it is settled)
-    res = None
-    keep_prev = os.environ.get("AHA_BENCH_KEEP_PREV") == "1"  # A/B: previous result still alive during the next scan
-    for _ in range(W):
+    # Results in flight.  With the previous result still alive during the next scan the hit buffers alternate between
+    # two pool blocks (C2: 632-643 GB/s against 592-620 GB/s when the block just freed is taken again, same box, A/B in
+    # tools/chunk_ab.sh).  With multi-GB results (C3, C5) two alive make the stream-ordered pool grow through the
+    # first calls, which puts cudaMallocAsync's mapping of the buffers into the timed steps (tools/gap_probe.py), so
+    # there the previous result is released first.  AHA_BENCH_KEEP_PREV=0|1 forces either.
+    res = step()
+    keep_prev = 12 * res.n_hits < (2 << 30)
+    if os.environ.get("AHA_BENCH_KEEP_PREV") in ("0", "1"):
+        keep_prev = os.environ["AHA_BENCH_KEEP_PREV"] == "1"
+    for _ in range(W - 1):
         if not keep_prev:
             res = None
         res = step()
@@ -312,6 +316,7 @@ def main():
                        "dfa_states": info["n_states"], "byte_classes": info["n_classes"], "hot_states": info["hot_states"],
                        "max_key_len": info["max_key_len"], "hits_per_gpu_step": int(n_hits),
                        "l2": "input (%.1f GB) larger than L2, no flush needed" % (total / 1e9),
+                       "results_in_flight": 2 if keep_prev else 1,
                        "impl": "two-pass" if os.environ.get("AHA_B200_IMPL") == "0" else (
                            "char walk -> scan -> expand" if wms > 0 else "fused byte DFA")},
             "hits_per_s": hits_all / (ms_step * 1e-3),

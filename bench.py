@@ -172,6 +172,9 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
+        # stdout carries exactly one JSON line: NCCL's own banner ("NCCL version ...", printed at NCCL_DEBUG=VERSION/INFO)
+        # would precede it.  AHA_NCCL_DEBUG=INFO brings it back for diagnostics (NVLS, rings).
+        os.environ["NCCL_DEBUG"] = os.environ.get("AHA_NCCL_DEBUG", "WARN")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     W = max(3, args.warmup)
     name = args.workload

@@ -167,14 +167,16 @@ def main():
     import aha_b200
     from aha_b200 import synth
 
+    # stdout carries exactly one JSON line: everything else that native libraries write to fd 1 (NCCL prints its
+    # version banner there) goes to stderr; the line itself is written to the saved descriptor at the end.
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
-        # stdout carries exactly one JSON line: NCCL's own banner ("NCCL version ...", printed at NCCL_DEBUG=VERSION/INFO)
-        # would precede it.  AHA_NCCL_DEBUG=INFO brings it back for diagnostics (NVLS, rings).
-        os.environ["NCCL_DEBUG"] = os.environ.get("AHA_NCCL_DEBUG", "WARN")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     W = max(3, args.warmup)
     name = args.workload
@@ -332,7 +334,8 @@ def main():
             "e2e": e2e, "gpu_launches": gpu_launches, "clocks": clocks,
             "dfa_build_s": build_s, "dfa_broadcast_ms": bcast_ms,
         }
-        print(json.dumps(line))
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
 

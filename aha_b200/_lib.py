@@ -18,7 +18,7 @@ NVCC_FLAGS = [
 
 
 def _sources():
-    out = [os.path.join(_HERE, "..", "include", "aha_b200.h")]
+    out = [os.path.join(_HERE, "..", "include", "aha_b200.h"), os.path.join(_HERE, "..", "include", "aha_synth.h")]
     for f in sorted(os.listdir(CSRC)):
         out.append(os.path.join(CSRC, f))
     return out
@@ -46,7 +46,8 @@ class Hit(C.Structure):
 class Hits(C.Structure):
     _fields_ = [
         ("hits", C.c_void_p), ("n_hits", C.c_int64), ("doc_hit_off", C.c_void_p), ("n_docs", C.c_int64),
-        ("on_device", C.c_int32), ("device", C.c_int32), ("scan_ms", C.c_double), ("walk_ms", C.c_double), ("opaque", C.c_void_p),
+        ("on_device", C.c_int32), ("device", C.c_int32), ("scan_ms", C.c_double), ("walk_ms", C.c_double), ("expand_ms", C.c_double),
+        ("opaque", C.c_void_p),
     ]
 
 
@@ -56,7 +57,7 @@ EXPORTS = [
     "aha_b200_dfa_from_cedar", "aha_b200_dfa_compile", "aha_b200_flatten_host", "aha_b200_blob_free",
     "aha_b200_dfa_blob", "aha_b200_dfa_from_blob", "aha_b200_dfa_from_device_blob", "aha_b200_dfa_info",
     "aha_b200_dfa_free", "aha_b200_scan", "aha_b200_scan_device", "aha_b200_hits_free",
-    "aha_b200_gen_text_host", "aha_b200_gen_text_device", "aha_b200_debug_char_scan",
+    "aha_b200_gen_text_host", "aha_b200_gen_text_device", "aha_b200_debug_char_scan", "aha_b200_debug_set",
 ]
 
 _lib = None
@@ -98,6 +99,7 @@ def lib():
     L.aha_b200_hits_free.argtypes = [P(Hits)]
     L.aha_b200_hits_free.restype = None
     L.aha_b200_debug_char_scan.argtypes = [vp, i64, vp, i64, i32, i64, vp, i64, P(i64), P(i64)]
+    L.aha_b200_debug_set.argtypes = [i32, i32]
     L.aha_b200_gen_text_host.argtypes = [i32, u64, i64, i64, vp]
     L.aha_b200_gen_text_device.argtypes = [i32, u64, i64, i64, vp, vp]
     _lib = L

@@ -143,7 +143,7 @@ class ScanResult:
         self._ph = ph
         h = ph.contents
         self.n_hits, self.n_docs, self.on_device, self.scan_ms = h.n_hits, h.n_docs, bool(h.on_device), h.scan_ms
-        self.walk_ms = h.walk_ms
+        self.walk_ms, self.expand_ms = h.walk_ms, h.expand_ms
 
     def __del__(self):
         try:

@@ -8,7 +8,7 @@
 #include <memory>
 
 #include "api_internal.cuh"
-#include "gen.cuh"
+#include "../../include/aha_synth.h"
 #include "char_table.hpp"
 #include "char_walk.cuh"
 #include "scan_common.cuh"
@@ -24,10 +24,24 @@ thread_local std::string g_err;
 std::atomic<long long> g_kernel_launches{0};
 static std::mutex g_mu;
 static std::vector<int> g_devices;  // devices selected by aha_b200_init
-// 0: two-pass v1 kernels (checker), 1: fused single-pass kernel (default); env AHA_B200_IMPL, read per call
-static int scan_impl() {
-  const char* e = getenv("AHA_B200_IMPL");
-  return (e && e[0] == '0') ? 0 : 1;
+
+// the environment is read once, when the library is first used; aha_b200_debug_set changes a knob afterwards
+Knobs& knobs() {
+  static Knobs k = [] {
+    Knobs v;
+    auto num = [](const char* name, int dflt) {
+      const char* e = getenv(name);
+      return e && *e ? atoi(e) : dflt;
+    };
+    v.no_char = num("AHA_B200_NO_CHAR", 0) == 1;
+    const char* impl = getenv("AHA_B200_IMPL");
+    v.force_v1 = impl && impl[0] == '0';
+    v.byte_chunk = num("AHA_B200_BYTE_CHUNK", 0);
+    v.e2e_chunk_mb = num("AHA_B200_E2E_CHUNK_MB", 64);
+    if (v.e2e_chunk_mb <= 0) v.e2e_chunk_mb = 64;
+    return v;
+  }();
+  return k;
 }
 
 static int32_t ensure_devices() {
@@ -58,8 +72,7 @@ static void fused_geometry(uint32_t max_key_len, bool char_kernel, int32_t* chun
   if (!char_kernel) {
     // byte kernel: bound by table lookups per second, and every lane repeats max_key_len - 1 of them as warm-up, so the
     // longest chunk (chunk / 4 odd: lanes in distinct banks) whose 32 per-warp buffers still fit next to the class map
-    int32_t want = kByteChunkDefault;
-    if (const char* e = getenv("AHA_B200_BYTE_CHUNK")) want = atoi(e);
+    int32_t want = knobs().byte_chunk ? knobs().byte_chunk : kByteChunkDefault;
     if (want >= 36 && want <= 1024 && want % 4 == 0 && (want / 4) % 2 == 1 &&
         (size_t)kByteWarps * (size_t)(buf_for(want) + 128) + 512 <= (size_t)227 * 1024)
       *chunk = want;
@@ -69,8 +82,6 @@ static void fused_geometry(uint32_t max_key_len, bool char_kernel, int32_t* chun
 
 static int32_t build_hot_table(const aha_dfa* d, DeviceDfa* dd) {
   dd->hot = HotTable();
-  const char* off = getenv("AHA_B200_NO_CHAR");
-  if (off && off[0] == '1') return AHA_OK;
   int32_t chunk, w16, buf;
   fused_geometry(d->header.max_key_len, true, &chunk, &w16, &buf);
   const size_t total_smem = 227 * 1024;
@@ -110,28 +121,46 @@ static int32_t build_hot_table(const aha_dfa* d, DeviceDfa* dd) {
 static int32_t upload(aha_dfa* d) {
   int32_t rc = ensure_devices();
   if (rc) return rc;
-  int prev = 0;
-  AHA_CUDA(cudaGetDevice(&prev));
-  for (int dev : g_devices) {
+  DeviceGuard guard;  // the caller's current device is restored on every path
+  std::vector<int> devices;
+  {
+    std::lock_guard<std::mutex> lk(g_mu);
+    devices = g_devices;
+  }
+  for (int dev : devices) {
     AHA_CUDA(cudaSetDevice(dev));
-    DeviceDfa dd;
+    d->dev.emplace_back();
+    DeviceDfa& dd = d->dev.back();
     dd.device = dev;
     AHA_CUDA(cudaMalloc(&dd.blob, d->blob.size()));
     AHA_CUDA(cudaMemcpy(dd.blob, d->blob.data(), d->blob.size(), cudaMemcpyHostToDevice));
     dd.view = view_of(d->header, dd.blob);
     rc = build_hot_table(d, &dd);
     if (rc) return rc;
-    d->dev.push_back(dd);
   }
-  AHA_CUDA(cudaSetDevice(prev));
   return AHA_OK;
+}
+
+static void free_dfa(aha_dfa* d) {
+  if (!d) return;
+  DeviceGuard guard;
+  for (auto& dd : d->dev) {
+    cudaSetDevice(dd.device);
+    dd.idle.clear();  // workspaces (their destructor frees on dd.device)
+    if (dd.blob) cudaFree(dd.blob);
+    if (dd.hot.dev) cudaFree(dd.hot.dev);
+  }
+  delete d;
 }
 
 static int32_t finish_dfa(std::unique_ptr<aha_dfa> d, aha_dfa** out) {
   std::string err;
   if (!parse_blob(d->blob.data(), (int64_t)d->blob.size(), &d->header, &err)) return set_err(AHA_ERR_ARG, err);
   int32_t rc = upload(d.get());
-  if (rc) return rc;
+  if (rc) {
+    free_dfa(d.release());  // device copies made so far
+    return rc;
+  }
   *out = d.release();
   return AHA_OK;
 }
@@ -142,7 +171,7 @@ using namespace aha;
 
 extern "C" {
 
-int32_t aha_b200_version(void) { return 100; }
+int32_t aha_b200_version(void) { return 200; }
 int64_t aha_b200_kernel_launches(void) { return (int64_t)aha::g_kernel_launches.load(); }
 const char* aha_b200_last_error(void) { return g_err.c_str(); }
 
@@ -151,6 +180,7 @@ int32_t aha_b200_init(const int32_t* devices, int32_t n) {
   cudaError_t e = cudaGetDeviceCount(&count);
   if (e != cudaSuccess || count == 0)
     return set_err(AHA_ERR_CUDA, std::string("no CUDA device: libaha_b200 has no CPU fallback (") + cudaGetErrorString(e) + ")");
+  knobs();
   std::lock_guard<std::mutex> lk(g_mu);
   g_devices.clear();
   if (devices == nullptr || n <= 0) {
@@ -289,17 +319,17 @@ int64_t aha_b200_dfa_info(const aha_dfa* d, int32_t what) {
   }
 }
 
-void aha_b200_dfa_free(aha_dfa* d) {
-  if (!d) return;
-  int prev = 0;
-  cudaGetDevice(&prev);
-  for (auto& dd : d->dev) {
-    cudaSetDevice(dd.device);
-    cudaFree(dd.blob);
-    if (dd.hot.dev) cudaFree(dd.hot.dev);
+void aha_b200_dfa_free(aha_dfa* d) { free_dfa(d); }
+
+int32_t aha_b200_debug_set(int32_t knob, int32_t value) {
+  Knobs& k = knobs();
+  switch (knob) {
+    case 0: k.no_char = value != 0; return AHA_OK;
+    case 1: k.force_v1 = value != 0; return AHA_OK;
+    case 2: k.byte_chunk = value; return AHA_OK;
+    case 3: k.e2e_chunk_mb = value > 0 ? value : 64; return AHA_OK;
+    default: return set_err(AHA_ERR_ARG, "unknown knob");
   }
-  cudaSetDevice(prev);
-  delete d;
 }
 
 int32_t aha_b200_debug_char_scan(const uint8_t* blob, int64_t blob_bytes, const uint8_t* text, int64_t n, int32_t chunk,

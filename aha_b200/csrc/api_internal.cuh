@@ -4,6 +4,7 @@
 
 #include <atomic>
 #include <cstdio>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -30,15 +31,114 @@ inline int32_t set_err(int32_t code, const std::string& m) {
     }                                                                                                \
   } while (0)
 
-// character automaton placed in shared memory by scan_char_kernel (built at upload time from the blob)
+// restores the caller's current device when a function that switches devices returns (any path)
+struct DeviceGuard {
+  int prev = -1;
+  DeviceGuard() { cudaGetDevice(&prev); }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+// character automaton placed in shared memory by char_walk_kernel (built at upload time from the blob)
 struct HotTable {
   bool ok = false;            // dictionary is whole-UTF-8-unit and fits the shared-memory budget
   uint32_t n_hot = 0;         // character-level states resident in shared memory
   uint32_t n_root = 0, m = 0, m_pad = 0, n_mwords = 0;
   uint32_t lo[3] = {0, 0, 0}, n[3] = {0, 0, 0}, off[3] = {0, 0, 0};
-  uint8_t* dev = nullptr;     // one allocation: root | val | check | gfail | ref_rec
+  uint8_t* dev = nullptr;     // one allocation: root | val | check | gfail | ref_rec | mbits
   size_t off_root = 0, off_val = 0, off_check = 0, off_gfail = 0, off_ref = 0, off_mbits = 0;
   size_t smem_bytes = 0;
+};
+
+// ---- device memory that outlives a call --------------------------------------------------------------------
+// One grow-only device allocation.  A warm scan call performs no CUDA allocation at all: every scratch array of
+// the pipeline is a slot of the Workspace it runs in, every result buffer comes from the per-device DevCache.
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);  // growth only: synchronises the device, never on a warm call
+    p = nullptr;
+    cap = 0;
+    const size_t want = ((bytes + bytes / 8 + 255) & ~size_t(255));  // head room: slightly larger inputs do not grow again
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) {
+      e = cudaMalloc(&p, (bytes + 255) & ~size_t(255));
+      if (e != cudaSuccess) return e;
+      cap = (bytes + 255) & ~size_t(255);
+      return cudaSuccess;
+    }
+    cap = want;
+    return cudaSuccess;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <class T> T* as() const { return static_cast<T*>(p); }
+};
+
+// what the device reports at the end of a scan (one small D2H copy per call)
+struct ScanStatus {
+  unsigned long long total_hits;
+  unsigned int n_direct;   // tiles delivered by the direct pass (diagnostics)
+  unsigned int bad_docs;   // doc_off violations seen by validate_docs_kernel
+};
+
+enum WsSlot {
+  kWsStore = 0,      // character path: event store
+  kWsTileMeta,
+  kWsTileHits,
+  kWsTileDoc,
+  kWsDirectList,
+  kWsTilePrefix,
+  kWsScanTmp,
+  kWsLeadCounts,
+  kWsTileLead,
+  kWsDocLead,
+  kWsStatus,         // ScanStatus + counters (device)
+  kWsTileState,      // byte path: look-back state
+  kWsScratch,
+  kWsEvScratch,
+  kWsMarks,
+  kWsCounts,         // per-document machines: counts / offsets / scratch
+  kWsOffsets,
+  kWsDocScratch,
+  kWsAligned,        // aligned copy of a text whose device pointer is not 16-byte aligned
+  kWsSlots
+};
+
+// Scratch of one scan call in flight on one device.  Acquired from the automaton's pool for the duration of a call
+// (calls from several host threads get one each) and handed back when the call's last kernel has finished.
+struct Workspace {
+  int device = -1;
+  DevBuf slot[kWsSlots];
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, evw0 = nullptr, evw1 = nullptr, evx0 = nullptr, evx1 = nullptr;
+  ScanStatus* h_status = nullptr;  // pinned
+  cudaError_t init(int dev) {
+    device = dev;
+    cudaError_t e;
+    for (cudaEvent_t* ev : {&ev0, &ev1, &evw0, &evw1, &evx0, &evx1})
+      if ((e = cudaEventCreate(ev)) != cudaSuccess) return e;
+    return cudaMallocHost(&h_status, sizeof(ScanStatus));
+  }
+  ~Workspace() {
+    if (device < 0) return;
+    DeviceGuard g;
+    cudaSetDevice(device);
+    for (auto& s : slot) s.release();
+    for (cudaEvent_t ev : {ev0, ev1, evw0, evw1, evx0, evx1})
+      if (ev) cudaEventDestroy(ev);
+    if (h_status) cudaFreeHost(h_status);
+  }
+  template <class T> cudaError_t get(WsSlot s, size_t count, T** out) {
+    cudaError_t e = slot[s].ensure((count ? count : 1) * sizeof(T));
+    *out = slot[s].as<T>();
+    return e;
+  }
 };
 
 struct DeviceDfa {
@@ -46,21 +146,46 @@ struct DeviceDfa {
   uint8_t* blob = nullptr;  // device copy of the whole blob
   DfaView view;             // device pointers
   HotTable hot;
+  // scan workspaces that are not in use (guarded by pool_mu of the owning aha_dfa)
+  std::vector<std::unique_ptr<Workspace>> idle;
+  double hits_per_byte = -1.0;  // largest hit density seen so far on this device: sizes the hit buffer up front
 };
 
-// workspace of one scan call: everything is stream-ordered (cudaMallocAsync) so repeated calls
-// reuse the pool without synchronising frees.
+// Result buffers (hits, doc_hit_off) are handed to the caller and come back through aha_b200_hits_free: they are
+// recycled through a per-device cache, so a steady stream of equally sized scans allocates nothing.
+struct DevCache {
+  struct Entry { void* p; size_t bytes; cudaEvent_t ev; };
+  std::mutex mu;
+  std::vector<Entry> free_list, in_use;
+  size_t cached = 0;
+  static constexpr size_t kMaxEntries = 16;
+  void* acquire(size_t bytes, cudaStream_t st, size_t* got);
+  void release(void* p, size_t bytes, cudaStream_t st);
+  void trim();
+};
+DevCache& dev_cache(int device);
+
 struct HitsOwner {
   int device = 0;
   cudaStream_t stream = nullptr;
-  void* dev_hits = nullptr;
-  void* dev_doc_hit_off = nullptr;
+  void* dev_hits = nullptr;          // from DevCache
+  size_t dev_hits_bytes = 0;
+  void* dev_doc_hit_off = nullptr;   // from DevCache
+  size_t dev_doc_hit_off_bytes = 0;
   void* host_hits = nullptr;         // pinned (recycled through PinnedPool)
   void* host_doc_hit_off = nullptr;  // pinned
   size_t host_hits_bytes = 0, host_doc_hit_off_bytes = 0;
-  void* dev_text = nullptr;          // owned copy made by aha_b200_scan
-  void* dev_doc_off = nullptr;
 };
+
+// test / diagnostics knobs, read from the environment once (aha_b200_init or first use) and settable through
+// aha_b200_debug_set; none of them selects an alternate implementation of the default path
+struct Knobs {
+  int no_char = 0;          // AHA_B200_NO_CHAR=1: byte automaton even when the character tables fit
+  int force_v1 = 0;         // AHA_B200_IMPL=0: two-pass checker kernels (the fallback for keys > 1024 bytes)
+  int byte_chunk = 0;       // AHA_B200_BYTE_CHUNK: bytes per lane of the byte kernel (0 = default)
+  int e2e_chunk_mb = 64;    // AHA_B200_E2E_CHUNK_MB: run size of the host pipeline
+};
+Knobs& knobs();
 
 }  // namespace aha
 
@@ -68,9 +193,9 @@ struct aha_dfa {
   std::vector<uint8_t> blob;  // host copy
   aha::BlobHeader header;
   std::vector<aha::DeviceDfa> dev;
-  mutable double hits_per_byte = -1.0;  // largest hit density seen so far: sizes the hit buffer of the fused scan
-  const aha::DeviceDfa* on(int device) const {
-    for (const auto& d : dev)
+  mutable std::mutex pool_mu;
+  aha::DeviceDfa* on(int device) const {
+    for (auto& d : const_cast<aha_dfa*>(this)->dev)
       if (d.device == device) return &d;
     return nullptr;
   }

@@ -4,7 +4,7 @@
 #pragma once
 #include <cstdint>
 
-#include "gen.cuh"  // AHA_HD
+#include "../../include/aha_synth.h"  // AHA_HD
 
 namespace aha {
 

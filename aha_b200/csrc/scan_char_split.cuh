@@ -1,16 +1,22 @@
-// scan_char_split.cuh -- the character-automaton scan as THREE kernels instead of one fused kernel:
+// scan_char_split.cuh -- the character-automaton scan as a pipeline of kernels, all launched back to back with no
+// host round trip between them:
 //
-//   1. char_walk_kernel    persistent walkers (same tables, staging and interleaved walk as scan_char.cuh).  A tile's
-//                          events go to its own slice of a global event store, its per-sub-chunk counts to tile_meta[],
-//                          its hit total to tile_hits[].  Nothing is ordered, nobody waits for anybody.
+//   0. tile_doc_kernel     which document every tile starts in (one binary search per tile, off the walkers' path).
+//   1. char_walk_kernel    persistent walkers (tables in shared memory, TMA-staged text, two interleaved sub-chunks per
+//                          lane).  A tile's events go to its own slice of a global event store (4 bytes per event), its
+//                          per-sub-chunk event counts to tile_meta[], its hit total to tile_hits[].  Nothing is ordered,
+//                          nobody waits for anybody.
 //   2. cub exclusive scan  over tile_hits[] -> tile_prefix[] (global position of every tile's first hit).
 //   3. char_expand_kernel  one warp per tile at FULL occupancy: events -> ref_rec[] -> Aha::Hit records at their final
-//                          position.  The L2 round trips that stall a 16-warp walker CTA are hidden by thousands of warps.
+//                          position.  The L2 round trips that would stall a 16-warp walker CTA are hidden by thousands
+//                          of warps.  Writes beyond the hit buffer's capacity are dropped; the total is read by the host
+//                          once, at the end of the call, and only an overflow re-runs this kernel with a larger buffer.
 //   4. char_direct_kernel  the few tiles the walk could not finish (malformed UTF-8, more events than a slice holds):
-//                          byte automaton over the staged tile, now with known offsets.
+//                          byte automaton over the staged tile, now with known offsets.  Always launched; reads the
+//                          length of its list from device memory.
 //
-// Document starts travel inside the event stream as marker events (ref = kMarkRef, end = document index): no separate
-// marker arrays, no marker overflow.  Output order = (tile, lane, sub-chunk, sequence) = reference order.
+// Document starts travel inside the event stream as marker events: no separate marker arrays, no marker overflow.
+// Output order = (tile, lane, sub-chunk, sequence) = reference order.
 #pragma once
 #include "scan_char.cuh"
 
@@ -18,13 +24,8 @@ namespace aha {
 
 constexpr int kStoreSlotsC = 16;                      // event slots per sub-chunk in the store (more: direct pass)
 constexpr int kStoreSlots = kStoreSlotsC * kChains;   // per lane
-#ifndef AHA_B200_EXPAND_ROUNDS
-#define AHA_B200_EXPAND_ROUNDS 1
-#endif
-constexpr int kExpandRounds = AHA_B200_EXPAND_ROUNDS;  // rounds of 32 events a warp of char_expand_kernel keeps in flight
-                                                       // (measured on C2: 1 -> 0.91 ms, 4 -> 1.03 ms: occupancy wins)
-constexpr uint32_t kMarkRef = 0xFFFFFFFFu;            // marker event: `end` holds a document index
 constexpr uint32_t kTileDirect = 0x80000000u;         // tile_hits[] flag: the tile is delivered by char_direct_kernel
+static_assert(32 * AHA_B200_CHAR_CHUNK < (1 << 15), "an event carries a 15-bit offset relative to its tile");
 
 // which document a tile starts in: looked up once per tile by tile_doc_kernel, so that the walkers (whose
 // consecutive tiles are megabytes apart) load one record a tile ahead instead of running a binary search
@@ -37,12 +38,12 @@ struct alignas(16) TileDoc {
 struct SplitParams {
   CharParams c;
   const TileDoc* tile_doc;   // [n_tiles]
-  CharEvent* store;          // [n_tiles][kStoreSlotsC][32 lanes][kChains]: slot-major, event i of every sub-chunk side by side
-  uint32_t* tile_meta;       // [n_tiles][32][kChains]  hits:16 | events:16 of a sub-chunk
+  uint32_t* store;           // [n_tiles][kStoreSlotsC][32 lanes][kChains]: slot-major, event i of every sub-chunk side by side
+  uint32_t* tile_meta;       // [n_tiles][32]  events of sub-chunk 0 | events of sub-chunk 1 << 16; direct tiles: hits of the lane
   uint32_t* tile_hits;       // [n_tiles + 1] hits of the tile | kTileDirect
   const uint64_t* tile_prefix;  // [n_tiles + 1] exclusive prefix of the hits (kernels 3 and 4)
   uint32_t* direct_list;     // [n_tiles] tiles for char_direct_kernel
-  unsigned int* n_direct_list;
+  ScanStatus* status;        // total_hits, n_direct (= length of direct_list), bad_docs
 };
 
 __global__ void tile_doc_kernel(const int64_t* doc_off, int64_t n_docs, int64_t tile, int64_t n_tiles, TileDoc* out) {
@@ -53,10 +54,10 @@ __global__ void tile_doc_kernel(const int64_t* doc_off, int64_t n_docs, int64_t 
   out[t] = TileDoc{ds, (int32_t)(doc_off[d + 1] - ds), (int32_t)d};
 }
 
-__global__ void tile_hits_to_u64_kernel(const uint32_t* tile_hits, int64_t n, uint64_t* out) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) out[i] = tile_hits[i] & ~kTileDirect;
-}
+// tile_hits[] as the scan's input: the direct flag stripped, widened to 64 bits
+struct TileHitsToU64 {
+  __host__ __device__ __forceinline__ uint64_t operator()(const uint32_t& x) const { return (uint64_t)(x & ~kTileDirect); }
+};
 
 // ---- 1. walk ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __grid_constant__ SplitParams Q) {
@@ -131,11 +132,6 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
     const int64_t cd = td_next.doc, cdoc_start = td_next.doc_start, cdoc_end = td_next.doc_start + td_next.doc_len;
     if (t + W < F.n_tiles) td_next = Q.tile_doc[t + W];  // used a whole tile later
     const bool one_doc = cdoc_start <= tile_start && cdoc_end >= tile_end;
-    uint64_t tl = 0, dlb = 0;
-    if (chars) {
-      tl = F.tile_lead[t];
-      if (one_doc) dlb = p.doc_lead_base[cd];
-    }
     if (bulk_end > origin) {
       mbar_wait(bar, parity);
       parity ^= 1u;
@@ -144,7 +140,9 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
 
     const int64_t a = min(tile_start + (int64_t)lane * F.chunk, tile_end);
     const int64_t b = min(a + (int64_t)F.chunk, tile_end);
-    uint32_t lead0[kChains] = {0, 0};
+    // character units: unit starts of the tile in front of each sub-chunk (the event offsets count from the tile start)
+    uint32_t rel0[kChains] = {0, 0};
+    uint32_t lead_doc = 0;  // direct pass only: characters of the lane's first document in front of the lane
     if (chars) {
       const int64_t a1 = min(a + sub, b);
       const uint32_t mine0 = count_leads_smem(sbuf, origin, a, a1);
@@ -154,23 +152,22 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
         uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
         if (lane >= o) incl += v;
       }
-      const uint64_t before_a = tl + (incl - mine);
-      if (a < b) lead0[0] = (uint32_t)(before_a - (one_doc ? dlb : p.doc_lead_base[last_le(p.doc_off, p.n_docs, a)]));
-      if (a1 < b) lead0[1] = (uint32_t)(before_a + mine0 - (one_doc ? dlb : p.doc_lead_base[last_le(p.doc_off, p.n_docs, a1)]));
+      rel0[0] = incl - mine;
+      rel0[1] = rel0[0] + mine0;
     }
 
-    CharEvent* my_ev = pin_ptr(Q.store + (size_t)t * 32 * kStoreSlots + lane * kChains);
-    uint32_t n_ev[kChains] = {0, 0}, n_hit[kChains] = {0, 0};
-    bool lookup = false;
+    uint32_t* my_ev = pin_ptr(Q.store + (size_t)t * 32 * kStoreSlots + lane * kChains);
+    uint32_t n_ev[kChains] = {0, 0};
     auto on_doc = [&](int c, int64_t d, uint32_t nev) {  // marker event in the stream of sub-chunk c
-      if (nev < (uint32_t)kStoreSlotsC * 64u) my_ev[nev + c] = CharEvent{(int32_t)d, kMarkRef};  // nev in steps of 64 (kLean)
+      if (nev < (uint32_t)kStoreSlotsC * 64u) my_ev[nev + c] = kEvMark | (uint32_t)d;  // nev in steps of 64
       n_ev[c] += 64u;
     };
     const int32_t stage_end = (int32_t)(want_end - origin);
-    const bool ok = chars ? char_tile_walk<true, kStoreSlotsC, true, true>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start,
-                                                                     cdoc_end, lead0, my_ev, n_ev, n_hit, lookup, on_doc)
-                          : char_tile_walk<false, kStoreSlotsC, true, true>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start,
-                                                                      cdoc_end, lead0, my_ev, n_ev, n_hit, lookup, on_doc);
+    const int32_t rel_base = 1 - (int32_t)(tile_start - origin);
+    const bool ok = chars ? char_tile_walk<true, kStoreSlotsC>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start,
+                                                                cdoc_end, rel_base, rel0, my_ev, n_ev, on_doc)
+                          : char_tile_walk<false, kStoreSlotsC>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start,
+                                                                 cdoc_end, rel_base, rel0, my_ev, n_ev, on_doc);
     n_ev[0] >>= 6;
     n_ev[1] >>= 6;
     const bool bad = __any_sync(0xffffffffu, !ok);
@@ -178,67 +175,71 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
     uint32_t n_hits = 0;
     if (bad || over) {
       // the expansion cannot use this tile's events: count with the byte automaton, deliver in char_direct_kernel
+      if (chars && a < b) {
+        const int64_t d = one_doc ? cd : last_le(p.doc_off, p.n_docs, a);
+        lead_doc = (uint32_t)(F.tile_lead[t] + rel0[0] - p.doc_lead_base[d]);
+      }
       CountSink cs;
-      fallback.walk(F, sbuf, origin, a, b, lead0[0], cs);
+      fallback.walk(F, sbuf, origin, a, b, lead_doc, cs);
       n_hits = cs.n;
-      n_hit[0] = cs.n;
-      n_hit[1] = 0;
     }
     // the staged text is not needed any more: the next tile's bulk copy flies while this tile's counts are settled
     __syncwarp();
     fence_proxy_async();  // reads of sbuf are done before the bulk copy overwrites it
     stage_tile(t + W);
     if (!(bad || over)) {
-      // hits per sub-chunk: the walk only stored events; the lane reads its own back (both sub-chunks of a slot share
-      // 16 bytes) and looks the hit counts up in the 2-bit table -- a few batched loads per tile instead of a table
+      // hits per lane: the walk only stored events; the lane reads its own back (both sub-chunks of a slot share
+      // 8 bytes) and looks the hit counts up in the 2-bit table -- a few batched loads per tile instead of a table
       // lookup inside the walk at every event
+      bool lookup = false;
       const uint32_t mx = max(n_ev[0], n_ev[1]);
       for (uint32_t i0 = 0; i0 < mx; i0 += 4) {
-        uint4 e[4];
+        uint2 e[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j)
-          if (i0 + j < mx) e[j] = *reinterpret_cast<const uint4*>(my_ev + (size_t)(i0 + j) * 64);
+          if (i0 + j < mx) e[j] = *reinterpret_cast<const uint2*>(my_ev + (size_t)(i0 + j) * 64);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          if (i0 + j < n_ev[0] && e[j].y != kMarkRef) {
-            const uint32_t cnt = (S.mbits[e[j].y >> 4] >> ((e[j].y & 15u) * 2u)) & 3u;
-            n_hit[0] += cnt;
+          if (i0 + j < n_ev[0] && !(e[j].x & kEvMark)) {
+            const uint32_t ref = e[j].x & 0xFFFFu;
+            const uint32_t cnt = (S.mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
+            n_hits += cnt;
             lookup = lookup || cnt == 0u;
           }
-          if (i0 + j < n_ev[1] && e[j].w != kMarkRef) {
-            const uint32_t cnt = (S.mbits[e[j].w >> 4] >> ((e[j].w & 15u) * 2u)) & 3u;
-            n_hit[1] += cnt;
+          if (i0 + j < n_ev[1] && !(e[j].y & kEvMark)) {
+            const uint32_t ref = e[j].y & 0xFFFFu;
+            const uint32_t cnt = (S.mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
+            n_hits += cnt;
             lookup = lookup || cnt == 0u;
           }
         }
       }
       if (lookup) {  // some output list is longer than the 2-bit table can say
+        n_hits = 0;
 #pragma unroll
         for (int c = 0; c < kChains; ++c) {
-          n_hit[c] = 0;
           for (uint32_t i = 0; i < n_ev[c]; ++i) {
-            const uint32_t ref = my_ev[i * 64 + c].ref;
-            if (ref != kMarkRef) n_hit[c] += P.t.ref_rec[ref].n;
+            const uint32_t e = my_ev[i * 64 + c];
+            if (!(e & kEvMark)) n_hits += P.t.ref_rec[e & 0xFFFFu].n;
           }
         }
       }
-      n_hits = n_hit[0] + n_hit[1];
     }
-    uint2 meta;
-    meta.x = (n_hit[0] << 16) | min(n_ev[0], 0xFFFFu);
-    meta.y = (n_hit[1] << 16) | min(n_ev[1], 0xFFFFu);
-    *reinterpret_cast<uint2*>(Q.tile_meta + ((size_t)t * 32 + lane) * kChains) = meta;
+    Q.tile_meta[(size_t)t * 32 + lane] = (bad || over) ? n_hits : (n_ev[0] | (n_ev[1] << 16));
     uint32_t T = n_hits;
     for (int o = 16; o > 0; o >>= 1) T += __shfl_xor_sync(0xffffffffu, T, o);
     if (lane == 0) {
       Q.tile_hits[t] = T | ((bad || over) ? kTileDirect : 0u);
-      if (bad || over) Q.direct_list[atomicAdd(Q.n_direct_list, 1u)] = t;
+      if (bad || over) Q.direct_list[atomicAdd(&Q.status->n_direct, 1u)] = (uint32_t)t;
     }
     t += W;
   }
 }
 
 // ---- 3. expansion: one warp per tile ---------------------------------------------------------------------------
+// An event's end offset = its tile-relative `rel` + the tile's base - the base of the document it lies in (bytes:
+// tile start / document start; characters: unit starts in front of the tile / in front of the document).  The
+// document of an event is the one of the last marker in front of it in the tile's stream, else the tile's first.
 __global__ void __launch_bounds__(256) char_expand_kernel(const __grid_constant__ SplitParams Q) {
   const CharParams& P = Q.c;
   const ScanParams& p = P.f.sp;
@@ -247,8 +248,8 @@ __global__ void __launch_bounds__(256) char_expand_kernel(const __grid_constant_
   const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   for (int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < P.f.n_tiles; t += n_warps) {
     if (Q.tile_hits[t] & kTileDirect) continue;
-    const uint2 meta = *reinterpret_cast<const uint2*>(Q.tile_meta + ((size_t)t * 32 + lane) * kChains);
-    const uint32_t n_ev0 = meta.x & 0xFFFFu, n_ev1 = meta.y & 0xFFFFu;
+    const uint32_t meta = Q.tile_meta[(size_t)t * 32 + lane];
+    const uint32_t n_ev0 = meta & 0xFFFFu, n_ev1 = meta >> 16;
     const uint32_t n_ev = n_ev0 + n_ev1;
     uint32_t ev_incl = n_ev;
     for (int o = 1; o < 32; o <<= 1) {
@@ -259,53 +260,52 @@ __global__ void __launch_bounds__(256) char_expand_kernel(const __grid_constant_
     const uint32_t E = __shfl_sync(0xffffffffu, ev_incl, 31);
     if (E == 0) continue;
     const unsigned long long prefix = Q.tile_prefix[t];
-    const CharEvent* tile_ev = Q.store + (size_t)t * 32 * kStoreSlots;
+    const uint32_t* tile_ev = Q.store + (size_t)t * 32 * kStoreSlots;
+    const TileDoc td = Q.tile_doc[t];
+    // bases as 64-bit differences: end = rel + (tile base - document base)
+    const int64_t tile_base = chars ? (int64_t)P.f.tile_lead[t] : t * (int64_t)P.f.tile;
+    int64_t delta = tile_base - (chars ? (int64_t)p.doc_lead_base[td.doc] : td.doc_start);  // warp-uniform, updated at markers
     uint32_t run = 0;
-    // kExpandRounds rounds of 32 events in flight: all event loads first, then all ref_rec loads, then the ordered stores
-    for (uint32_t base = 0; base < E; base += 32 * kExpandRounds) {
-      CharEvent ev[kExpandRounds];
-      RefRec rr[kExpandRounds];
+    for (uint32_t base = 0; base < E; base += 32) {
+      const uint32_t i = base + lane;
+      uint32_t lo = 0;
 #pragma unroll
-      for (int r = 0; r < kExpandRounds; ++r) {
-        ev[r] = CharEvent{0, kMarkRef};
-        if (base + r * 32 < E) {  // warp-uniform
-          const uint32_t i = base + r * 32 + lane;
-          uint32_t lo = 0;
-#pragma unroll
-          for (int step = 16; step > 0; step >>= 1) {
-            const uint32_t cand = lo + step;
-            const uint32_t ex = __shfl_sync(0xffffffffu, ev_excl, cand & 31);
-            if (cand < 32 && ex <= i) lo = cand;
-          }
-          const uint32_t ex = __shfl_sync(0xffffffffu, ev_excl, lo);
-          const uint32_t n0 = __shfl_sync(0xffffffffu, n_ev0, lo);
-          if (i < E) {
-            const uint32_t idx = i - ex;
-            ev[r] = idx < n0 ? tile_ev[idx * 64 + lo * kChains] : tile_ev[(idx - n0) * 64 + lo * kChains + 1];
-          }
+      for (int step = 16; step > 0; step >>= 1) {
+        const uint32_t cand = lo + step;
+        const uint32_t ex = __shfl_sync(0xffffffffu, ev_excl, cand & 31);
+        if (cand < 32 && ex <= i) lo = cand;
+      }
+      const uint32_t ex = __shfl_sync(0xffffffffu, ev_excl, lo);
+      const uint32_t n0 = __shfl_sync(0xffffffffu, n_ev0, lo);
+      uint32_t ev = 0;
+      bool live = i < E;
+      if (live) {
+        const uint32_t idx = i - ex;
+        ev = idx < n0 ? tile_ev[idx * 64 + lo * kChains] : tile_ev[(idx - n0) * 64 + lo * kChains + 1];
+      }
+      const bool mark = live && (ev & kEvMark);
+      RefRec rr = RefRec{0, 0, 0, 0};
+      if (live && !mark) rr = P.t.ref_rec[ev & 0xFFFFu];
+      int64_t my_delta = delta;
+      if (__any_sync(0xffffffffu, mark)) {
+        // document of every event of this round: the last marker at or in front of it, else the carried one
+        int64_t d_here = mark ? (int64_t)(ev & ~kEvMark) : -1;
+        for (int o = 1; o < 32; o <<= 1) {
+          const int64_t v = __shfl_up_sync(0xffffffffu, d_here, o);
+          if (lane >= o && d_here < 0) d_here = v;
         }
+        if (d_here >= 0) my_delta = tile_base - (chars ? (int64_t)p.doc_lead_base[d_here] : p.doc_off[d_here]);
+        delta = __shfl_sync(0xffffffffu, my_delta, 31);
       }
-#pragma unroll
-      for (int r = 0; r < kExpandRounds; ++r) {
-        rr[r] = RefRec{0, 0, 0, 0};
-        if (ev[r].ref != kMarkRef) rr[r] = P.t.ref_rec[ev[r].ref];
+      uint32_t len_incl = rr.n;
+      for (int o = 1; o < 32; o <<= 1) {
+        uint32_t v = __shfl_up_sync(0xffffffffu, len_incl, o);
+        if (lane >= o) len_incl += v;
       }
-#pragma unroll
-      for (int r = 0; r < kExpandRounds; ++r) {
-        if (base + r * 32 < E) {  // warp-uniform
-          uint32_t len_incl = rr[r].n;
-          for (int o = 1; o < 32; o <<= 1) {
-            uint32_t v = __shfl_up_sync(0xffffffffu, len_incl, o);
-            if (lane >= o) len_incl += v;
-          }
-          const int64_t at = (int64_t)prefix + run + (len_incl - rr[r].n);
-          if (base + r * 32 + lane < E) {
-            if (ev[r].ref == kMarkRef) p.doc_hit_off[ev[r].end] = at;
-            else if (p.hits) expand_event(p, rr[r], ev[r].end, chars, p.hits, at, P.f.hit_cap);
-          }
-          run += __shfl_sync(0xffffffffu, len_incl, 31);
-        }
-      }
+      const int64_t at = (int64_t)prefix + run + (len_incl - rr.n);
+      if (mark) p.doc_hit_off[ev & ~kEvMark] = at;
+      else if (live && p.hits) expand_event(p, rr, (int32_t)((int64_t)((ev >> 16) & 0x7FFFu) + my_delta), chars, p.hits, at, P.f.hit_cap);
+      run += __shfl_sync(0xffffffffu, len_incl, 31);
     }
   }
 }
@@ -316,6 +316,8 @@ __global__ void __launch_bounds__(128) char_direct_kernel(const __grid_constant_
   const CharParams& P = Q.c;
   const FusedParams& F = P.f;
   const ScanParams& p = F.sp;
+  const unsigned int n_list = Q.status->n_direct;
+  if (n_list == 0) return;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint8_t* s_cmap = smem;
   for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) s_cmap[i] = P.cmap_g[i];
@@ -325,7 +327,6 @@ __global__ void __launch_bounds__(128) char_direct_kernel(const __grid_constant_
   fallback.cmap_g = P.cmap_g;
   fallback.cmap = s_cmap;
   const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
-  const unsigned int n_list = *Q.n_direct_list;
   const unsigned int n_warps = gridDim.x * (blockDim.x >> 5);
   for (unsigned int k = blockIdx.x * (blockDim.x >> 5) + warp; k < n_list; k += n_warps) {
     const unsigned int t = Q.direct_list[k];
@@ -350,7 +351,7 @@ __global__ void __launch_bounds__(128) char_direct_kernel(const __grid_constant_
       if (a < b) lead0 = (uint32_t)(before_a - p.doc_lead_base[last_le(p.doc_off, p.n_docs, a)]);
     }
     // hits of the lanes in front of this one (counted by the walk kernel with the same automaton)
-    const uint32_t mine_hits = Q.tile_meta[((size_t)t * 32 + lane) * kChains] >> 16;
+    const uint32_t mine_hits = Q.tile_meta[(size_t)t * 32 + lane];
     uint32_t incl = mine_hits;
     for (int o = 1; o < 32; o <<= 1) {
       uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
@@ -360,6 +361,31 @@ __global__ void __launch_bounds__(128) char_direct_kernel(const __grid_constant_
     ds.out = p.hits; ds.doc_hit_off = p.doc_hit_off; ds.idx = (int64_t)(Q.tile_prefix[t] + (incl - mine_hits)); ds.cap = F.hit_cap;
     fallback.walk(F, sbuf, origin, a, b, lead0, ds);
   }
+}
+
+// ---- small helpers of the pipeline ---------------------------------------------------------------------------------
+// doc_off must start at 0, be non-decreasing, end at `total`, and no document may reach 2^31 bytes (Aha::Hit offsets
+// are Int32, matcher.cr:3-5): counted into status->bad_docs, reported by the host at the end of the call
+__global__ void validate_docs_kernel(const int64_t* doc_off, int64_t n_docs, int64_t total, ScanStatus* status) {
+  const int64_t d = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (d > n_docs) return;
+  bool bad = false;
+  if (d == 0 && doc_off[0] != 0) bad = true;
+  if (d == n_docs && doc_off[d] != total) bad = true;
+  if (d < n_docs) {
+    const int64_t len = doc_off[d + 1] - doc_off[d];
+    if (len < 0 || len > (int64_t)INT32_MAX) bad = true;
+  }
+  if (bad) atomicAdd(&status->bad_docs, 1u);
+}
+
+// documents that start at the very end of the text (trailing empty documents and the n_docs sentinel); publishes the
+// total for the host
+__global__ void finalize_split_kernel(const int64_t* doc_off, int64_t n_docs, int64_t total, const uint64_t* total_hits,
+                                      int64_t* doc_hit_off, ScanStatus* status) {
+  const int64_t d = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (d == 0) status->total_hits = *total_hits;
+  if (d <= n_docs && doc_off[d] >= total) doc_hit_off[d] = (int64_t)*total_hits;
 }
 
 }  // namespace aha

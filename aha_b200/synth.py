@@ -16,7 +16,19 @@ def doc_bytes(target):
     return max(BLOCK, (target // BLOCK) * BLOCK)
 
 
+_host_generator = None
+
+
+def set_host_generator(fn):
+    """fn(corpus, seed, first, nbytes) -> uint8 array.  bench.py's reference arm installs the oracle's generator
+    (same include/aha_synth.h stream) so that it builds its corpus and patterns without loading libaha_b200.so."""
+    global _host_generator
+    _host_generator = fn
+
+
 def gen_host(corpus, seed, first, nbytes):
+    if _host_generator is not None:
+        return _host_generator(corpus, seed, first, nbytes)
     out = np.empty(nbytes, np.uint8)
     check(lib().aha_b200_gen_text_host(corpus, seed, first, nbytes, out.ctypes.data))
     return out

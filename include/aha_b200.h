@@ -34,8 +34,9 @@ typedef struct aha_hits {
   int64_t n_docs;
   int32_t on_device;      /* 1: hits/doc_hit_off are device pointers (aha_b200_scan_device)  */
   int32_t device;
-  double scan_ms;         /* device time of the scan kernels only (CUDA events)              */
-  double walk_ms;         /* of which the dominant kernel (char_walk_kernel); 0 on other paths */
+  double scan_ms;         /* device time of all launches of the scan (CUDA events)           */
+  double walk_ms;         /* of which char_walk_kernel; 0 on other paths                     */
+  double expand_ms;       /* of which char_expand_kernel; 0 on other paths                   */
   void* opaque;
 } aha_hits;
 
@@ -60,8 +61,12 @@ enum aha_mode {
 };
 
 /* ---- library / devices ------------------------------------------------------------------- */
-/* Selects the CUDA devices this process scans on (one per process under torchrun; n > 1 lets a
- * single process drive several GPUs).  devices == NULL, n == 0 -> current device only.        */
+/* Selects the CUDA devices this process scans on.  One per process under torchrun; with n > 1 a
+ * single process (a Crystal host has one thread) drives several GPUs: automata built afterwards are
+ * uploaded to every selected device, and aha_b200_scan deals the batch to them in runs of whole
+ * documents, one host thread and three streams per device, hits landing in document order in one
+ * pinned buffer.  devices == NULL, n == 0 -> current device only.  Also reads the AHA_B200_*
+ * environment knobs (once).                                                                   */
 int32_t aha_b200_init(const int32_t* devices, int32_t n);
 const char* aha_b200_last_error(void);
 int32_t aha_b200_version(void);
@@ -116,13 +121,20 @@ void aha_b200_dfa_free(aha_dfa* d);
 int32_t aha_b200_scan(const aha_dfa* d, const uint8_t* text, const int64_t* doc_off, int64_t n_docs, uint32_t mode,
                       const uint8_t* sep_bits, int32_t sep_size, aha_hits** out);
 /* Same, text and doc_off already in the current device's memory; results stay on the device.
- * stream: a cudaStream_t (0 = default stream).                                                */
+ * stream: a cudaStream_t (0 = default stream).  doc_off is validated on the device (must start at
+ * 0, be non-decreasing, end at total_bytes, no document >= 2^31 bytes): AHA_ERR_ARG otherwise.
+ * The call returns when the scan has finished (the reference call is synchronous, ac.cr:280-286);
+ * inside it nothing waits for the host: a warm call makes no allocation and one host wait.   */
 int32_t aha_b200_scan_device(const aha_dfa* d, const void* dev_text, const void* dev_doc_off, int64_t n_docs,
                              int64_t total_bytes, uint32_t mode, const uint8_t* sep_bits, int32_t sep_size,
                              void* stream, aha_hits** out);
 void aha_b200_hits_free(aha_hits* h);
 
 /* ---- diagnostics ------------------------------------------------------------------------- */
+/* Test knobs (also read once from the environment): 0 = AHA_B200_NO_CHAR (byte automaton even when
+ * the character tables fit shared memory), 1 = two-pass checker kernels (AHA_B200_IMPL=0; otherwise
+ * only the path of keys > 1024 bytes), 2 = AHA_B200_BYTE_CHUNK, 3 = AHA_B200_E2E_CHUNK_MB.      */
+int32_t aha_b200_debug_set(int32_t knob, int32_t value);
 /* Host-side replay of the shared-memory character automaton the fused kernel uses (same table builder,
  * same per-lane walk, lanes emulated sequentially with `chunk`-byte owned regions) over ONE document.
  * info[0] = 1 if the dictionary is eligible (whole UTF-8 units, fits `smem_budget`), info[1] = 1 if the

@@ -1,4 +1,7 @@
-// gen.cuh -- counter-based synthetic corpora, identical bytes on host and device.
+// aha_synth.h -- counter-based synthetic corpora, identical bytes on host and device.
+// Bench / test infrastructure shared by the product library (device generator for corpora that do not fit the host,
+// aha_b200_gen_text_*) and by the CPU oracle (orc_gen_text: the reference arm of bench.py generates its own text and
+// never loads the product).  Nothing of the scan path depends on it except the AHA_HD macro.
 //
 // The stream is a sequence of independent 192-byte blocks (192 = 64 * 3, so CJK blocks end on a
 // character boundary).  Block k depends only on (corpus, seed, k); integer arithmetic only, so

@@ -22,6 +22,9 @@
 #include <thread>
 #include <atomic>
 #include <vector>
+#include <algorithm>
+
+#include "../include/aha_synth.h"  // corpus generator only (bench input), not part of the restatement
 
 namespace {
 
@@ -785,6 +788,69 @@ int64_t orc_ac_scan_count_mt(void* a, const uint8_t* text, const int64_t* doc_of
   work();
   for (auto& t : pool) t.join();
   return total.load();
+}
+
+// Order-sensitive checksum of the hit stream of a batch, document-parallel: sum over documents d and over the j-th hit
+// of d of mix(d, j, start, end, value) mod 2^64 (bench.py computes the same on the GPU's stream with torch).
+// *hash_out = checksum; returns the hit count.
+static inline uint64_t mix_hit(int64_t d, int64_t j, const Hit& h) {
+  uint64_t x = (uint64_t)(int64_t)h.start * 0x9E3779B97F4A7C15ull + (uint64_t)(int64_t)h.end * 0xC2B2AE3D27D4EB4Full +
+               (uint64_t)(int64_t)h.value * 0x165667B19E3779F9ull + (uint64_t)j * 0x85EBCA77C2B2AE63ull +
+               (uint64_t)d * 0x27D4EB2F165667C5ull;
+  x = (x ^ (uint64_t)((int64_t)x >> 29)) * 0xBF58476D1CE4E5B9ull;  // arithmetic shift: what torch's int64 >> does
+  return x;
+}
+int64_t orc_ac_scan_hash_mt(void* a, const uint8_t* text, const int64_t* doc_off, int64_t n_docs, int32_t threads, uint64_t* hash_out) {
+  AC* ac = (AC*)a;
+  std::atomic<int64_t> next(0), total(0);
+  std::atomic<uint64_t> hash(0);
+  auto work = [&]() {
+    int64_t local = 0;
+    uint64_t hsum = 0;
+    for (;;) {
+      int64_t d = next.fetch_add(1);
+      if (d >= n_docs) break;
+      int64_t j = 0;
+      match_(ac, text + doc_off[d], doc_off[d + 1] - doc_off[d], [&](int32_t idx, int32_t nid) {
+        fetch(ac, idx, nid, [&](Hit h) { hsum += mix_hit(d, j++, h); });
+      });
+      local += j;
+    }
+    total += local;
+    hash += hsum;
+  };
+  std::vector<std::thread> pool;
+  for (int t = 1; t < threads; t++) pool.emplace_back(work);
+  work();
+  for (auto& t : pool) t.join();
+  *hash_out = hash.load();
+  return total.load();
+}
+
+// synthetic corpus text (include/aha_synth.h): the reference arm of bench.py generates its own input
+int32_t orc_gen_text(int32_t corpus, uint64_t seed, int64_t first, int64_t bytes, uint8_t* out, int32_t threads) {
+  if (corpus < 0 || corpus > 2 || first < 0 || bytes < 0) return -1;
+  const int64_t end = first + bytes;
+  const int64_t k0 = first / aha::kGenBlock, k1 = (end + aha::kGenBlock - 1) / aha::kGenBlock;
+  std::atomic<int64_t> next(k0);
+  auto work = [&]() {
+    uint8_t buf[aha::kGenBlock];
+    for (;;) {
+      const int64_t ka = next.fetch_add(1024);
+      if (ka >= k1) break;
+      for (int64_t k = ka; k < std::min<int64_t>(ka + 1024, k1); ++k) {
+        aha::gen_block(corpus, seed, (uint64_t)k, buf);
+        const int64_t b0 = k * aha::kGenBlock;
+        const int64_t lo = std::max<int64_t>(first, b0), hi = std::min<int64_t>(end, b0 + aha::kGenBlock);
+        if (hi > lo) memcpy(out + (lo - first), buf + (lo - b0), (size_t)(hi - lo));
+      }
+    }
+  };
+  std::vector<std::thread> pool;
+  for (int t = 1; t < threads; t++) pool.emplace_back(work);
+  work();
+  for (auto& t : pool) t.join();
+  return 0;
 }
 
 // CedarX#match_longest(String, ignore_case, sep) (cedar.cr:1075-1121); character offsets.

@@ -64,11 +64,24 @@ def lib():
         L.orc_ac_scan_count.restype = i64
         L.orc_ac_scan_count_mt.argtypes = [vp, vp, vp, i64, i32]
         L.orc_ac_scan_count_mt.restype = i64
+        L.orc_ac_scan_hash_mt.argtypes = [vp, vp, vp, i64, i32, C.POINTER(C.c_uint64)]
+        L.orc_ac_scan_hash_mt.restype = i64
+        L.orc_gen_text.argtypes = [i32, C.c_uint64, i64, i64, vp, i32]
+        L.orc_gen_text.restype = i32
         L.orc_cedar_match_longest.argtypes = [vp, vp, i64, i32, i32, C.c_char_p, i32, i32]
         L.orc_cedar_match_longest.restype = i64
         L.orc_trie_hits.restype = vp
         _lib = L
     return _lib
+
+
+def gen_text(corpus, seed, first, nbytes, threads=None):
+    """include/aha_synth.h stream on the host cores (the reference arm of bench.py never loads the product)."""
+    out = np.empty(nbytes, np.uint8)
+    rc = lib().orc_gen_text(corpus, seed, first, nbytes, out.ctypes.data, threads or os.cpu_count() or 1)
+    if rc != 0:
+        raise ValueError("orc_gen_text: bad argument")
+    return out
 
 
 def _bytes(x):
@@ -254,3 +267,11 @@ class AC:
         a = _as_u8(text)
         off = np.ascontiguousarray(doc_off, dtype=np.int64)
         return self._L.orc_ac_scan_count_mt(self._h, a.ctypes.data, off.ctypes.data, len(off) - 1, threads)
+
+    def scan_hash_mt(self, text, doc_off, threads):
+        """(hit count, order-sensitive 64-bit checksum of the per-document hit streams)"""
+        a = _as_u8(text)
+        off = np.ascontiguousarray(doc_off, dtype=np.int64)
+        h = C.c_uint64()
+        n = self._L.orc_ac_scan_hash_mt(self._h, a.ctypes.data, off.ctypes.data, len(off) - 1, threads, C.byref(h))
+        return n, h.value

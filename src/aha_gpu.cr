@@ -27,6 +27,7 @@ lib LibAhaB200
     device : Int32
     scan_ms : Float64
     walk_ms : Float64
+    expand_ms : Float64
     opaque : Void*
   end
 

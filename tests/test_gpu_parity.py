@@ -14,18 +14,22 @@ from tests.test_oracle_kat import _rand_keys
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(autouse=True, params=["fused", "char-fused", "fused-byte", "fused-byte-records", "two-pass"])
-def scan_impl(request, monkeypatch):
-    """every parity test runs against all device paths: the default (character automaton in shared memory where the
-    dictionary allows: walk / scan / expand kernels, else the fused byte-automaton kernel), the single-kernel variant
-    of the character path, the fused kernel forced to the byte automaton (both deliveries), and the two-pass baseline"""
-    monkeypatch.setenv("AHA_B200_IMPL", "0" if request.param == "two-pass" else "1")
-    monkeypatch.setenv("AHA_B200_NO_CHAR", "1" if request.param.startswith("fused-byte") else "0")
-    # the byte kernel delivers from {state, end} events expanded after the walk; "records" is its older delivery
-    # (lists expanded inside the walk into a lane-private ring), still the path of sep scans
-    monkeypatch.setenv("AHA_B200_BYTE_RECORDS", "1" if request.param == "fused-byte-records" else "0")
-    monkeypatch.setenv("AHA_B200_CHAR_IMPL", "fused" if request.param == "char-fused" else "split")
-    return request.param
+@pytest.fixture(autouse=True, params=["default", "byte", "two-pass"])
+def scan_impl(request):
+    """every parity test runs against the default device path (character automaton in shared memory where the
+    dictionary allows: walk / scan / expand kernels, else the fused byte-automaton kernel), the fused kernel forced to
+    the byte automaton, and the two-pass checker kernels (the path of keys > 1024 bytes); the heavy full-size tests
+    run on the default path only.  The knobs are test hooks of the C ABI (aha_b200_debug_set), not product switches."""
+    from aha_b200 import _lib
+    heavy = request.node.get_closest_marker("heavy") is not None
+    if heavy and request.param != "default":
+        pytest.skip("full-size test: default path only")
+    L = _lib.lib()
+    L.aha_b200_debug_set(0, 1 if request.param == "byte" else 0)
+    L.aha_b200_debug_set(1, 1 if request.param == "two-pass" else 0)
+    yield request.param
+    L.aha_b200_debug_set(0, 0)
+    L.aha_b200_debug_set(1, 0)
 
 
 def as_tuples(h):
@@ -288,6 +292,7 @@ def _stream_hash(hits_i32, base=0):
     return int(x.sum().item())
 
 
+@pytest.mark.heavy
 def test_full_size_c2_properties():
     """BASELINE config C2 at full size (10 k CJK patterns, 2 048 documents of 1 MiB = 2.1 GB resident in HBM).  The oracle
     cannot replay 80 M hits record by record in test time, so the full-size run is checked through size-independent
@@ -342,6 +347,7 @@ def test_hit_density_swings_between_calls():
             assert res.hits().tobytes() == want.tobytes()
 
 
+@pytest.mark.heavy
 def test_large_c3_properties():
     """BASELINE config C3's dictionary (100 k mixed patterns: the byte automaton in global memory) over 1 GiB of MIX
     text, checked like the full-size C2 run: oracle total count over all text, every 61st document hit for hit,
@@ -385,6 +391,7 @@ def test_large_c3_properties():
     assert np.array_equal(r.doc_hit_off(), want_off) and r.hits().tobytes() == want.tobytes()
 
 
+@pytest.mark.heavy
 def test_scaled_c5_million_patterns():
     """BASELINE config C5's dictionary (1 M mixed patterns: a 3.2 GB byte automaton, far beyond L2) over 256 MiB of
     MIX text: oracle total count over all text, every 37th document hit for hit, halves against the whole, and the

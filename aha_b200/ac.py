@@ -266,8 +266,20 @@ class AC:
                 raise AhaError(-1, "not an aha_b200 automaton file")
             parts = []
             for _ in range(4):
-                (n,) = struct.unpack("<q", f.read(8))
+                head = f.read(8)
+                if len(head) != 8:
+                    raise AhaError(-1, "corrupt automaton file: truncated")
+                (n,) = struct.unpack("<q", head)
+                if n < 0:
+                    raise AhaError(-1, "corrupt automaton file")
                 parts.append(f.read(n))
+                if len(parts[-1]) != n:
+                    raise AhaError(-1, "corrupt automaton file: truncated")
+        if len(parts[1]) % 4 or len(parts[3]) % 4:
+            raise AhaError(-1, "corrupt automaton file")
+        n = len(parts[1]) // 4
+        if n < 256 or len(parts[0]) != 12 * n or len(parts[2]) != 8 * n:  # the file is an untrusted input
+            raise AhaError(-1, "corrupt automaton file: array sizes disagree")
         nodes = np.frombuffer(parts[0], dtype=np.uint8).copy()
         fails = np.frombuffer(parts[1], dtype=np.int32).copy()
         output = np.frombuffer(parts[2], dtype=np.int32).reshape(-1, 2).copy()

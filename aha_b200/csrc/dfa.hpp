@@ -104,7 +104,13 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
     const int32_t id = slot_of[s];
     const int32_t b = base_of(id);
     uint8_t sib = nodes[id].child;
-    if (sib == 0 && b > 0) sib = nodes[b].sibling;
+    if (sib == 0 && b > 0) {
+      if (b >= array_size) {  // the arrays may come from a file (AC.load): never index past them
+        *err = "corrupt node: base out of range";
+        return false;
+      }
+      sib = nodes[b].sibling;
+    }
     while (sib != 0) {
       const int32_t to = b ^ sib;
       if (to < 0) break;
@@ -160,6 +166,10 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
       if (key_lens[v] < 0x7FFFFFFFu) out_val.push_back(v);
       if (!(output[e].next >= 0)) break;
       e = output[e].next;
+      if (e >= array_size) {
+        *err = "output chain leaves the array";
+        return false;
+      }
       if (++guard > 1 << 20) {
         *err = "output chain loop";
         return false;
@@ -234,6 +244,42 @@ inline bool parse_blob(const uint8_t* blob, int64_t bytes, BlobHeader* h, std::s
   memcpy(h, blob, sizeof(BlobHeader));
   if (h->magic != kBlobMagic || h->version != 2 || h->total_bytes != static_cast<uint64_t>(bytes)) {
     *err = "bad blob header";
+    return false;
+  }
+  // a blob may arrive from a file or from another rank: every section must lie inside it and every index it holds
+  // must stay inside the section it points into, or the kernels would read out of bounds
+  const uint64_t S = h->n_states, C = h->n_classes, K = h->n_keys, O = h->n_out, T = h->total_bytes;
+  if (S == 0 || S > kStateMask || C == 0 || C > 256 || K > 0x7FFFFFFFull || O > 0xFFFFFFFFull) {
+    *err = "bad blob header: counts out of range";
+    return false;
+  }
+  auto inside = [&](uint64_t off, uint64_t n, uint64_t width) {
+    return (off & 3) == 0 && off <= T && n <= (T - off) / width;
+  };
+  if (!inside(h->off_classmap, 256, 1) || !inside(h->off_delta, S * C, 4) || !inside(h->off_out_off, S + 1, 4) ||
+      !inside(h->off_out_val, O, 4) || !inside(h->off_key_len, K, 4) || !inside(h->off_key_tail, K, 4) ||
+      !inside(h->off_depth, S, 2) || !inside(h->off_fail, S, 4)) {
+    *err = "bad blob header: section out of bounds";
+    return false;
+  }
+  const DfaView v = view_of(*h, blob);
+  for (int b = 0; b < 256; ++b)
+    if (v.classmap[b] >= C) {
+      *err = "corrupt blob: class map";
+      return false;
+    }
+  uint32_t bad = 0;
+  for (uint64_t s = 0; s < S; ++s) bad |= (v.out_off[s] > v.out_off[s + 1]) | (v.fail[s] >= S);
+  bad |= v.out_off[S] != O;
+  for (uint64_t j = 0; j < O; ++j) bad |= (static_cast<uint64_t>(static_cast<uint32_t>(v.out_val[j])) >= K);
+  const uint64_t n_delta = S * C;
+  uint32_t worst = 0;
+  for (uint64_t i = 0; i < n_delta; ++i) {
+    const uint32_t t = v.delta[i] & kStateMask;
+    worst = t > worst ? t : worst;
+  }
+  if (bad || worst >= S) {
+    *err = "corrupt blob: an index leaves its section";
     return false;
   }
   return true;

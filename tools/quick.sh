@@ -1,7 +1,15 @@
 #!/bin/bash
-# quick GPU-box check while tuning: parity tests, then the short bench (prints throughput, step ms, walk ms, e2e, launches)
-timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -2
-timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu --e2e-steps 2 2>&1 | tail -1 | python -c "
-import json,sys
-d=json.loads(sys.stdin.read())
-print('GB/s %.1f  step %.3f ms  walk %.3f ms  e2e %.1f  launches %d  hits %d' % (d['value'], d['ms_per_step'], d['roofline']['dominant_kernel']['ms'], d['e2e']['value'], d['gpu_launches'], d['config']['hits_per_gpu_step']))"
+# quick GPU-box check while tuning: parity tests, then the bench line (saved under gpurun_out/)
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -15
+timeout 600 python bench.py --steps 20 --warmup 3 > gpurun_out/bench_c2.json 2> gpurun_out/bench_c2.err
+tail -3 gpurun_out/bench_c2.err
+python - <<'PY'
+import json
+d=json.loads(open('gpurun_out/bench_c2.json').read().strip().splitlines()[-1])
+r=d['per_rank'][0]
+print('GB/s %.1f  step %.3f ms  frac %.3f  e2e %.1f  launches %d  hits %d' % (d['value'], d['ms_per_step'], d['roofline']['frac'], d['e2e']['value'], d['gpu_launches'], d['config']['hits_per_gpu_step']))
+print('scan', r['scan_ms'], 'walk', r['walk_ms'], 'expand', r['expand_ms'], 'gap', r['host_gap_ms'])
+print('parity', d['parity'])
+print('cpu', d['cpu_baseline'])
+PY

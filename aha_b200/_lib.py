@@ -8,7 +8,8 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "libaha_b200.so")
+# AHA_B200_SO: load another build of the library (tools/ab.py compares builds with different -D flags on one box)
+SO_PATH = os.environ.get("AHA_B200_SO") or os.path.join(_HERE, "libaha_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 NVCC_FLAGS = [
@@ -24,8 +25,15 @@ def _sources():
     return out
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, out=None, extra_flags=()):
     """nvcc cross-compiles for sm_100a (no GPU needed).  Rebuilds when any source is newer."""
+    if out is not None:
+        nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+        subprocess.check_call([nvcc] + NVCC_FLAGS + list(extra_flags) + ["-o", out, os.path.join(CSRC, "api.cu")],
+                              stderr=subprocess.DEVNULL)
+        return out
+    if os.environ.get("AHA_B200_SO"):
+        return SO_PATH
     if not force and os.path.exists(SO_PATH):
         t = os.path.getmtime(SO_PATH)
         if all(os.path.getmtime(s) <= t for s in _sources()):
@@ -67,8 +75,7 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(SO_PATH):
-        build()
+    build()  # no-op when the library is newer than every source: a stale binary is never loaded silently
     L = C.CDLL(SO_PATH)
     vp, i32, i64, u32, u64 = C.c_void_p, C.c_int32, C.c_int64, C.c_uint32, C.c_uint64
     P = C.POINTER

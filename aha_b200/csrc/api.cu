@@ -98,7 +98,22 @@ static int32_t build_hot_table(const aha_dfa* d, DeviceDfa* dd) {
   h.off_gfail = place(cursor, T.gfail.size() * 2);
   h.off_ref = place(cursor, T.ref_rec.size() * sizeof(RefRec));
   h.off_mbits = place(cursor, T.multi_bits.size() * 4);
+  // ref_rec in 8 bytes for the expansion's shared-memory table (scan_char_split.cuh)
+  std::vector<uint2> ref8(T.ref_rec.size());
+  bool ref8_ok = true;
+  for (size_t i = 0; i < T.ref_rec.size(); ++i) {
+    const RefRec& r = T.ref_rec[i];
+    if (r.n == 1) {
+      if (r.b >= 0x8000u || r.c >= 0x10000u || r.b == 0) ref8_ok = false;
+      ref8[i] = make_uint2(r.a, (r.b << 16) | r.c);
+    } else {
+      ref8[i] = make_uint2(r.a, r.n ? (0x80000000u | r.n) : 0u);
+    }
+  }
+  h.off_ref8 = place(cursor, ref8.size() * sizeof(uint2));
   std::vector<uint8_t> stage(cursor, 0);
+  memcpy(stage.data() + h.off_ref8, ref8.data(), ref8.size() * sizeof(uint2));
+  h.n_ref8 = ref8_ok ? (uint32_t)ref8.size() : 0u;
   memcpy(stage.data() + h.off_root, T.root.data(), T.root.size() * 4);
   memcpy(stage.data() + h.off_val, T.val.data(), T.val.size() * 4);
   memcpy(stage.data() + h.off_check, T.check.data(), T.check.size() * 2);

@@ -383,6 +383,15 @@ static int32_t run_char_split(ScanParams p, ScanCall& c) {
   AHA_CUDA(ws->get(kWsStatus, 4, &sp.status));
   sp.tile_doc = tile_doc;
   sp.tile_prefix = tile_prefix;
+  sp.mbits_g = reinterpret_cast<const uint32_t*>(h.dev + h.off_mbits);
+  sp.ref8_g = reinterpret_cast<const uint2*>(h.dev + h.off_ref8);
+  sp.n_ref8 = h.n_ref8;
+  // the expansion keeps the 8-byte ref table in shared memory when it fits next to nothing else
+  const size_t ref8_bytes = (size_t)h.n_ref8 * sizeof(uint2);
+#ifndef AHA_EXP_SMEM
+#define AHA_EXP_SMEM 0  // measured on C2: 0.83 ms with the table in shared memory (32 warps per SM) against 0.71 ms from L1 (64 warps)
+#endif
+  const bool smem_refs = AHA_EXP_SMEM && h.n_ref8 > 0 && ref8_bytes <= (size_t)224 * 1024;
   int32_t rc = alloc_doc_hit_off(c, p.n_docs, &p.doc_hit_off);
   if (rc) return rc;
   int64_t cap = 0;
@@ -397,6 +406,8 @@ static int32_t run_char_split(ScanParams p, ScanCall& c) {
   cudaError_t attr_err = cudaSuccess;
   std::call_once(attr_once[c.dd->device & 63], [&] {
     attr_err = cudaFuncSetAttribute(char_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(char_expand_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   });
   AHA_CUDA(attr_err);
 
@@ -422,6 +433,13 @@ static int32_t run_char_split(ScanParams p, ScanCall& c) {
     AHA_CUDA(cudaEventRecord(ws->evw1, st));
     AHA_CUDA(cudaGetLastError());
   }
+#if !AHA_W_COUNT
+  if (nt > 0) {
+    const unsigned grid = (unsigned)std::min<int64_t>((nt + 7) / 8, (int64_t)n_sm * 8);
+    char_count_kernel<<<grid, 256, (size_t)h.n_mwords * 4, st>>>(sp);
+    count_launch();
+  }
+#endif
   {
     cub::TransformInputIterator<uint64_t, TileHitsToU64, const uint32_t*> it(sp.tile_hits, TileHitsToU64());
     rc = exclusive_sum_u64(ws, it, tile_prefix, nt + 1, st);
@@ -431,7 +449,8 @@ static int32_t run_char_split(ScanParams p, ScanCall& c) {
     if (nt > 0) {
       const unsigned grid = (unsigned)std::min<int64_t>((nt + 7) / 8, (int64_t)n_sm * 64);
       if (timed) AHA_CUDA(cudaEventRecord(ws->evx0, st));
-      char_expand_kernel<<<grid, 256, 0, st>>>(sp);
+      if (smem_refs) char_expand_kernel<true><<<(unsigned)std::min<int64_t>((nt + 31) / 32, n_sm), 1024, ref8_bytes, st>>>(sp);
+      else char_expand_kernel<false><<<grid, 256, 0, st>>>(sp);
       count_launch();
       if (timed) AHA_CUDA(cudaEventRecord(ws->evx1, st));
       // tiles the walk handed over (normally none: the kernel reads the list length on the device and leaves)

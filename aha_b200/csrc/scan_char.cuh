@@ -21,6 +21,18 @@ namespace aha {
 
 constexpr uint32_t kEvMark = 0x80000000u;  // marker event: low 31 bits = document index
 
+// build-time variants of the walk (tools/ab.py compares them on one box)
+#ifndef AHA_W_FAST
+#define AHA_W_FAST 0     // 12-byte steps that lie wholly inside every sub-chunk's owned region skip the range and slot-bound tests
+#endif
+#ifndef AHA_W_COUNT
+#define AHA_W_COUNT 0    // hits counted inside the walk from a 2-bit table in shared memory (measured on C2: walk 2.45 ms against
+                         // 2.05 ms without: one more shared-memory lookup per character; char_count_kernel does it instead)
+#endif
+#ifndef AHA_W_FMA
+#define AHA_W_FMA 0      // table addresses as multiply-adds (multiply pipe) instead of three-input adds / LEA (integer pipe)
+#endif
+
 struct CharDeviceTables {
   const uint32_t* root_g;   // global copies, loaded into shared memory at kernel start
   const uint16_t* check_g;
@@ -85,13 +97,22 @@ __device__ __forceinline__ T* pin_ptr(T* p) {
   asm volatile("" : "+l"(p));
   return p;
 }
+__device__ __forceinline__ uint32_t mad_addr(uint32_t i, uint32_t scale, uint32_t base) {
+#if AHA_W_FMA
+  uint32_t a;
+  asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(a) : "r"(i), "r"(scale), "r"(base));
+  return a;
+#else
+  return base + i * scale;
+#endif
+}
 struct SmemU32 {
   uint32_t base;
-  __device__ __forceinline__ uint32_t operator[](uint32_t i) const { return lds_u32(base + i * 4u); }
+  __device__ __forceinline__ uint32_t operator[](uint32_t i) const { return lds_u32(mad_addr(i, 4u, base)); }
 };
 struct SmemU16 {
   uint32_t base;
-  __device__ __forceinline__ uint32_t operator[](uint32_t i) const { return lds_u16(base + i * 2u); }
+  __device__ __forceinline__ uint32_t operator[](uint32_t i) const { return lds_u16(mad_addr(i, 2u, base)); }
 };
 struct CharSmem {
   SmemU32 root;            // [n_root]
@@ -195,10 +216,14 @@ template <bool kChars, int kStride, class OnDoc>
 __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanParams& p, const uint8_t* sbuf, int64_t origin, int64_t a,
                                                int64_t b, int32_t sub, int32_t stage_end, int32_t warmc, bool one_doc, int64_t cd,
                                                int64_t cdoc_start, int64_t cdoc_end, int32_t rel_base, const uint32_t (&rel0)[kChains],
-                                               uint32_t* my_ev, uint32_t (&n_ev)[kChains], OnDoc on_doc) {
+                                               uint32_t* my_ev, uint32_t (&n_ev)[kChains], uint32_t& n_hit, bool& lookup, OnDoc on_doc) {
   constexpr unsigned kFull = 0xffffffffu;
   const uint32_t sbuf_s = pin_u32((uint32_t)__cvta_generic_to_shared(sbuf));
   bool ok = true;
+#if defined(AHA_PERTURB_LDS) || defined(AHA_PERTURB_ALU) || defined(AHA_PERTURB_FMA)
+  uint32_t junk = 0;
+  struct JunkSink { uint32_t& j; uint32_t* out; __device__ ~JunkSink() { if (j == 0x12345679u) out[0] = j; } } junk_sink{junk, my_ev};
+#endif
   // per sub-chunk state (all offsets relative to sbuf)
   int32_t rb[kChains], a_seg[kChains], pos[kChains], de[kChains], seg_end[kChains];
   uint32_t s[kChains], f1[kChains], k[kChains];
@@ -256,14 +281,23 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
     if (fire) {  // n_ev[c] counts in steps of 64 = the slot-major element stride (see multi_step)
       if (n_ev[c] < (uint32_t)kStride * 64u) my_ev[n_ev[c] + c] = (kChars ? k[c] : (uint32_t)(last + rel_base)) * 65536u + ref;
       n_ev[c] += 64u;
+#if AHA_W_COUNT
+      const uint32_t cnt = (S.mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
+      n_hit += cnt;
+      lookup = lookup || cnt == 0u;
+#endif
     }
   };
 
   // one character of EVERY sub-chunk (warp converged): probes first, then the rare continuation behind a single
-  // vote, then the state update, then the events behind a single branch
-  // rl[c] = offset of the character's last byte relative to a_seg[c], span[c] = rb[c] - a_seg[c] (hoisted by the caller)
-  auto multi_step = [&](const uint32_t (&vr)[kChains], const uint32_t (&ci)[kChains], const int32_t (&cs)[kChains], int32_t len,
+  // vote, then the state update, then the events (predicated, no branch).
+  // evw[c] = the event word of this character without its ref (byte units: rel << 16); rl[c] = offset of the
+  // character's last byte relative to a_seg[c], span[c] = rb[c] - a_seg[c] (hoisted by the caller).
+  // fast: the caller has established that every sub-chunk of the warp owns this character and has slots left, so
+  // the range test and the slot-bound test are not made.
+  auto multi_step = [&](auto fast, const uint32_t (&vr)[kChains], const uint32_t (&ci)[kChains], const uint32_t (&evw)[kChains], int32_t len,
                         const int32_t (&rl)[kChains], const uint32_t (&span)[kChains]) {
+    constexpr bool kFast = decltype(fast)::value;
     ProbeResult q[kChains];
     bool any_rare = false;
 #pragma unroll
@@ -271,6 +305,9 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
       q[c] = char_probe(S, vr[c], ci[c], s[c], f1[c], deep[c]);
       any_rare = any_rare || q[c].rare;
     }
+#ifdef AHA_PROBE_NORARE  // timing probe only (wrong results): never follow the gfail chain
+    any_rare = false;
+#endif
     if (__any_sync(kFull, any_rare)) {
 #pragma unroll
       for (int c = 0; c < kChains; ++c)
@@ -286,19 +323,25 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
       s[c] = v & 0x7FFFu;
       f1[c] = (v >> 16) & 0x7FFFu;
       deep[c] = (v >> 31) != 0u;
-      if (kChars) k[c] += (rl[c] >= len - 1) ? 1u : 0u;
+      if (kChars) k[c] += kFast ? 1u : ((rl[c] >= len - 1) ? 1u : 0u);
       // the fires bit as a sign test of v << 16: the shift can run on the multiply pipe, the test folds into the range compare
       int32_t vs;
       asm("shl.b32 %0, %1, 16;" : "=r"(vs) : "r"(v));
-      fire[c] = (uint32_t)rl[c] < span[c] && vs < 0;
+      fire[c] = kFast ? (vs < 0) : ((uint32_t)rl[c] < span[c] && vs < 0);
     }
     // branch-free: a handful of predicated instructions per sub-chunk cost less than the divergent branches around them
 #pragma unroll
     for (int c = 0; c < kChains; ++c) {
       // n_ev[c] is kept pre-multiplied by the slot-major element stride: the address is one multiply-add away
-      if (fire[c] && n_ev[c] < (uint32_t)kStride * 64u)
-        my_ev[n_ev[c] + c] = (kChars ? k[c] : (uint32_t)(cs[c] + len - 1 + rel_base)) * 65536u + q[c].slotv;
+      if (fire[c] && (kFast || n_ev[c] < (uint32_t)kStride * 64u)) my_ev[n_ev[c] + c] = (kChars ? k[c] * 65536u : evw[c]) + q[c].slotv;
       if (fire[c]) n_ev[c] += 64u;
+#if AHA_W_COUNT
+      // hits of the event from the 2-bit table (0: more than three keys fire there, the caller looks it up)
+      const uint32_t ref = q[c].slotv;
+      const uint32_t cnt = fire[c] ? (S.mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u : 4u;
+      n_hit += cnt & 3u;
+      lookup = lookup || cnt == 0u;
+#endif
     }
   };
 
@@ -342,27 +385,43 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
       };
       // twelve bytes = three words: character u sits at a fixed place in A:B:C, one funnel shift each
       int32_t rl0[kChains];
-      uint32_t span[kChains];
+      uint32_t span[kChains], pe[kChains];
+      bool plain = AHA_W_FAST != 0;  // every sub-chunk of the lane owns all four characters and has four slots left
 #pragma unroll
       for (int c = 0; c < kChains; ++c) {
         rl0[c] = pos[c] + 2 - a_seg[c];
         span[c] = (uint32_t)(rb[c] - a_seg[c]);
+        pe[c] = (uint32_t)(pos[c] + rel_base + 2) << 16;  // event word of the first character, ref still to be added
+        plain = plain && !done[c] && pos[c] >= a_seg[c] && pos[c] + 12 <= rb[c] && n_ev[c] <= (uint32_t)(kStride - 4) * 64u;
       }
+      auto four = [&](auto fast) {
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        uint32_t vr[kChains], ci[kChains];
-        int32_t cs[kChains], rl[kChains];
+        for (int u = 0; u < 4; ++u) {
+          uint32_t vr[kChains], ci[kChains], evw[kChains];
+          int32_t rl[kChains];
 #pragma unroll
-        for (int c = 0; c < kChains; ++c) {
-          const uint32_t w = u == 0 ? A[c] : (u == 1 ? __funnelshift_r(A[c], B[c], 24) : (u == 2 ? __funnelshift_r(B[c], C[c], 16) : C[c] >> 8));
-          const uint32_t ra = root3(w);
-          vr[c] = lds_u16(ra);      // the two halves of the entry as two loads: the load pipe has room, the integer pipe has not
-          ci[c] = lds_u16(ra + 2);
-          cs[c] = pos[c] + 3 * u;
-          rl[c] = rl0[c] + 3 * u;
+          for (int c = 0; c < kChains; ++c) {
+            const uint32_t w = u == 0 ? A[c] : (u == 1 ? __funnelshift_r(A[c], B[c], 24) : (u == 2 ? __funnelshift_r(B[c], C[c], 16) : C[c] >> 8));
+            const uint32_t ra = root3(w);
+            vr[c] = lds_u16(ra);      // the two halves of the entry as two loads: the load pipe has room, the integer pipe has not
+            ci[c] = lds_u16(ra + 2);
+#ifdef AHA_PERTURB_LDS   // sensitivity probe (not a product build): one more shared-memory load per character
+            junk += lds_u16(ra ^ 4u);
+#endif
+#ifdef AHA_PERTURB_ALU   // ... two more integer-pipe instructions per character
+            junk = (junk ^ w) & (vr[c] | 0x55u);
+#endif
+#ifdef AHA_PERTURB_FMA   // ... two more multiply-pipe instructions per character
+            junk = junk * 3u + w; junk = junk * 5u + vr[c];
+#endif
+            evw[c] = pe[c] + ((uint32_t)(3 * u) << 16);
+            rl[c] = rl0[c] + 3 * u;
+          }
+          multi_step(fast, vr, ci, evw, 3, rl, span);
         }
-        multi_step(vr, ci, cs, 3, rl, span);
-      }
+      };
+      if (AHA_W_FAST && __all_sync(kFull, plain)) four(std::true_type());
+      else four(std::false_type());
 #pragma unroll
       for (int c = 0; c < kChains; ++c)
         if (!done[c]) pos[c] += 12;
@@ -377,13 +436,13 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
       for (int c = 0; c < kChains; ++c) span[c] = (uint32_t)(rb[c] - a_seg[c]);
 #pragma unroll 1
       for (int i = 0; i < 12; ++i) {
-        uint32_t r[kChains];
-        int32_t cs[kChains], rl[kChains];
+        uint32_t r[kChains], evw[kChains];
+        int32_t rl[kChains];
 #pragma unroll
         for (int c = 0; c < kChains; ++c) {
           r[c] = S.root[A[c] & 0xFFu];
-          cs[c] = pos[c] + i;
-          rl[c] = cs[c] - a_seg[c];
+          rl[c] = pos[c] + i - a_seg[c];
+          evw[c] = (uint32_t)(pos[c] + i + rel_base) << 16;
           A[c] = __funnelshift_r(A[c], B[c], 8);
           B[c] = __funnelshift_r(B[c], C[c], 8);
           C[c] >>= 8;
@@ -394,7 +453,7 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
           vr[c] = r[c] & 0xFFFFu;
           ci[c] = r[c] >> 16;
         }
-        multi_step(vr, ci, cs, 1, rl, span);
+        multi_step(std::false_type(), vr, ci, evw, 1, rl, span);
       }
 #pragma unroll
       for (int c = 0; c < kChains; ++c)

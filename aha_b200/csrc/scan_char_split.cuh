@@ -4,9 +4,13 @@
 //   0. tile_doc_kernel     which document every tile starts in (one binary search per tile, off the walkers' path).
 //   1. char_walk_kernel    persistent walkers (tables in shared memory, TMA-staged text, two interleaved sub-chunks per
 //                          lane).  A tile's events go to its own slice of a global event store (4 bytes per event), its
-//                          per-sub-chunk event counts to tile_meta[], its hit total to tile_hits[].  Nothing is ordered,
-//                          nobody waits for anybody.
-//   2. cub exclusive scan  over tile_hits[] -> tile_prefix[] (global position of every tile's first hit).
+//                          per-sub-chunk event counts to tile_meta[].  The walk reads nothing back from global memory:
+//                          nothing is counted, nothing is ordered, nobody waits for anybody.
+//   2. char_count_kernel   one warp per tile at full occupancy: hits of the tile's events (2-bit table, L1-resident)
+//                          -> tile_hits[]; cub exclusive sum -> tile_prefix[] (position of every tile's first hit).
+//                          (A decoupled look-back inside the expansion was measured instead of these two launches: with
+//                          half a million small tiles and ten thousand warps in flight the look-back chains were three
+//                          orders of magnitude slower than the scan.)
 //   3. char_expand_kernel  one warp per tile at FULL occupancy: events -> ref_rec[] -> Aha::Hit records at their final
 //                          position.  The L2 round trips that would stall a 16-warp walker CTA are hidden by thousands
 //                          of warps.  Writes beyond the hit buffer's capacity are dropped; the total is read by the host
@@ -22,6 +26,9 @@
 
 namespace aha {
 
+#ifndef AHA_W_PREFETCH
+#define AHA_W_PREFETCH 0
+#endif
 constexpr int kStoreSlotsC = 16;                      // event slots per sub-chunk in the store (more: direct pass)
 constexpr int kStoreSlots = kStoreSlotsC * kChains;   // per lane
 constexpr uint32_t kTileDirect = 0x80000000u;         // tile_hits[] flag: the tile is delivered by char_direct_kernel
@@ -40,10 +47,18 @@ struct SplitParams {
   const TileDoc* tile_doc;   // [n_tiles]
   uint32_t* store;           // [n_tiles][kStoreSlotsC][32 lanes][kChains]: slot-major, event i of every sub-chunk side by side
   uint32_t* tile_meta;       // [n_tiles][32]  events of sub-chunk 0 | events of sub-chunk 1 << 16; direct tiles: hits of the lane
-  uint32_t* tile_hits;       // [n_tiles + 1] hits of the tile | kTileDirect
-  const uint64_t* tile_prefix;  // [n_tiles + 1] exclusive prefix of the hits (kernels 3 and 4)
+  uint32_t* tile_hits;       // [n_tiles + 1] hits of the tile (char_count_kernel), | kTileDirect for a tile the walk counted itself
+  const uint64_t* tile_prefix;  // [n_tiles + 1] exclusive prefix of the hits
+  const uint32_t* mbits_g;   // 2 bits per ref: hits it expands to when 1..3, 0 = see ref_rec[ref].n
+  const uint2* ref8_g;       // [n_ref8] ref_rec in 8 bytes (RefRec8): the expansion keeps it in shared memory when it fits
+  uint32_t n_ref8;
   uint32_t* direct_list;     // [n_tiles] tiles for char_direct_kernel
   ScanStatus* status;        // total_hits, n_direct (= length of direct_list), bad_docs
+};
+
+// tile_hits[] as the scan's input: the direct flag stripped, widened to 64 bits
+struct TileHitsToU64 {
+  __host__ __device__ __forceinline__ uint64_t operator()(const uint32_t& x) const { return (uint64_t)(x & ~kTileDirect); }
 };
 
 __global__ void tile_doc_kernel(const int64_t* doc_off, int64_t n_docs, int64_t tile, int64_t n_tiles, TileDoc* out) {
@@ -54,11 +69,6 @@ __global__ void tile_doc_kernel(const int64_t* doc_off, int64_t n_docs, int64_t 
   out[t] = TileDoc{ds, (int32_t)(doc_off[d + 1] - ds), (int32_t)d};
 }
 
-// tile_hits[] as the scan's input: the direct flag stripped, widened to 64 bits
-struct TileHitsToU64 {
-  __host__ __device__ __forceinline__ uint64_t operator()(const uint32_t& x) const { return (uint64_t)(x & ~kTileDirect); }
-};
-
 // ---- 1. walk ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __grid_constant__ SplitParams Q) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -68,15 +78,16 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint32_t* s_root = reinterpret_cast<uint32_t*>(smem);
   uint32_t* s_val = s_root + P.t.n_root;
+  const uint32_t n_mw = AHA_W_COUNT ? P.t.n_mwords : 0u;
   uint32_t* s_mbits = s_val + P.t.m;
-  uint16_t* s_check = reinterpret_cast<uint16_t*>(s_mbits + P.t.n_mwords);
+  uint16_t* s_check = reinterpret_cast<uint16_t*>(s_mbits + n_mw);
   uint8_t* s_cmap = reinterpret_cast<uint8_t*>(s_check + P.t.m_pad);
-  for (uint32_t i = threadIdx.x; i < P.t.n_mwords; i += blockDim.x) s_mbits[i] = P.t.mbits_g[i];
+  for (uint32_t i = threadIdx.x; i < n_mw; i += blockDim.x) s_mbits[i] = P.t.mbits_g[i];
   for (uint32_t i = threadIdx.x; i < P.t.n_root; i += blockDim.x) s_root[i] = P.t.root_g[i];
   for (uint32_t i = threadIdx.x; i < P.t.m; i += blockDim.x) s_val[i] = P.t.val_g[i];
   for (uint32_t i = threadIdx.x; i < P.t.m_pad; i += blockDim.x) s_check[i] = P.t.check_g[i];
   for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) s_cmap[i] = P.cmap_g[i];
-  const uint32_t table_bytes = P.t.n_root * 4 + P.t.m * 4 + P.t.n_mwords * 4 + P.t.m_pad * 2 + 256;
+  const uint32_t table_bytes = P.t.n_root * 4 + P.t.m * 4 + n_mw * 4 + P.t.m_pad * 2 + 256;
   uint8_t* wbase = smem + ((table_bytes + 127) & ~127u) + (size_t)warp * (size_t)(F.buf_bytes + 128);
   uint64_t* bar = reinterpret_cast<uint64_t*>(wbase);
   uint8_t* sbuf = wbase + 128;
@@ -104,6 +115,18 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
   // Tiles are dealt round-robin (tile t -> warp t mod W): every tile costs about the same, nothing orders them, and
   // a warp knows its next tile early enough to have that tile's document record in registers before it needs it.
   const int64_t W = (int64_t)gridDim.x * kFusedWarps;
+  // the tile after the next one is pulled into L2 while this one is walked, so that the bulk copy that stages it
+  // finds it there
+  auto prefetch_tile = [&](int64_t nt) {
+#if AHA_W_PREFETCH
+    if (nt < F.n_tiles && lane == 0) {
+      const int64_t tile_start = nt * F.tile;
+      const int64_t org = max((int64_t)0, tile_start - (int64_t)F.w16);
+      const int64_t end = min(p.total, tile_start + (int64_t)F.tile + 16) & ~(int64_t)15;
+      if (end > org) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.text + org), "r"((uint32_t)(end - org)) : "memory");
+    }
+#endif
+  };
   auto stage_tile = [&](int64_t nt) {
     if (nt < F.n_tiles) {
       const int64_t tile_start = nt * F.tile;
@@ -131,6 +154,7 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
     const int64_t bulk_end = origin + ((want_end - origin) & ~(int64_t)15);
     const int64_t cd = td_next.doc, cdoc_start = td_next.doc_start, cdoc_end = td_next.doc_start + td_next.doc_len;
     if (t + W < F.n_tiles) td_next = Q.tile_doc[t + W];  // used a whole tile later
+    prefetch_tile(t + W);
     const bool one_doc = cdoc_start <= tile_start && cdoc_end >= tile_end;
     if (bulk_end > origin) {
       mbar_wait(bar, parity);
@@ -158,6 +182,8 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
 
     uint32_t* my_ev = pin_ptr(Q.store + (size_t)t * 32 * kStoreSlots + lane * kChains);
     uint32_t n_ev[kChains] = {0, 0};
+    uint32_t n_hits = 0;
+    bool lookup = false;
     auto on_doc = [&](int c, int64_t d, uint32_t nev) {  // marker event in the stream of sub-chunk c
       if (nev < (uint32_t)kStoreSlotsC * 64u) my_ev[nev + c] = kEvMark | (uint32_t)d;  // nev in steps of 64
       n_ev[c] += 64u;
@@ -165,14 +191,13 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
     const int32_t stage_end = (int32_t)(want_end - origin);
     const int32_t rel_base = 1 - (int32_t)(tile_start - origin);
     const bool ok = chars ? char_tile_walk<true, kStoreSlotsC>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start,
-                                                                cdoc_end, rel_base, rel0, my_ev, n_ev, on_doc)
+                                                                cdoc_end, rel_base, rel0, my_ev, n_ev, n_hits, lookup, on_doc)
                           : char_tile_walk<false, kStoreSlotsC>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start,
-                                                                 cdoc_end, rel_base, rel0, my_ev, n_ev, on_doc);
+                                                                 cdoc_end, rel_base, rel0, my_ev, n_ev, n_hits, lookup, on_doc);
     n_ev[0] >>= 6;
     n_ev[1] >>= 6;
     const bool bad = __any_sync(0xffffffffu, !ok);
     const bool over = __any_sync(0xffffffffu, n_ev[0] > (uint32_t)kStoreSlotsC || n_ev[1] > (uint32_t)kStoreSlotsC);
-    uint32_t n_hits = 0;
     if (bad || over) {
       // the expansion cannot use this tile's events: count with the byte automaton, deliver in char_direct_kernel
       if (chars && a < b) {
@@ -187,46 +212,18 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
     __syncwarp();
     fence_proxy_async();  // reads of sbuf are done before the bulk copy overwrites it
     stage_tile(t + W);
-    if (!(bad || over)) {
-      // hits per lane: the walk only stored events; the lane reads its own back (both sub-chunks of a slot share
-      // 8 bytes) and looks the hit counts up in the 2-bit table -- a few batched loads per tile instead of a table
-      // lookup inside the walk at every event
-      bool lookup = false;
-      const uint32_t mx = max(n_ev[0], n_ev[1]);
-      for (uint32_t i0 = 0; i0 < mx; i0 += 4) {
-        uint2 e[4];
+    if (AHA_W_COUNT && !(bad || over) && __any_sync(0xffffffffu, lookup)) {
+      // some output list is longer than the 2-bit table can say (rare): this lane's events once more, through ref_rec
+      n_hits = 0;
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if (i0 + j < mx) e[j] = *reinterpret_cast<const uint2*>(my_ev + (size_t)(i0 + j) * 64);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          if (i0 + j < n_ev[0] && !(e[j].x & kEvMark)) {
-            const uint32_t ref = e[j].x & 0xFFFFu;
-            const uint32_t cnt = (S.mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
-            n_hits += cnt;
-            lookup = lookup || cnt == 0u;
-          }
-          if (i0 + j < n_ev[1] && !(e[j].y & kEvMark)) {
-            const uint32_t ref = e[j].y & 0xFFFFu;
-            const uint32_t cnt = (S.mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
-            n_hits += cnt;
-            lookup = lookup || cnt == 0u;
-          }
+      for (int c = 0; c < kChains; ++c)
+        for (uint32_t i = 0; i < n_ev[c]; ++i) {
+          const uint32_t e = my_ev[i * 64 + c];
+          if (!(e & kEvMark)) n_hits += P.t.ref_rec[e & 0xFFFFu].n;
         }
-      }
-      if (lookup) {  // some output list is longer than the 2-bit table can say
-        n_hits = 0;
-#pragma unroll
-        for (int c = 0; c < kChains; ++c) {
-          for (uint32_t i = 0; i < n_ev[c]; ++i) {
-            const uint32_t e = my_ev[i * 64 + c];
-            if (!(e & kEvMark)) n_hits += P.t.ref_rec[e & 0xFFFFu].n;
-          }
-        }
-      }
     }
     Q.tile_meta[(size_t)t * 32 + lane] = (bad || over) ? n_hits : (n_ev[0] | (n_ev[1] << 16));
-    uint32_t T = n_hits;
+    uint32_t T = n_hits;  // (without AHA_W_COUNT: zero unless the tile goes to the direct pass; char_count_kernel counts)
     for (int o = 16; o > 0; o >>= 1) T += __shfl_xor_sync(0xffffffffu, T, o);
     if (lane == 0) {
       Q.tile_hits[t] = T | ((bad || over) ? kTileDirect : 0u);
@@ -236,56 +233,139 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
   }
 }
 
-// ---- 3. expansion: one warp per tile ---------------------------------------------------------------------------
+// ---- 2. / 3. count and expansion: one warp per tile ---------------------------------------------------------------
 // An event's end offset = its tile-relative `rel` + the tile's base - the base of the document it lies in (bytes:
 // tile start / document start; characters: unit starts in front of the tile / in front of the document).  The
 // document of an event is the one of the last marker in front of it in the tile's stream, else the tile's first.
-__global__ void __launch_bounds__(256) char_expand_kernel(const __grid_constant__ SplitParams Q) {
-  const CharParams& P = Q.c;
-  const ScanParams& p = P.f.sp;
-  const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
-  const int lane = threadIdx.x & 31;
-  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  for (int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < P.f.n_tiles; t += n_warps) {
-    if (Q.tile_hits[t] & kTileDirect) continue;
+__device__ __forceinline__ uint32_t event_hits(const SplitParams& Q, uint32_t ref) {
+  const uint32_t n = (__ldg(Q.mbits_g + (ref >> 4)) >> ((ref & 15u) * 2u)) & 3u;
+  return n ? n : Q.c.t.ref_rec[ref].n;
+}
+
+// the tile's events in stream order (lane, sub-chunk, sequence), 32 per round: which slot of the store holds event i
+struct TileEvents {
+  const uint32_t* tile_ev;
+  uint32_t n_ev0, ev_excl, E;
+  __device__ __forceinline__ void init(const SplitParams& Q, int64_t t, int lane) {
     const uint32_t meta = Q.tile_meta[(size_t)t * 32 + lane];
-    const uint32_t n_ev0 = meta & 0xFFFFu, n_ev1 = meta >> 16;
-    const uint32_t n_ev = n_ev0 + n_ev1;
+    n_ev0 = meta & 0xFFFFu;
+    const uint32_t n_ev = n_ev0 + (meta >> 16);
     uint32_t ev_incl = n_ev;
     for (int o = 1; o < 32; o <<= 1) {
       uint32_t v = __shfl_up_sync(0xffffffffu, ev_incl, o);
       if (lane >= o) ev_incl += v;
     }
-    const uint32_t ev_excl = ev_incl - n_ev;
-    const uint32_t E = __shfl_sync(0xffffffffu, ev_incl, 31);
-    if (E == 0) continue;
+    ev_excl = ev_incl - n_ev;
+    E = __shfl_sync(0xffffffffu, ev_incl, 31);
+    tile_ev = Q.store + (size_t)t * 32 * kStoreSlots;
+  }
+  // event i (all lanes call it together); a lane beyond the end gets a marker-like word: no hits, nothing to expand
+  __device__ __forceinline__ uint32_t fetch(uint32_t i) const {
+    uint32_t lo = 0;
+#pragma unroll
+    for (int step = 16; step > 0; step >>= 1) {
+      const uint32_t cand = lo + step;
+      const uint32_t ex = __shfl_sync(0xffffffffu, ev_excl, cand & 31);
+      if (cand < 32 && ex <= i) lo = cand;
+    }
+    const uint32_t ex = __shfl_sync(0xffffffffu, ev_excl, lo);
+    const uint32_t n0 = __shfl_sync(0xffffffffu, n_ev0, lo);
+    if (i >= E) return kEvMark;
+    const uint32_t idx = i - ex;
+    return idx < n0 ? tile_ev[idx * 64 + lo * kChains] : tile_ev[(idx - n0) * 64 + lo * kChains + 1];
+  }
+};
+
+// Counting needs no order: every lane adds up the events of its own two sub-chunks (slot k of both is one aligned
+// 8-byte word, and the 32 lanes' words are one 256-byte row of the store), with the 2-bit table in shared memory.
+// The rows of a tile are independent loads: eight are issued before the first is looked at.
+__global__ void __launch_bounds__(256) char_count_kernel(const __grid_constant__ SplitParams Q) {
+  extern __shared__ uint32_t s_mbits[];
+  const uint32_t n_mwords = Q.c.t.n_mwords;
+  for (uint32_t i = threadIdx.x; i < n_mwords; i += blockDim.x) s_mbits[i] = Q.mbits_g[i];
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  auto hits_of = [&](uint32_t ev) -> uint32_t {
+    if (ev & kEvMark) return 0u;
+    const uint32_t ref = ev & 0xFFFFu;
+    const uint32_t n = (s_mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
+    return n ? n : Q.c.t.ref_rec[ref].n;
+  };
+  int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  uint32_t meta = t < Q.c.f.n_tiles ? Q.tile_meta[(size_t)t * 32 + lane] : 0u;
+  uint32_t th = t < Q.c.f.n_tiles ? Q.tile_hits[t] : 0u;
+  for (; t < Q.c.f.n_tiles; t += n_warps) {
+    const uint32_t n0 = meta & 0xFFFFu, n1 = meta >> 16;
+    const bool direct = (th & kTileDirect) != 0;  // counted by the walk with the byte automaton
+    const int64_t tn = t + n_warps;  // the next tile's counts are on their way while this one's rows are read
+    if (tn < Q.c.f.n_tiles) {
+      meta = Q.tile_meta[(size_t)tn * 32 + lane];
+      th = Q.tile_hits[tn];
+    }
+    if (direct) continue;
+    const uint2* mine = reinterpret_cast<const uint2*>(Q.store + (size_t)t * 32 * kStoreSlots) + lane;
+    uint32_t part = 0;
+    const uint32_t mx = max(n0, n1);
+    for (uint32_t k0 = 0; k0 < mx; k0 += 8) {
+      uint2 e[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (k0 + j < mx) e[j] = mine[(size_t)(k0 + j) * 32];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (k0 + j < n0) part += hits_of(e[j].x);
+        if (k0 + j < n1) part += hits_of(e[j].y);
+      }
+    }
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+    if (lane == 0) Q.tile_hits[t] = part;
+  }
+}
+
+// ref_rec[] in 8 bytes: x = key id, y = key length << 16 | characters after the first   (one key fires: y != 0, bit 31 clear)
+//                       x = first index into out_val, y = 0x80000000 | n                (n >= 2 keys fire)
+// One warp per tile.  kSmemRefs: the 8-byte table sits in shared memory (one CTA of 32 warps per SM, tiles dealt
+// round-robin): the per-event lookup is a shared-memory gather of a few wavefronts instead of 32 L1 tag lookups,
+// which were 60 % of this kernel's load/store traffic.  Otherwise (table too large) ref_rec[] is read from global memory.
+template <bool kSmemRefs>
+__global__ void __launch_bounds__(kSmemRefs ? 1024 : 256, kSmemRefs ? 1 : 4) char_expand_kernel(const __grid_constant__ SplitParams Q) {
+  extern __shared__ uint2 s_ref[];
+  const CharParams& P = Q.c;
+  const FusedParams& F = P.f;
+  const ScanParams& p = F.sp;
+  if (kSmemRefs) {
+    for (uint32_t i = threadIdx.x; i < Q.n_ref8; i += blockDim.x) s_ref[i] = Q.ref8_g[i];
+    __syncthreads();
+  }
+  const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
+  const int lane = threadIdx.x & 31;
+  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < F.n_tiles; t += n_warps) {
+    if (Q.tile_hits[t] & kTileDirect) continue;
+    TileEvents te;
+    te.init(Q, t, lane);
+    if (te.E == 0) continue;
     const unsigned long long prefix = Q.tile_prefix[t];
-    const uint32_t* tile_ev = Q.store + (size_t)t * 32 * kStoreSlots;
     const TileDoc td = Q.tile_doc[t];
     // bases as 64-bit differences: end = rel + (tile base - document base)
-    const int64_t tile_base = chars ? (int64_t)P.f.tile_lead[t] : t * (int64_t)P.f.tile;
+    const int64_t tile_base = chars ? (int64_t)F.tile_lead[t] : t * (int64_t)F.tile;
     int64_t delta = tile_base - (chars ? (int64_t)p.doc_lead_base[td.doc] : td.doc_start);  // warp-uniform, updated at markers
     uint32_t run = 0;
-    for (uint32_t base = 0; base < E; base += 32) {
-      const uint32_t i = base + lane;
-      uint32_t lo = 0;
-#pragma unroll
-      for (int step = 16; step > 0; step >>= 1) {
-        const uint32_t cand = lo + step;
-        const uint32_t ex = __shfl_sync(0xffffffffu, ev_excl, cand & 31);
-        if (cand < 32 && ex <= i) lo = cand;
-      }
-      const uint32_t ex = __shfl_sync(0xffffffffu, ev_excl, lo);
-      const uint32_t n0 = __shfl_sync(0xffffffffu, n_ev0, lo);
-      uint32_t ev = 0;
-      bool live = i < E;
-      if (live) {
-        const uint32_t idx = i - ex;
-        ev = idx < n0 ? tile_ev[idx * 64 + lo * kChains] : tile_ev[(idx - n0) * 64 + lo * kChains + 1];
-      }
+    for (uint32_t base = 0; base < te.E; base += 32) {
+      const uint32_t ev = te.fetch(base + lane);
+      const bool live = base + lane < te.E;
       const bool mark = live && (ev & kEvMark);
-      RefRec rr = RefRec{0, 0, 0, 0};
-      if (live && !mark) rr = P.t.ref_rec[ev & 0xFFFFu];
+      uint2 r8 = make_uint2(0u, 0u);
+      if (live && !mark) {
+        if (kSmemRefs) {
+          r8 = s_ref[ev & 0xFFFFu];
+        } else {
+          const RefRec rr = P.t.ref_rec[ev & 0xFFFFu];
+          r8 = rr.n == 1 ? make_uint2(rr.a, (rr.b << 16) | rr.c) : make_uint2(rr.a, rr.n ? (0x80000000u | rr.n) : 0u);
+        }
+      }
+      const uint32_t n = (r8.y & 0x80000000u) ? (r8.y & 0x7FFFFFFFu) : (r8.y != 0u ? 1u : 0u);
       int64_t my_delta = delta;
       if (__any_sync(0xffffffffu, mark)) {
         // document of every event of this round: the last marker at or in front of it, else the carried one
@@ -297,14 +377,26 @@ __global__ void __launch_bounds__(256) char_expand_kernel(const __grid_constant_
         if (d_here >= 0) my_delta = tile_base - (chars ? (int64_t)p.doc_lead_base[d_here] : p.doc_off[d_here]);
         delta = __shfl_sync(0xffffffffu, my_delta, 31);
       }
-      uint32_t len_incl = rr.n;
+      uint32_t len_incl = n;
       for (int o = 1; o < 32; o <<= 1) {
         uint32_t v = __shfl_up_sync(0xffffffffu, len_incl, o);
         if (lane >= o) len_incl += v;
       }
-      const int64_t at = (int64_t)prefix + run + (len_incl - rr.n);
-      if (mark) p.doc_hit_off[ev & ~kEvMark] = at;
-      else if (live && p.hits) expand_event(p, rr, (int32_t)((int64_t)((ev >> 16) & 0x7FFFu) + my_delta), chars, p.hits, at, P.f.hit_cap);
+      int64_t at = (int64_t)prefix + run + (len_incl - n);
+      if (mark) {
+        p.doc_hit_off[ev & ~kEvMark] = at;
+      } else if (n != 0 && p.hits) {
+        const int32_t end = (int32_t)((int64_t)((ev >> 16) & 0x7FFFu) + my_delta);
+        if (!(r8.y & 0x80000000u)) {
+          if (at < F.hit_cap)
+            p.hits[at] = chars ? aha_hit{end - 1 - (int32_t)(r8.y & 0xFFFFu), end, (int32_t)r8.x} : aha_hit{end - (int32_t)(r8.y >> 16), end, (int32_t)r8.x};
+        } else {
+          for (uint32_t j = r8.x; j < r8.x + n; ++j, ++at) {
+            const int32_t v = p.out_val[j];
+            if (at < F.hit_cap) p.hits[at] = chars ? aha_hit{end - 1 - (int32_t)p.key_tail[v], end, v} : aha_hit{end - (int32_t)p.key_len[v], end, v};
+          }
+        }
+      }
       run += __shfl_sync(0xffffffffu, len_incl, 31);
     }
   }

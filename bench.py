@@ -394,7 +394,13 @@ def main():
     res = None
 
     # ---- end to end through the C ABI with host buffers (rank-local shard, pinned host text) ----
+    if args.e2e_steps <= 0:
+        args.e2e_steps, e2e_skip = 1, True
+    else:
+        e2e_skip = False
     e2e_bytes = min(total, (1 << 30) // D * D) if not args.bytes else total
+    if e2e_skip:
+        e2e_bytes = D
     e2e_docs = e2e_bytes // D
     host_text = torch.empty(e2e_bytes, dtype=torch.uint8, pin_memory=True)
     host_text.copy_(text[:e2e_bytes])

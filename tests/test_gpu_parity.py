@@ -84,6 +84,15 @@ def test_quirks_q1_q5_q7():
     assert m.scan_batch([b"\xe4a\xe4"], 0, sep=[" "], sep_size=256).n_hits == 0
 
 
+def test_q4_stale_end_flag_vector():
+    """the hand-derived Q4 vector of tests/test_oracle_kat.py (stale END flag on the interior node "bc"), on the GPU"""
+    g = aha_b200.AC.compile(["bba", "bca"])
+    assert as_tuples(g.match_longest(b"bcbba")) == []
+    assert as_tuples(g.match_longest(b"bcbba", True)) == [(2, 5, 0)]
+    assert as_tuples(g.match(b"bcbba")) == [(2, 5, 0)]
+    assert as_tuples(aha_b200.AC.compile(["bca", "bba"]).match_longest(b"bcbba")) == [(2, 5, 1)]
+
+
 def test_errors():
     with pytest.raises(aha_b200.AhaError, match="appear twice"):
         aha_b200.AC.compile(["a", "a"])

@@ -139,6 +139,65 @@ def _rand_keys(rng, n, alphabet, maxlen):
     return keys
 
 
+def test_q4_stale_end_flag_hand_derived():
+    """SURVEY Q4, pinned by reasoning about the Crystal source, not by a second port.
+
+    Keys "bba" (id 0), "bca" (id 1); a = 97, b = 98, c = 99.  Trace of cedar.cr / ac.cr, slot numbers in decimal:
+
+    insert "bba" (cedar.cr:755-778 -> get 224-241 -> follow 244-259):
+      * root 0 has base 0 (value -1): 'b' goes to slot 0 ^ 98 = 98, free, popped (pop_enode 327-357); root.child = 98.
+      * node 98 is fresh (value = value_limit, base = -(MAX + 1) wraps negative): find_place (527-531) sees no block
+        on the Closed / Open rings (block 0 is never on one), so add_block (298-313) creates block 1 (slots 256-511,
+        ehead 256): 'b' lands in 256, node 98 gets base 256 ^ 98 = 354, child 98.
+      * node 256 is fresh: find_place -> ehead of block 1 = 257: 'a' lands in 257, node 256 gets base 257 ^ 97 = 352.
+      * node 257 keeps value_limit >= 0, so get returns 257 itself (line 240); insert sets value = 0 and end!
+        (flags = 0x200, line 773-774).
+    insert "bca":
+      * 'b': slot 98 exists.  'c' from node 98: to = 354 ^ 99 = 257 -- occupied by the child of node 256 -> resolve
+        (585-655) with from_n = 98, base_n = 354, label_n = 99, to_pn = 257, from_p = 256, base_p = 352.
+        consult (428-430): child_num(98) = 1 < child_num(256) = 1 is false, so the OCCUPANT's family moves:
+        children = ['a'], find_place -> ehead of block 1 = 258, base = 258 ^ 97 = 355, node 256 gets base 355.
+        The child is copied to slot 258 (value 0, flags 0x200 copied at line 620, leafs[0] = 258).  Since
+        to_ == to_pn (line 635) slot 257 is taken over for the new child: push_sibling (636), child = 0 (638),
+        value = value_limit (639), check = 98 (640) -- and flags is NOT touched: slot 257, now the interior node
+        "bc", still carries END = 0x200.  (push_enode, the only place that clears flags, 394-396, is the else branch.)
+      * 'a' from node 257: fresh node -> find_place = 259; node 257 gets base 259 ^ 97 = 354, child 97, and
+        child_num= (69-71) keeps the END bit: flags = 0x201.  Node 259 gets value = 1, end!.
+    Result: is_end?(257 = "bc") is true (657-660) although "bc" is no key.
+
+    ACX.compile (ac.cr:71-112): fails[98] = 0; children of 98 in sibling order: 'c' (257) then 'b' (256);
+    fails[257] = 0, fails[256] = 98; node 257 is_end? -> vk = value(257) = -1 (726-734: its base slot 354 is free), so
+    key_lens[-1] = 2 (unchecked write) and output[257].value = -1; fails[259] = 0, fails[258] = 0;
+    output[259].value = 1, output[258].value = 0, key_lens = [3, 3].
+
+    match_longest_("bcbba", false) (ac.cr:118-143): b -> 98; c -> 257, is_end? -> prev = (1, 257); b: child(257, 98)
+    = 354 ^ 98 = 256 whose check is 98 -> miss, prev_i != -1 -> yield (1, 257): fetch_one (249-263) finds
+    output[257].value = -1 and yields nothing; prev_i = -1, nid = 0, `break if nid == 0` drops this 'b' (Q5);
+    b -> 98; a: child(98, 97) = 354 ^ 97 = 259 whose check is 257 -> miss, nid = fails[98] = 0, child(0, 97) misses,
+    break.  End of text with prev_i == -1: NO hit at all -- a textbook longest-match reports "bba" at [2, 5).
+    With intersectable = true nid stays 257 after the empty yield, fails to 0, then b -> 98, b -> 256, a -> 258 (end):
+    [(2, 5, 0)].  Plain match (176-192, 265-278): [(2, 5, 0)] as well (the spurious end state yields an empty list).
+    """
+    keys = ["bba", "bca"]
+    ac = O.AC.compile(keys)
+    nodes, fails, output, kl = ac.arrays()
+    nd = np.asarray(nodes).view(np.uint8).reshape(-1, 12)
+    flags = nd[:, 10].astype(np.int32) | (nd[:, 11].astype(np.int32) << 8)
+    check = nd[:, 4:8].copy().view("<i4").reshape(-1)
+    value = nd[:, 0:4].copy().view("<i4").reshape(-1)
+    assert (int(check[257]), int(flags[257]), int(value[257])) == (98, 0x201, -355)   # "bc": stale END, base 354
+    assert (int(check[258]), int(flags[258]), int(value[258])) == (256, 0x200, 0)     # "bba" after the move
+    assert (int(check[259]), int(flags[259]), int(value[259])) == (257, 0x200, 1)     # "bca"
+    assert int(value[256]) == -356 and int(value[98]) == -355
+    assert [int(fails[i]) for i in (98, 257, 256, 259, 258)] == [0, 0, 98, 0, 0]
+    assert sev(ac.match_longest(b"bcbba", False)) == []
+    assert sev(ac.match_longest(b"bcbba", True)) == [(2, 5, 0)]
+    assert sev(ac.match(b"bcbba")) == [(2, 5, 0)]
+    # the same dictionary without the collision: insertion order "bca", "bba" leaves no stale flag
+    ac2 = O.AC.compile(["bca", "bba"])
+    assert sev(ac2.match_longest(b"bcbba", False)) == [(2, 5, 1)]
+
+
 def _has_stale_end_flag(nodes_u8, keys):
     """Q4: an interior node that carries the END flag (bit 9) although no key ends there."""
     nd = nodes_u8.view(np.dtype([("value", "<i4"), ("check", "<i4"), ("sibling", "u1"), ("child", "u1"), ("flags", "<u2")]))

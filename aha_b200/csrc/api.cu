@@ -92,7 +92,7 @@ static int32_t build_hot_table(const aha_dfa* d, DeviceDfa* dd) {
   HotTable& h = dd->hot;
   auto place = [](size_t& cursor, size_t bytes) { size_t at = cursor; cursor = (cursor + bytes + 255) & ~size_t(255); return at; };
   size_t cursor = 0;
-  h.off_root = place(cursor, T.root.size() * 4);
+  h.off_root = place(cursor, T.root.size() * 2);
   h.off_val = place(cursor, T.val.size() * 4);
   h.off_check = place(cursor, T.check.size() * 2);
   h.off_gfail = place(cursor, T.gfail.size() * 2);
@@ -113,8 +113,9 @@ static int32_t build_hot_table(const aha_dfa* d, DeviceDfa* dd) {
   h.off_ref8 = place(cursor, ref8.size() * sizeof(uint2));
   std::vector<uint8_t> stage(cursor, 0);
   memcpy(stage.data() + h.off_ref8, ref8.data(), ref8.size() * sizeof(uint2));
-  h.n_ref8 = ref8_ok ? (uint32_t)ref8.size() : 0u;
-  memcpy(stage.data() + h.off_root, T.root.data(), T.root.size() * 4);
+  if (!ref8_ok) return AHA_OK;  // a key longer than 32 KB: the byte automaton serves this dictionary (h.ok stays false)
+  h.n_ref8 = (uint32_t)ref8.size();
+  memcpy(stage.data() + h.off_root, T.root.data(), T.root.size() * 2);
   memcpy(stage.data() + h.off_val, T.val.data(), T.val.size() * 4);
   memcpy(stage.data() + h.off_check, T.check.data(), T.check.size() * 2);
   memcpy(stage.data() + h.off_gfail, T.gfail.data(), T.gfail.size() * 2);
@@ -128,6 +129,7 @@ static int32_t build_hot_table(const aha_dfa* d, DeviceDfa* dd) {
   h.m = T.m;
   h.m_pad = (uint32_t)T.check.size();
   h.n_mwords = (uint32_t)T.multi_bits.size();
+  h.n_gfail_s = T.n_gfail_s;
   for (int c = 0; c < 3; ++c) { h.lo[c] = T.lo[c]; h.n[c] = T.n[c]; h.off[c] = T.off[c]; }
   h.smem_bytes = T.smem_bytes();
   return AHA_OK;

@@ -44,11 +44,11 @@ struct DeviceGuard {
 struct HotTable {
   bool ok = false;            // dictionary is whole-UTF-8-unit and fits the shared-memory budget
   uint32_t n_hot = 0;         // character-level states resident in shared memory
-  uint32_t n_root = 0, m = 0, m_pad = 0, n_mwords = 0;
+  uint32_t n_root = 0, m = 0, m_pad = 0, n_mwords = 0, n_gfail_s = 0;
   uint32_t lo[3] = {0, 0, 0}, n[3] = {0, 0, 0}, off[3] = {0, 0, 0};
   uint8_t* dev = nullptr;     // one allocation: root | val | check | gfail | ref_rec | mbits
   size_t off_root = 0, off_val = 0, off_check = 0, off_gfail = 0, off_ref = 0, off_mbits = 0, off_ref8 = 0;
-  uint32_t n_ref8 = 0;        // entries of the 8-byte ref table (0: a key length does not fit it, use ref_rec)
+  uint32_t n_ref8 = 0;        // entries of the 8-byte ref table
   size_t smem_bytes = 0;
 };
 

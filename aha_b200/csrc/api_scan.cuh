@@ -340,7 +340,7 @@ static int32_t run_v1(ScanParams p, ScanCall& c) {
 }
 
 static void fill_char_tables(CharDeviceTables* t, const HotTable& h) {
-  t->root_g = reinterpret_cast<const uint32_t*>(h.dev + h.off_root);
+  t->root_g = reinterpret_cast<const uint16_t*>(h.dev + h.off_root);
   t->val_g = reinterpret_cast<const uint32_t*>(h.dev + h.off_val);
   t->check_g = reinterpret_cast<const uint16_t*>(h.dev + h.off_check);
   t->gfail = reinterpret_cast<const uint16_t*>(h.dev + h.off_gfail);
@@ -349,6 +349,7 @@ static void fill_char_tables(CharDeviceTables* t, const HotTable& h) {
   t->m = h.m;
   t->m_pad = h.m_pad;
   t->n_mwords = h.n_mwords;
+  t->n_gfail_s = h.n_gfail_s;
   t->mbits_g = reinterpret_cast<const uint32_t*>(h.dev + h.off_mbits);
   for (int k = 0; k < 3; ++k) { t->lo[k] = h.lo[k]; t->n[k] = h.n[k]; t->off[k] = h.off[k]; }
 }
@@ -386,12 +387,6 @@ static int32_t run_char_split(ScanParams p, ScanCall& c) {
   sp.mbits_g = reinterpret_cast<const uint32_t*>(h.dev + h.off_mbits);
   sp.ref8_g = reinterpret_cast<const uint2*>(h.dev + h.off_ref8);
   sp.n_ref8 = h.n_ref8;
-  // the expansion keeps the 8-byte ref table in shared memory when it fits next to nothing else
-  const size_t ref8_bytes = (size_t)h.n_ref8 * sizeof(uint2);
-#ifndef AHA_EXP_SMEM
-#define AHA_EXP_SMEM 0  // measured on C2: 0.83 ms with the table in shared memory (32 warps per SM) against 0.71 ms from L1 (64 warps)
-#endif
-  const bool smem_refs = AHA_EXP_SMEM && h.n_ref8 > 0 && ref8_bytes <= (size_t)224 * 1024;
   int32_t rc = alloc_doc_hit_off(c, p.n_docs, &p.doc_hit_off);
   if (rc) return rc;
   int64_t cap = 0;
@@ -406,8 +401,6 @@ static int32_t run_char_split(ScanParams p, ScanCall& c) {
   cudaError_t attr_err = cudaSuccess;
   std::call_once(attr_once[c.dd->device & 63], [&] {
     attr_err = cudaFuncSetAttribute(char_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (attr_err == cudaSuccess)
-      attr_err = cudaFuncSetAttribute(char_expand_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   });
   AHA_CUDA(attr_err);
 
@@ -449,8 +442,7 @@ static int32_t run_char_split(ScanParams p, ScanCall& c) {
     if (nt > 0) {
       const unsigned grid = (unsigned)std::min<int64_t>((nt + 7) / 8, (int64_t)n_sm * 64);
       if (timed) AHA_CUDA(cudaEventRecord(ws->evx0, st));
-      if (smem_refs) char_expand_kernel<true><<<(unsigned)std::min<int64_t>((nt + 31) / 32, n_sm), 1024, ref8_bytes, st>>>(sp);
-      else char_expand_kernel<false><<<grid, 256, 0, st>>>(sp);
+      char_expand_kernel<<<grid, 256, 0, st>>>(sp);
       count_launch();
       if (timed) AHA_CUDA(cudaEventRecord(ws->evx1, st));
       // tiles the walk handed over (normally none: the kernel reads the list length on the device and leaves)

@@ -7,10 +7,14 @@
 // can fire in the middle of a unit.  One transition then consumes 1-4 text bytes.
 //
 // Representation (all in shared memory, 6 bytes per edge slot):
-//   root[idx(char)]      -> id of the one-character state:15 | fires:1 | cid:15 | 0               (direct table)
-//   state id == base     -> edge slot = base + cid ; check[slot] == base means the goto edge exists
+//   root[idx(char)]      -> id of the one-character state:15 | fires:1                          (direct table, u16)
+//   column of a char     =  idx(char), its index into root[]: the walk has it in a register already, no lookup
+//   state id == base     -> edge slot = base + column ; check[slot] == base means the goto edge exists
 //   val[slot]            -> next state id:15 | fires:1 | effective fail of next:15 | deep:1
 //                           deep = the fail link of next has a non-root fail link itself (a third probe may be needed)
+//   gfail[id]            -> effective fail of state id; the states a chain can pass through are packed first, so that
+//                           they get the smallest ids and the part of gfail[] the walk ever reads is a short prefix
+//                           that fits in shared memory too (the rest stays in global memory)
 // States without children are never "current": an edge into one stores the nearest fail-ancestor that
 // has children (its transitions are identical by the closure of the goto/fail loop) but still reports
 // the target's own output list (ref_rec[slot], global memory, read only when hits are written out).
@@ -43,15 +47,17 @@ struct CharTableHost {
   uint32_t lo[3] = {0, 0, 0}, n[3] = {0, 0, 0}, off[3] = {256, 256, 256};  // entries 128..255 stay 0: idle lanes of the ASCII step may index them
   uint32_t n_root = 256;
   uint32_t m = 0;                  // slots
-  std::vector<uint32_t> root;      // [n_root]
-  std::vector<uint16_t> check;     // [m_pad = m + n_cid + 1 rounded up]: unused / padding = 0xFFFF, so base + cid never needs a bound test
+  std::vector<uint16_t> root;      // [n_root]
+  std::vector<uint16_t> check;     // [m_pad = m + n_root + 1 rounded up]: unused / padding = 0xFFFF, so base + column never needs a bound test
   std::vector<uint32_t> val;       // [m]
   std::vector<uint32_t> multi_bits; // 2 bits per ref: ref_rec[ref].n when it is 1..3, 0 = look it up (shared memory: the walk
                                     // counts hits without touching ref_rec)
-  std::vector<RefRec> ref_rec;     // [m + n_cid + 1] what fires at edge slot / at the one-character state of cid (global)
-  std::vector<uint16_t> gfail;     // [m] effective fail of the state whose id is the index (global)
+  std::vector<RefRec> ref_rec;     // [m + n_root] what fires at edge slot / at the one-character state of column c: m + c (global)
+  std::vector<uint16_t> gfail;     // [m] effective fail of the state whose id is the index (global; prefix in shared memory)
+  uint32_t n_gfail_s = 0;          // gfail[0 .. n_gfail_s) covers every state a fail chain can pass through
   uint32_t n_cid = 0, n_edges = 0, n_states = 0;
-  size_t smem_bytes() const { return root.size() * 4 + (size_t)m * 4 + multi_bits.size() * 4 + check.size() * 2 + 256; }
+  // shared memory of the walk: val | root | check | gfail prefix | class map of the fallback walk
+  size_t smem_bytes() const { return (size_t)m * 4 + root.size() * 2 + check.size() * 2 + (size_t)n_gfail_s * 2 + 256 + 16; }
   uint32_t root_index(uint32_t code) const {
     const uint32_t cls = code >> 30;
     return cls ? off[cls - 1] + ((code & 0x3FFFFFFFu) - lo[cls - 1]) : code;
@@ -76,7 +82,7 @@ inline int unit_follow(uint8_t b) {
 }
 
 struct CharEdge { uint32_t from, to, code; };
-struct CharRow { uint32_t st; uint32_t first, count; bool depth1; };
+struct CharRow { uint32_t st; uint32_t first, count; bool depth1; bool chain; };
 
 inline bool parent_is_root_unit(uint32_t st, const std::vector<int8_t>& phase, const std::vector<uint32_t>& parent) {
   uint32_t p = parent[st];
@@ -84,54 +90,56 @@ inline bool parent_is_root_unit(uint32_t st, const std::vector<int8_t>& phase, c
   return p == 0;
 }
 
-// First-fit row displacement: state id = base, edge slot = base + cid.
+// First-fit row displacement: state id = base, edge slot = base + column (column = root index of the character).
 inline CharTableHost pack_rows(CharTableHost T, const DfaView& v, const std::vector<CharEdge>& edges,
-                               const std::vector<CharRow>& rows, const std::map<uint32_t, uint32_t>& cid_of,
-                               const std::vector<uint32_t>& eff, size_t smem_budget) {
+                               const std::vector<CharRow>& rows, const std::vector<uint32_t>& eff, size_t smem_budget) {
   T.ok = false;
-  const size_t root_bytes = (size_t)T.n_root * 4;
-  if (smem_budget < root_bytes + 256 + 64) { T.why = "shared memory budget too small"; return T; }
-  // check[] is padded by n_cid + 1 entries; plus the multi bitmap (1 bit per edge slot and per character)
-  const size_t pad_bytes = ((size_t)T.n_cid + 1 + 16) * 2 + ((size_t)T.n_cid + 64) / 4 + 8;
-  if (smem_budget < root_bytes + 256 + pad_bytes + 64) { T.why = "shared memory budget too small"; return T; }
-  size_t m_max = (smem_budget - root_bytes - 256 - pad_bytes) * 4 / 25;  // 6 bytes + 2 bits per slot
-  if (m_max > 0x7FF0) m_max = 0x7FF0;
-  std::vector<uint8_t> used(m_max + 1, 0), base_used(m_max + 1, 0);
+  const size_t root_bytes = (size_t)T.n_root * 2;
+  // check[] is padded by n_root + 1 entries; 16 KB at most for the gfail prefix (sized below)
+  const size_t pad_bytes = ((size_t)T.n_root + 1 + 16) * 2 + 8;
+  if (smem_budget < root_bytes + 256 + 16 + pad_bytes + 64) { T.why = "shared memory budget too small"; return T; }
+  size_t m_max = (smem_budget - root_bytes - 256 - 16 - pad_bytes) / 6;  // 6 bytes per slot
+  if (m_max + T.n_root > 0xFFF0) m_max = 0xFFF0 - T.n_root;  // an event carries its ref (slot, or m + column) in 16 bits
+  const size_t base_max = 0x7FFF;                             // a state id has 15 bits
+  std::vector<uint8_t> used(m_max + 1, 0), base_used(base_max + 1, 0);
   used[0] = 1;
   std::vector<uint32_t> id_of(v.n_states, 0);
-  std::vector<uint32_t> cids;
-  uint32_t max_slot = 0;
+  std::vector<uint32_t> cols;
+  uint32_t max_slot = 0, max_base = 0, max_chain_base = 0;
   uint32_t first_free = 1;  // lowest free slot
   for (const CharRow& r : rows) {
-    cids.clear();
-    for (uint32_t i = r.first; i < r.first + r.count; ++i) cids.push_back(cid_of.at(edges[i].code));
-    std::sort(cids.begin(), cids.end());
-    const uint32_t c0 = cids[0], c_last = cids.back();
+    cols.clear();
+    for (uint32_t i = r.first; i < r.first + r.count; ++i) cols.push_back(T.root_index(edges[i].code));
+    std::sort(cols.begin(), cols.end());
+    const uint32_t c0 = cols[0], c_last = cols.back();
     while (first_free <= m_max && used[first_free]) ++first_free;
     bool placed = false;
     uint32_t b = 0;
-    for (uint32_t f = std::max(first_free, c0 + 1); f <= m_max; ++f) {  // candidate slot for the smallest cid
+    for (uint32_t f = std::max(first_free, c0 + 1); f <= m_max; ++f) {  // candidate slot for the smallest column
       if (used[f]) continue;
       b = f - c0;
-      if ((size_t)b + c_last > m_max) break;
+      if ((size_t)b + c_last > m_max || b > base_max) break;
       if (base_used[b]) continue;
       bool fit = true;
-      for (size_t i = 1; i < cids.size(); ++i)
-        if (used[b + cids[i]]) { fit = false; break; }
+      for (size_t i = 1; i < cols.size(); ++i)
+        if (used[b + cols[i]]) { fit = false; break; }
       if (fit) { placed = true; break; }
     }
     if (!placed) { T.why = "character automaton does not fit in shared memory"; return T; }
     base_used[b] = 1;
-    for (uint32_t c : cids) used[b + c] = 1;
+    for (uint32_t c : cols) used[b + c] = 1;
     id_of[r.st] = b;
     if (b + c_last > max_slot) max_slot = b + c_last;
+    if (b > max_base) max_base = b;
+    if (r.chain && b > max_chain_base) max_chain_base = b;
   }
   T.m = (max_slot + 1 + 15) & ~15u;
-  T.check.assign(((size_t)T.m + T.n_cid + 1 + 15) & ~size_t(15), 0xFFFFu);
+  T.check.assign(((size_t)max_base + T.n_root + 1 + 15) & ~size_t(15), 0xFFFFu);
+  if (T.check.size() < T.m) T.check.resize(T.m, 0xFFFFu);
   T.val.assign(T.m, 0);
   T.gfail.assign(T.m, 0);
   T.root.assign(T.n_root, 0);
-  T.ref_rec.assign((size_t)T.m + T.n_cid + 1, RefRec{0, 0, 0, 0});
+  T.ref_rec.assign((size_t)T.m + T.n_root, RefRec{0, 0, 0, 0});
   // reference record of a firing state: single output -> {value, key_len, key_tail, 1}; else list bounds
   auto rec_of = [&](uint32_t st) -> RefRec {
     const uint32_t j0 = v.out_off[st], j1 = v.out_off[st + 1];
@@ -142,18 +150,18 @@ inline CharTableHost pack_rows(CharTableHost T, const DfaView& v, const std::vec
     return RefRec{j0, j1, 0, j1 - j0};
   };
   for (const CharEdge& e : edges) {
-    const uint32_t cid = cid_of.at(e.code);
+    const uint32_t col = T.root_index(e.code);
     const uint32_t cont = eff[e.to];  // state we continue in (byte-level id, 0 = root)
     const uint32_t next_id = cont ? id_of[cont] : 0;
     const uint32_t n_out = v.out_off[e.to + 1] - v.out_off[e.to];
     const uint32_t flags = (n_out ? 0x8000u : 0u);
     if (e.from == 0) {
-      T.root[T.root_index(e.code)] = next_id | flags | (cid << 16);
-      if (n_out) T.ref_rec[(size_t)T.m + cid] = rec_of(e.to);
+      T.root[col] = (uint16_t)(next_id | flags);
+      if (n_out) T.ref_rec[(size_t)T.m + col] = rec_of(e.to);
       continue;
     }
     const uint32_t base = id_of[e.from];
-    const uint32_t slot = base + cid;
+    const uint32_t slot = base + col;
     const uint32_t cf = cont ? eff[v.fail[cont]] : 0;
     const uint32_t cont_fail = cf ? id_of[cf] : 0;
     T.check[slot] = (uint16_t)base;
@@ -161,14 +169,17 @@ inline CharTableHost pack_rows(CharTableHost T, const DfaView& v, const std::vec
     T.val[slot] = next_id | flags | (cont_fail << 16) | deep;
     if (n_out) T.ref_rec[slot] = rec_of(e.to);
   }
-  // characters that never start a key still need their cid in the root table
-  for (const auto& kv : cid_of) {
-    const uint32_t idx = T.root_index(kv.first);
-    if (T.root[idx] == 0) T.root[idx] = kv.second << 16;
-  }
   for (const CharRow& r : rows) {
     const uint32_t f = eff[v.fail[r.st]];
     T.gfail[id_of[r.st]] = (uint16_t)(f ? id_of[f] : 0);
+  }
+  // the chain states were packed first: gfail[0 .. max_chain_base] is all a chain ever reads.  What does not fit
+  // the budget stays in global memory (the walk tests the id against n_gfail_s).
+  {
+    const size_t fixed = (size_t)T.m * 4 + T.root.size() * 2 + T.check.size() * 2 + 256 + 16;
+    size_t room = smem_budget > fixed ? (smem_budget - fixed) / 2 : 0;
+    size_t want = max_chain_base ? ((size_t)max_chain_base + 1 + 7) & ~size_t(7) : 0;
+    T.n_gfail_s = (uint32_t)std::min(std::min(want, room), (size_t)T.m);
   }
   T.multi_bits.assign((T.ref_rec.size() + 15) / 16, 0u);
   for (size_t i = 0; i < T.ref_rec.size(); ++i)
@@ -250,31 +261,28 @@ inline CharTableHost build_char_table(const BlobHeader& h, const uint8_t* blob, 
       }
     }
   }
-  // 3. character ids (cid 0 = not in the dictionary) and the root index range
-  std::map<uint32_t, uint32_t> cid_of;  // unit code -> cid
+  // 3. the dictionary's characters and the root index ranges (the root index of a character is also its column)
+  std::map<uint32_t, uint32_t> seen;  // unit code -> 1
   uint32_t lo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, hi[3] = {0, 0, 0};
   for (auto& e : edges) {
     const uint32_t cls = e.code >> 30;
-    if (cid_of.emplace(e.code, 0).second && cls) {
+    if (seen.emplace(e.code, 1).second && cls) {
       lo[cls - 1] = std::min(lo[cls - 1], e.code & 0x3FFFFFFFu);
       hi[cls - 1] = std::max(hi[cls - 1], e.code & 0x3FFFFFFFu);
     }
   }
-  uint32_t n_cid = 0;
-  for (auto& kv : cid_of) kv.second = ++n_cid;
-  if (n_cid >= 0x7FFF) { T.why = "more than 32766 distinct characters"; return T; }
-  T.n_cid = n_cid;
+  T.n_cid = (uint32_t)seen.size();
   T.n_root = 256;
   for (int c = 0; c < 3; ++c) {
     T.off[c] = T.n_root;
     if (lo[c] != 0xFFFFFFFFu) {
       T.lo[c] = lo[c] & ~63u;  // multiple of 64: the kernel folds it into the decode (scan_char.cuh)
       T.n[c] = hi[c] - T.lo[c] + 1;
-      if (T.n[c] > (1u << 20)) { T.why = "character range too wide for the root table"; return T; }
+      if (T.n[c] > (1u << 15)) { T.why = "character range too wide for the root table"; return T; }
     }
     T.n_root += T.n[c] + 1;  // one zero entry behind every range: the kernel clamps an out-of-range index to it
   }
-  if ((size_t)T.n_root * 4 > smem_budget / 2) { T.why = "character range too wide for the root table"; return T; }
+  if ((size_t)T.n_root * 2 > smem_budget / 2 || T.n_root > 0xC000) { T.why = "character range too wide for the root table"; return T; }
   // 4. effective state: nearest fail-ancestor (self included) that has children; 0 = root
   std::vector<uint32_t> eff(S, 0);
   for (uint64_t s = 1; s < S; ++s) {
@@ -289,15 +297,27 @@ inline CharTableHost build_char_table(const BlobHeader& h, const uint8_t* blob, 
   for (uint32_t i = 0; i < edges.size();) {
     uint32_t j = i;
     while (j < edges.size() && edges[j].from == edges[i].from) ++j;
-    if (edges[i].from != 0) rows.push_back(Row{edges[i].from, i, j - i, parent_is_root_unit(edges[i].from, phase, parent)});
+    if (edges[i].from != 0) rows.push_back(Row{edges[i].from, i, j - i, parent_is_root_unit(edges[i].from, phase, parent), false});
     i = j;
   }
-  // first-fit packs large rows first
-  std::stable_sort(rows.begin(), rows.end(), [](const Row& a, const Row& b) { return a.count > b.count; });
+  // states a fail chain can pass through: the effective fail of a state with children (or of an edge's continuation)
+  // that has a non-root effective fail of its own.  gfail[] is read for exactly these.
+  {
+    std::vector<uint8_t> is_target(S, 0);
+    for (uint64_t s = 1; s < S; ++s)
+      if (phase[s] == 0) is_target[eff[v.fail[eff[s] ? eff[s] : 0]]] = 1;
+    for (Row& r : rows) r.chain = is_target[r.st] && eff[v.fail[r.st]] != 0;
+  }
+  // first-fit: the widest rows first (they are the hardest to place), then the chain states (smallest ids: their part
+  // of gfail[] goes to shared memory), then everything else by width
+  std::stable_sort(rows.begin(), rows.end(), [](const Row& a, const Row& b) {
+    const int ka = a.count >= 16 ? 0 : (a.chain ? 1 : 2), kb = b.count >= 16 ? 0 : (b.chain ? 1 : 2);
+    return ka != kb ? ka < kb : a.count > b.count;
+  });
   T.n_edges = (uint32_t)edges.size();
   T.n_states = (uint32_t)rows.size() + 1;
   T.ok = true;  // provisional; packing below may still fail
-  return pack_rows(T, v, edges, rows, cid_of, eff, smem_budget);
+  return pack_rows(T, v, edges, rows, eff, smem_budget);
 }
 
 }  // namespace aha

@@ -9,8 +9,8 @@
 namespace aha {
 
 struct CharTablesView {
-  const uint32_t* root;       // [n_root]
-  const uint16_t* check;      // [m]
+  const uint16_t* root;       // [n_root] one-character state:15 | fires:1; the index of a character is also its column
+  const uint16_t* check;      // [m_pad]
   const uint32_t* val;        // [m]
   const uint16_t* gfail;      // [m]   (global memory on the device)
   uint32_t lo[3], n[3], off[3];  // root index ranges for 2-, 3-, 4-byte units
@@ -70,28 +70,24 @@ AHA_HD int char_walk(const CharTablesView& T, const uint8_t* buf, int32_t w, int
         }
       }
       const uint32_t rel = code - T.lo[len - 2];
-      idx = rel < T.n[len - 2] ? T.off[len - 2] + rel : 0xFFFFFFFFu;
+      idx = T.off[len - 2] + (rel < T.n[len - 2] ? rel : T.n[len - 2]);  // out of range: the zero entry behind the range
     }
     const int32_t last = cs + len - 1;
     if (last >= b) break;  // the unit ends in the next lane's region
     if (cs >= a) ++k;
     cs += len;
-    const uint32_t r = idx == 0xFFFFFFFFu ? 0u : T.root[idx];
-    const uint32_t cid = r >> 16;
-    if (cid == 0) {  // character not in the dictionary: every suffix dies, back to the root
-      s = 0;
-      continue;
-    }
+    const uint32_t r = T.root[idx];
+    const uint32_t col = idx;  // no state has an edge in the column of a character outside the dictionary: every probe misses
     uint32_t t = s;
     bool first = true;
     for (;;) {
       if (t == 0) {  // the root: direct table entry of this character
-        if ((r & 0x8000u) && last >= a) emit(T.m + cid, last, k);
+        if ((r & 0x8000u) && last >= a) emit(T.m + col, last, k);
         s = r & 0x7FFFu;
         f1 = 0;
         break;
       }
-      const uint32_t slot = t + cid;
+      const uint32_t slot = t + col;
       if (slot < T.m && T.check[slot] == t) {
         const uint32_t v = T.val[slot];
         if ((v & 0x8000u) && last >= a) emit(slot, last, k);

@@ -24,20 +24,25 @@ constexpr uint32_t kEvMark = 0x80000000u;  // marker event: low 31 bits = docume
 // build-time variants of the walk (tools/ab.py compares them on one box)
 #ifndef AHA_W_FAST
 #define AHA_W_FAST 0     // 12-byte steps that lie wholly inside every sub-chunk's owned region skip the range and slot-bound tests
+                         // (measured on C2: 9 % fewer instructions per character, walk 2.55 -> 2.69 ms: the second copy of the step costs more)
 #endif
 #ifndef AHA_W_COUNT
 #define AHA_W_COUNT 0    // hits counted inside the walk from a 2-bit table in shared memory (measured on C2: walk 2.45 ms against
                          // 2.05 ms without: one more shared-memory lookup per character; char_count_kernel does it instead)
 #endif
+#ifndef AHA_W_PRED2
+#define AHA_W_PRED2 1    // the fail-link probe only in lanes that have a fail link (C2: walk 2.008 -> 1.981 ms)
+#endif
 #ifndef AHA_W_FMA
-#define AHA_W_FMA 0      // table addresses as multiply-adds (multiply pipe) instead of three-input adds / LEA (integer pipe)
+#define AHA_W_FMA 0      // table addresses as multiply-adds (multiply pipe) instead of three-input adds / LEA (integer pipe): 2.55 -> 2.58 ms
 #endif
 
 struct CharDeviceTables {
-  const uint32_t* root_g;   // global copies, loaded into shared memory at kernel start
+  const uint16_t* root_g;   // global copies, loaded into shared memory at kernel start
   const uint16_t* check_g;
   const uint32_t* val_g;
-  const uint16_t* gfail;    // stays in global memory
+  const uint16_t* gfail;    // [m]: the first n_gfail_s entries are copied to shared memory
+  uint32_t n_gfail_s;
   const RefRec* ref_rec;    // stays in global memory
   uint32_t n_root, m;
   uint32_t m_pad;           // entries of check[] (m + n_cid + 1, padding = 0xFFFF)
@@ -115,49 +120,53 @@ struct SmemU16 {
   __device__ __forceinline__ uint32_t operator[](uint32_t i) const { return lds_u16(mad_addr(i, 2u, base)); }
 };
 struct CharSmem {
-  SmemU32 root;            // [n_root]
-  SmemU32 root3;           // root + off[1]: entries of the 3-byte units
+  SmemU16 root;            // [n_root]
+  SmemU16 root3;           // root + off[1]: entries of the 3-byte units
   SmemU32 val;             // [m]
   SmemU16 check;           // [m_pad]
-  const uint16_t* gfail;   // global
+  SmemU16 gfail_s;         // [n_gfail_s] effective fail of the states a chain can pass through (they have the smallest ids)
+  uint32_t n_gfail_s;
+  const uint16_t* gfail;   // global: ids >= n_gfail_s (only when the prefix did not fit)
   SmemU32 mbits;           // [n_mwords] 2 bits per ref: ref_rec[ref].n if 1..3, else 0
   uint32_t m;
   uint32_t lo2, n2, off2, lo3, n3, off3, lo4, n4, off4;  // root index ranges of 2-, 3-, 4-byte units
   uint32_t neg_lo3_64;     // -(lo3 / 64): lo is a multiple of 64 (char_table.hpp)
 };
 
-// One character.  r = root entry of the character (0: not in the dictionary).  s / f1 = current state and
-// its effective fail link, deep = that fail link has a non-root fail link of its own.
+// effective fail of state t: shared memory for the ids a chain passes through, global memory beyond the prefix
+__device__ __forceinline__ uint32_t gfail_of(const CharSmem& S, uint32_t t) { return t < S.n_gfail_s ? S.gfail_s[t] : (uint32_t)S.gfail[t]; }
+
+// One character.  r = root entry of the character (0: it starts no key), col = its column (= its root index).
+// s / f1 = current state and its effective fail link, deep = that fail link has a non-root fail link of its own.
 // Returns v = next:15 | fires:1 | fail of next:15 | deep of next:1 and the firing slot.
-// Two unconditional probes (the state, then its fail link) cover everything except "deep fail link
-// missed as well", which walks gfail[] in global memory; kVote = the whole warp is converged here.
+// Two probes (the state, then its fail link) cover everything except "deep fail link missed as well", which walks
+// the gfail chain; kVote = the whole warp is converged here.
 template <bool kVote>
-__device__ __forceinline__ uint32_t char_advance(const CharSmem& S, uint32_t r, uint32_t s, uint32_t f1, bool deep, uint32_t& ref) {
-  const uint32_t cid = r >> 16;
-  const uint32_t slot1 = s + cid, slot2 = f1 + cid;
+__device__ __forceinline__ uint32_t char_advance(const CharSmem& S, uint32_t r, uint32_t col, uint32_t s, uint32_t f1, bool deep, uint32_t& ref) {
+  const uint32_t slot1 = s + col, slot2 = f1 + col;
   const uint32_t c1 = S.check[slot1], c2 = S.check[slot2];
   const bool hit1 = c1 == s, hit2 = c2 == f1;
   bool hit = hit1 || hit2;
   uint32_t slotv = hit1 ? slot1 : slot2;
-  uint32_t v = r & 0xFFFFu;  // the root entry in val[] format (fail = 0)
+  uint32_t v = r;  // the root entry in val[] format (fail = 0)
   if (hit) v = S.val[slotv];
-  const bool rare = !hit && deep && cid != 0;
+  const bool rare = !hit && deep;
   if (kVote ? __any_sync(0xffffffffu, rare) : rare) {
     if (rare) {
-      uint32_t t = S.gfail[f1];
+      uint32_t t = gfail_of(S, f1);
       while (t != 0) {
-        const uint32_t sl = t + cid;
+        const uint32_t sl = t + col;
         if (S.check[sl] == t) {
           v = S.val[sl];
           slotv = sl;
           hit = true;
           break;
         }
-        t = S.gfail[t];
+        t = gfail_of(S, t);
       }
     }
   }
-  ref = hit ? slotv : S.m + cid;
+  ref = hit ? slotv : S.m + col;
   return v;
 }
 
@@ -165,30 +174,38 @@ __device__ __forceinline__ uint32_t char_advance(const CharSmem& S, uint32_t r, 
 // probes of several sub-chunks share one basic block and overlap their shared-memory latencies),
 // char_rare() is the out-of-line continuation along gfail[].
 struct ProbeResult {
-  uint32_t v, slotv, cid;
+  uint32_t v, slotv, cid;  // cid: the character's column
   bool hit, rare;
 };
-__device__ __forceinline__ ProbeResult char_probe(const CharSmem& S, uint32_t vroot, uint32_t cid, uint32_t s, uint32_t f1, bool deep) {
+__device__ __forceinline__ ProbeResult char_probe(const CharSmem& S, uint32_t vroot, uint32_t col, uint32_t s, uint32_t f1, bool deep) {
   ProbeResult q;
-  q.cid = cid;
-  const uint32_t slot1 = s + q.cid, slot2 = f1 + q.cid;
-  const uint32_t c1 = S.check[slot1], c2 = S.check[slot2];
+  q.cid = col;
+  const uint32_t slot1 = s + col, slot2 = f1 + col;
+  const uint32_t c1 = S.check[slot1];
+#if AHA_W_PRED2
+  uint32_t c2 = 0xFFFFu;  // the second probe only where there is a fail link to probe: fewer lanes, fewer bank conflicts
+  if (f1 != 0u) c2 = S.check[slot2];
+#else
+  const uint32_t c2 = S.check[slot2];
+#endif
   const bool hit1 = c1 == s, hit2 = c2 == f1;
   q.hit = hit1 || hit2;
   const uint32_t slot12 = hit1 ? slot1 : slot2;
   q.v = vroot;  // the root entry in val[] format (fail = 0)
   if (q.hit) q.v = S.val[slot12];
-  q.slotv = q.hit ? slot12 : S.m + q.cid;  // what fires, as a ref_rec[] index
-  q.rare = !q.hit && deep && q.cid != 0;
+  q.slotv = q.hit ? slot12 : S.m + col;  // what fires, as a ref_rec[] index
+  q.rare = !q.hit && deep;
   return q;
 }
-// returns {val entry, slot} of the first fail-chain state behind f1 that has an edge for cid; slot 0 = none
-__device__ __noinline__ uint2 char_rare(SmemU16 check, SmemU32 val, const uint16_t* gfail, uint32_t f1, uint32_t cid) {
-  uint32_t t = gfail[f1];
+// returns {val entry, slot} of the first fail-chain state behind f1 that has an edge in column col; slot 0 = none
+// (out of line; the tables by value: a reference would force the caller's copy into local memory)
+__device__ __noinline__ uint2 char_rare(SmemU16 check, SmemU32 val, SmemU16 gfail_s, uint32_t n_gfail_s, const uint16_t* gfail, uint32_t f1,
+                                        uint32_t col) {
+  uint32_t t = f1 < n_gfail_s ? gfail_s[f1] : (uint32_t)gfail[f1];
   while (t != 0) {
-    const uint32_t sl = t + cid;
+    const uint32_t sl = t + col;
     if (check[sl] == t) return make_uint2(val[sl], sl);
-    t = gfail[t];
+    t = t < n_gfail_s ? gfail_s[t] : (uint32_t)gfail[t];
   }
   return make_uint2(0u, 0u);
 }
@@ -220,10 +237,6 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
   constexpr unsigned kFull = 0xffffffffu;
   const uint32_t sbuf_s = pin_u32((uint32_t)__cvta_generic_to_shared(sbuf));
   bool ok = true;
-#if defined(AHA_PERTURB_LDS) || defined(AHA_PERTURB_ALU) || defined(AHA_PERTURB_FMA)
-  uint32_t junk = 0;
-  struct JunkSink { uint32_t& j; uint32_t* out; __device__ ~JunkSink() { if (j == 0x12345679u) out[0] = j; } } junk_sink{junk, my_ev};
-#endif
   // per sub-chunk state (all offsets relative to sbuf)
   int32_t rb[kChains], a_seg[kChains], pos[kChains], de[kChains], seg_end[kChains];
   uint32_t s[kChains], f1[kChains], k[kChains];
@@ -270,9 +283,9 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
   }
 
   // consume one character of sub-chunk c whose root entry is r; cs / last = offsets of its first / last byte
-  auto step = [&](int c, uint32_t r, int32_t cs, int32_t last, auto vote) {
+  auto step = [&](int c, uint32_t r, uint32_t col, int32_t cs, int32_t last, auto vote) {
     uint32_t ref;
-    const uint32_t v = char_advance<decltype(vote)::value>(S, r, s[c], f1[c], deep[c], ref);
+    const uint32_t v = char_advance<decltype(vote)::value>(S, r, col, s[c], f1[c], deep[c], ref);
     s[c] = v & 0x7FFFu;
     f1[c] = (v >> 16) & 0x7FFFu;
     deep[c] = (v >> 31) != 0u;
@@ -305,14 +318,11 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
       q[c] = char_probe(S, vr[c], ci[c], s[c], f1[c], deep[c]);
       any_rare = any_rare || q[c].rare;
     }
-#ifdef AHA_PROBE_NORARE  // timing probe only (wrong results): never follow the gfail chain
-    any_rare = false;
-#endif
     if (__any_sync(kFull, any_rare)) {
 #pragma unroll
       for (int c = 0; c < kChains; ++c)
         if (q[c].rare) {
-          const uint2 x = char_rare(S.check, S.val, S.gfail, f1[c], q[c].cid);
+          const uint2 x = char_rare(S.check, S.val, S.gfail_s, S.n_gfail_s, S.gfail, f1[c], q[c].cid);
           if (x.y) { q[c].v = x.x; q[c].slotv = x.y; q[c].hit = true; }
         }
     }
@@ -377,11 +387,11 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
     const bool can3 = bad3 == 0u;
     if (__all_sync(kFull, can3)) {
       // four 3-byte units per sub-chunk: payload = (b0 & 0xF) << 12 | (b1 & 0x3F) << 6 | (b2 & 0x3F), root index = payload - lo
-      auto root3 = [&](uint32_t w) {
+      auto root3 = [&](uint32_t w) {  // index of the character inside its range, clamped to the zero entry behind it
         const uint32_t wm = w & 0x3F3F0Fu;
         const uint32_t h = __dp4a(wm, 0x00000140u, S.neg_lo3_64);
         const uint32_t rel = h * 64u + (wm >> 16);
-        return S.root3.base + min(rel, S.n3) * 4u;  // address of the entry; root3[n3] = 0 (char_table.hpp)
+        return min(rel, S.n3);  // root3[n3] = 0 (char_table.hpp)
       };
       // twelve bytes = three words: character u sits at a fixed place in A:B:C, one funnel shift each
       int32_t rl0[kChains];
@@ -402,18 +412,9 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
 #pragma unroll
           for (int c = 0; c < kChains; ++c) {
             const uint32_t w = u == 0 ? A[c] : (u == 1 ? __funnelshift_r(A[c], B[c], 24) : (u == 2 ? __funnelshift_r(B[c], C[c], 16) : C[c] >> 8));
-            const uint32_t ra = root3(w);
-            vr[c] = lds_u16(ra);      // the two halves of the entry as two loads: the load pipe has room, the integer pipe has not
-            ci[c] = lds_u16(ra + 2);
-#ifdef AHA_PERTURB_LDS   // sensitivity probe (not a product build): one more shared-memory load per character
-            junk += lds_u16(ra ^ 4u);
-#endif
-#ifdef AHA_PERTURB_ALU   // ... two more integer-pipe instructions per character
-            junk = (junk ^ w) & (vr[c] | 0x55u);
-#endif
-#ifdef AHA_PERTURB_FMA   // ... two more multiply-pipe instructions per character
-            junk = junk * 3u + w; junk = junk * 5u + vr[c];
-#endif
+            const uint32_t ri = root3(w);
+            vr[c] = S.root3[ri];      // state:15 | fires:1 of the character's own state
+            ci[c] = ri + S.off3;      // its column = its root index: nothing to look up
             evw[c] = pe[c] + ((uint32_t)(3 * u) << 16);
             rl[c] = rl0[c] + 3 * u;
           }
@@ -440,7 +441,7 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
         int32_t rl[kChains];
 #pragma unroll
         for (int c = 0; c < kChains; ++c) {
-          r[c] = S.root[A[c] & 0xFFu];
+          r[c] = A[c] & 0xFFu;
           rl[c] = pos[c] + i - a_seg[c];
           evw[c] = (uint32_t)(pos[c] + i + rel_base) << 16;
           A[c] = __funnelshift_r(A[c], B[c], 8);
@@ -450,8 +451,8 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
         uint32_t vr[kChains], ci[kChains];
 #pragma unroll
         for (int c = 0; c < kChains; ++c) {
-          vr[c] = r[c] & 0xFFFFu;
-          ci[c] = r[c] >> 16;
+          vr[c] = S.root[r[c]];
+          ci[c] = r[c];
         }
         multi_step(std::false_type(), vr, ci, evw, 1, rl, span);
       }
@@ -487,7 +488,7 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
           // one unit of any length
           const uint32_t b0 = A[c] & 0xFFu;
           int32_t len = 1;
-          uint32_t r = 0;
+          uint32_t r = 0, col = b0;
           if (b0 < 0x80u) {
             r = S.root[b0];
           } else if (b0 < 0xC0u || b0 >= 0xF8u) {
@@ -510,14 +511,14 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
               code = ((b0 & 0x07u) << 18) | ((b1 & 0x3Fu) << 12) | ((b2 & 0x3Fu) << 6) | (b3 & 0x3Fu);
               lo = S.lo4; n = S.n4; off = S.off4;
             }
-            const uint32_t rel = code - lo;
-            if (ok && rel < n) r = S.root[off + rel];
+            col = off + min(code - lo, n);  // out of range: the zero entry behind the range (a column no state has)
+            if (ok) r = S.root[col];
           }
           if (ok) {
             if (pos[c] + len - 1 >= rb[c]) {
               done[c] = true;  // the unit ends in the next region (the document goes on beyond it)
             } else {
-              step(c, r, pos[c], pos[c] + len - 1, std::false_type());
+              step(c, r, col, pos[c], pos[c] + len - 1, std::false_type());
               pos[c] += len;
             }
           }

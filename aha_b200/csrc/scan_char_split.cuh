@@ -50,7 +50,7 @@ struct SplitParams {
   uint32_t* tile_hits;       // [n_tiles + 1] hits of the tile (char_count_kernel), | kTileDirect for a tile the walk counted itself
   const uint64_t* tile_prefix;  // [n_tiles + 1] exclusive prefix of the hits
   const uint32_t* mbits_g;   // 2 bits per ref: hits it expands to when 1..3, 0 = see ref_rec[ref].n
-  const uint2* ref8_g;       // [n_ref8] ref_rec in 8 bytes (RefRec8): the expansion keeps it in shared memory when it fits
+  const uint2* ref8_g;       // [n_ref8] ref_rec in 8 bytes (see char_expand_kernel)
   uint32_t n_ref8;
   uint32_t* direct_list;     // [n_tiles] tiles for char_direct_kernel
   ScanStatus* status;        // total_hits, n_direct (= length of direct_list), bad_docs
@@ -76,18 +76,22 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
   const FusedParams& F = P.f;
   const ScanParams& p = F.sp;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  uint32_t* s_root = reinterpret_cast<uint32_t*>(smem);
-  uint32_t* s_val = s_root + P.t.n_root;
+  // shared layout: val u32[m] | hit-count bits (AHA_W_COUNT) | root u16[n_root] | check u16[m_pad] | gfail prefix u16 |
+  //                class map of the fallback walk | per-warp {mbarrier, text}
+  uint32_t* s_val = reinterpret_cast<uint32_t*>(smem);
   const uint32_t n_mw = AHA_W_COUNT ? P.t.n_mwords : 0u;
   uint32_t* s_mbits = s_val + P.t.m;
-  uint16_t* s_check = reinterpret_cast<uint16_t*>(s_mbits + n_mw);
-  uint8_t* s_cmap = reinterpret_cast<uint8_t*>(s_check + P.t.m_pad);
+  uint16_t* s_root = reinterpret_cast<uint16_t*>(s_mbits + n_mw);
+  uint16_t* s_check = s_root + P.t.n_root;
+  uint16_t* s_gfail = s_check + P.t.m_pad;
+  uint8_t* s_cmap = reinterpret_cast<uint8_t*>(s_gfail + P.t.n_gfail_s);
   for (uint32_t i = threadIdx.x; i < n_mw; i += blockDim.x) s_mbits[i] = P.t.mbits_g[i];
   for (uint32_t i = threadIdx.x; i < P.t.n_root; i += blockDim.x) s_root[i] = P.t.root_g[i];
   for (uint32_t i = threadIdx.x; i < P.t.m; i += blockDim.x) s_val[i] = P.t.val_g[i];
   for (uint32_t i = threadIdx.x; i < P.t.m_pad; i += blockDim.x) s_check[i] = P.t.check_g[i];
+  for (uint32_t i = threadIdx.x; i < P.t.n_gfail_s; i += blockDim.x) s_gfail[i] = P.t.gfail[i];
   for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) s_cmap[i] = P.cmap_g[i];
-  const uint32_t table_bytes = P.t.n_root * 4 + P.t.m * 4 + n_mw * 4 + P.t.m_pad * 2 + 256;
+  const uint32_t table_bytes = P.t.m * 4 + n_mw * 4 + (P.t.n_root + P.t.m_pad + P.t.n_gfail_s) * 2 + 256;
   uint8_t* wbase = smem + ((table_bytes + 127) & ~127u) + (size_t)warp * (size_t)(F.buf_bytes + 128);
   uint64_t* bar = reinterpret_cast<uint64_t*>(wbase);
   uint8_t* sbuf = wbase + 128;
@@ -98,6 +102,7 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
   CharSmem S;
   S.root.base = pin_u32(smem_u32(s_root)); S.root3.base = pin_u32(smem_u32(s_root + P.t.off[1])); S.val.base = pin_u32(smem_u32(s_val));
   S.check.base = pin_u32(smem_u32(s_check)); S.gfail = P.t.gfail; S.mbits.base = pin_u32(smem_u32(s_mbits));
+  S.gfail_s.base = pin_u32(smem_u32(s_gfail)); S.n_gfail_s = P.t.n_gfail_s;
   S.m = P.t.m;
   S.lo2 = P.t.lo[0]; S.n2 = P.t.n[0]; S.off2 = P.t.off[0];
   S.lo3 = P.t.lo[1]; S.n3 = P.t.n[1]; S.off3 = P.t.off[1];
@@ -286,12 +291,12 @@ __global__ void __launch_bounds__(256) char_count_kernel(const __grid_constant__
   __syncthreads();
   const int lane = threadIdx.x & 31;
   const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  auto hits_of = [&](uint32_t ev) -> uint32_t {
-    if (ev & kEvMark) return 0u;
+  // hits of an event from the 2-bit table; 0 there with a live event = more than three keys: looked up afterwards (rare)
+  auto bits_of = [&](uint32_t ev) -> uint32_t {
     const uint32_t ref = ev & 0xFFFFu;
-    const uint32_t n = (s_mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
-    return n ? n : Q.c.t.ref_rec[ref].n;
+    return (s_mbits[ref >> 4] >> ((ref & 15u) * 2u)) & 3u;
   };
+  // (Measured and dropped: the first rows of the next tile in flight across the tile loop, 0.35 against 0.30 ms.)
   int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   uint32_t meta = t < Q.c.f.n_tiles ? Q.tile_meta[(size_t)t * 32 + lane] : 0u;
   uint32_t th = t < Q.c.f.n_tiles ? Q.tile_hits[t] : 0u;
@@ -306,16 +311,26 @@ __global__ void __launch_bounds__(256) char_count_kernel(const __grid_constant__
     if (direct) continue;
     const uint2* mine = reinterpret_cast<const uint2*>(Q.store + (size_t)t * 32 * kStoreSlots) + lane;
     uint32_t part = 0;
+    bool more = false;
     const uint32_t mx = max(n0, n1);
-    for (uint32_t k0 = 0; k0 < mx; k0 += 8) {
-      uint2 e[8];
+    for (uint32_t k0 = 0; k0 < mx; k0 += 4) {
+      uint2 e[4];
 #pragma unroll
-      for (int j = 0; j < 8; ++j)
-        if (k0 + j < mx) e[j] = mine[(size_t)(k0 + j) * 32];
+      for (int j = 0; j < 4; ++j) e[j] = (k0 + j < mx) ? mine[(size_t)(k0 + j) * 32] : make_uint2(kEvMark, kEvMark);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        if (k0 + j < n0) part += hits_of(e[j].x);
-        if (k0 + j < n1) part += hits_of(e[j].y);
+      for (int j = 0; j < 4; ++j) {
+        const bool l0 = k0 + j < n0 && !(e[j].x & kEvMark), l1 = k0 + j < n1 && !(e[j].y & kEvMark);
+        const uint32_t c0 = l0 ? bits_of(e[j].x) : 4u, c1 = l1 ? bits_of(e[j].y) : 4u;
+        part += (c0 & 3u) + (c1 & 3u);
+        more = more || c0 == 0u || c1 == 0u;
+      }
+    }
+    if (__any_sync(0xffffffffu, more)) {  // some output list is longer than the table can say: this lane's events through ref_rec
+      part = 0;
+      for (uint32_t k = 0; k < mx; ++k) {
+        const uint2 ev = mine[(size_t)k * 32];
+        if (k < n0 && !(ev.x & kEvMark)) part += Q.c.t.ref_rec[ev.x & 0xFFFFu].n;
+        if (k < n1 && !(ev.y & kEvMark)) part += Q.c.t.ref_rec[ev.y & 0xFFFFu].n;
       }
     }
     for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
@@ -325,19 +340,14 @@ __global__ void __launch_bounds__(256) char_count_kernel(const __grid_constant__
 
 // ref_rec[] in 8 bytes: x = key id, y = key length << 16 | characters after the first   (one key fires: y != 0, bit 31 clear)
 //                       x = first index into out_val, y = 0x80000000 | n                (n >= 2 keys fire)
-// One warp per tile.  kSmemRefs: the 8-byte table sits in shared memory (one CTA of 32 warps per SM, tiles dealt
-// round-robin): the per-event lookup is a shared-memory gather of a few wavefronts instead of 32 L1 tag lookups,
-// which were 60 % of this kernel's load/store traffic.  Otherwise (table too large) ref_rec[] is read from global memory.
-template <bool kSmemRefs>
-__global__ void __launch_bounds__(kSmemRefs ? 1024 : 256, kSmemRefs ? 1 : 4) char_expand_kernel(const __grid_constant__ SplitParams Q) {
-  extern __shared__ uint2 s_ref[];
+// One warp per tile.  The lookup goes through L1 (the 8-byte table of C2 is 200 KB; this kernel uses no shared memory).
+// Measured and dropped: the table in shared memory -- 8-byte entries, one CTA of 32 warps per SM: 0.83 ms; single-key
+// entries packed into 4 bytes, two CTAs of 24 warps: 0.74 ms -- against 0.63 ms from L1 at 64 warps per SM: the kernel
+// lives on occupancy.  (16-byte ref_rec entries through L1: 0.73 ms.)
+__global__ void __launch_bounds__(256, 4) char_expand_kernel(const __grid_constant__ SplitParams Q) {
   const CharParams& P = Q.c;
   const FusedParams& F = P.f;
   const ScanParams& p = F.sp;
-  if (kSmemRefs) {
-    for (uint32_t i = threadIdx.x; i < Q.n_ref8; i += blockDim.x) s_ref[i] = Q.ref8_g[i];
-    __syncthreads();
-  }
   const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
   const int lane = threadIdx.x & 31;
   const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -357,14 +367,7 @@ __global__ void __launch_bounds__(kSmemRefs ? 1024 : 256, kSmemRefs ? 1 : 4) cha
       const bool live = base + lane < te.E;
       const bool mark = live && (ev & kEvMark);
       uint2 r8 = make_uint2(0u, 0u);
-      if (live && !mark) {
-        if (kSmemRefs) {
-          r8 = s_ref[ev & 0xFFFFu];
-        } else {
-          const RefRec rr = P.t.ref_rec[ev & 0xFFFFu];
-          r8 = rr.n == 1 ? make_uint2(rr.a, (rr.b << 16) | rr.c) : make_uint2(rr.a, rr.n ? (0x80000000u | rr.n) : 0u);
-        }
-      }
+      if (live && !mark) r8 = Q.ref8_g[ev & 0xFFFFu];
       const uint32_t n = (r8.y & 0x80000000u) ? (r8.y & 0x7FFFFFFFu) : (r8.y != 0u ? 1u : 0u);
       int64_t my_delta = delta;
       if (__any_sync(0xffffffffu, mark)) {

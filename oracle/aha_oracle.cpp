@@ -870,4 +870,40 @@ int64_t orc_cedar_match_longest(void* c, const uint8_t* s, int64_t n, int32_t ig
 }
 const Hit* orc_trie_hits() { return g_trie_hits.data(); }
 
+// the same over a batch, document-parallel (early-exit form, identical results: Q9): hit count, and in *hash_out the
+// order-sensitive checksum of the per-document streams (mix_hit) when hash_out is not null
+int64_t orc_cedar_match_longest_mt(void* c, const uint8_t* text, const int64_t* doc_off, int64_t n_docs, int32_t ignore_case,
+                                   int32_t use_sep, const uint8_t* sep_bits, int32_t sep_size, int32_t threads, uint64_t* hash_out) {
+  Cedar* da = (Cedar*)c;
+  std::atomic<int64_t> next(0), total(0);
+  std::atomic<uint64_t> hash(0);
+  Sep sep{sep_bits, sep_size};
+  auto work = [&]() {
+    std::vector<uint32_t> chars;
+    std::vector<Hit> hits;
+    int64_t local = 0;
+    uint64_t hsum = 0;
+    for (;;) {
+      const int64_t d0 = next.fetch_add(16);
+      if (d0 >= n_docs) break;
+      for (int64_t d = d0; d < std::min<int64_t>(d0 + 16, n_docs); ++d) {
+        decode_utf8(text + doc_off[d], doc_off[d + 1] - doc_off[d], chars);
+        hits.clear();
+        trie_longest(da, chars.data(), (int64_t)chars.size(), ignore_case != 0, use_sep ? &sep : nullptr, true, hits);
+        if (hash_out)
+          for (size_t j = 0; j < hits.size(); ++j) hsum += mix_hit(d, (int64_t)j, hits[j]);
+        local += (int64_t)hits.size();
+      }
+    }
+    total += local;
+    hash += hsum;
+  };
+  std::vector<std::thread> pool;
+  for (int t = 1; t < threads; t++) pool.emplace_back(work);
+  work();
+  for (auto& t : pool) t.join();
+  if (hash_out) *hash_out = hash.load();
+  return total.load();
+}
+
 }  // extern "C"

@@ -71,6 +71,8 @@ def lib():
         L.orc_cedar_match_longest.argtypes = [vp, vp, i64, i32, i32, C.c_char_p, i32, i32]
         L.orc_cedar_match_longest.restype = i64
         L.orc_trie_hits.restype = vp
+        L.orc_cedar_match_longest_mt.argtypes = [vp, vp, vp, i64, i32, i32, C.c_char_p, i32, i32, C.POINTER(C.c_uint64)]
+        L.orc_cedar_match_longest_mt.restype = i64
         _lib = L
     return _lib
 
@@ -172,6 +174,23 @@ class Cedar:
                                             bits, size, int(early_exit))
         buf = C.string_at(self._L.orc_trie_hits(), n * 12) if n else b""
         return np.frombuffer(buf, dtype=HIT_DTYPE).copy()
+
+    def _mt(self, text, doc_off, ignore_case, sep, threads, want_hash):
+        a = _as_u8(text)
+        off = np.ascontiguousarray(doc_off, dtype=np.int64)
+        bits, size = (sep_bits(sep) if sep is not None else (bytes(32), 0))
+        h = C.c_uint64()
+        n = self._L.orc_cedar_match_longest_mt(self._h, a.ctypes.data, off.ctypes.data, len(off) - 1, int(ignore_case),
+                                               int(sep is not None), bits, size, threads, C.byref(h) if want_hash else None)
+        return n, h.value
+
+    def match_longest_count_mt(self, text, doc_off, ignore_case, sep, threads):
+        """hits of CedarX#match_longest over a batch of documents, document-parallel (early-exit form, Q9)"""
+        return self._mt(text, doc_off, ignore_case, sep, threads, False)[0]
+
+    def match_longest_hash_mt(self, text, doc_off, ignore_case, sep, threads):
+        """(hit count, order-sensitive checksum of the per-document streams)"""
+        return self._mt(text, doc_off, ignore_case, sep, threads, True)
 
     def gsub(self, text, ignore_case=False, sep=None, block=None):
         """CedarX#gsub(String, ignore_case, sep) { |hit| ... } (cedar.cr:1123-1177), restated loop by loop.

@@ -253,6 +253,27 @@ def test_cedar_match_longest_random(seed):
             assert res.hits().tobytes() == np.concatenate(want).tobytes()
 
 
+def test_cedar_match_longest_long_documents():
+    """documents of several windows of the warp-per-document kernel: multi-byte characters and matches across window
+    boundaries, keys that contain the separator, with and without sep / ignore_case, one very long document"""
+    rng = random.Random(77)
+    letters = "abAB cCdé日本Я "
+    words = list(dict.fromkeys("".join(rng.choice(letters.replace(" ", "")) for _ in range(rng.randint(1, 6))) for _ in range(300)))
+    words += ["a b", "ab a", "日本 é", "b  b"]
+    words = list(dict.fromkeys(words))
+    gt, ot = aha_b200.Cedar(), O.Cedar()
+    for w in words:
+        assert gt.insert(w) == ot.insert(w)
+    docs = ["".join(rng.choice(letters) for _ in range(n)) for n in (1023, 1024, 1025, 2047, 3000, 5000, 40000)] + ["", "a"]
+    for icase in (False, True):
+        for sep in (None, [" "]):
+            res = gt.match_longest_batch(docs, icase, sep)
+            want = [ot.match_longest(d, icase, sep) for d in docs]
+            off = np.cumsum([0] + [len(w) for w in want])
+            assert np.array_equal(res.doc_hit_off(), off)
+            assert res.hits().tobytes() == np.concatenate(want).tobytes()
+
+
 ZH = "的一是在不了有和人这中大为上个国我以要他时来用们生到作地于出就分对成会可主发年动同工也能下过子说产种面而方后多定行学法所民得经"
 
 

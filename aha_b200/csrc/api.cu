@@ -82,6 +82,7 @@ static void fused_geometry(uint32_t max_key_len, bool char_kernel, int32_t* chun
 
 static int32_t build_hot_table(const aha_dfa* d, DeviceDfa* dd) {
   dd->hot = HotTable();
+  if (!d->header.has_delta) return AHA_OK;  // a dictionary too large for a dense table is far too large for shared memory
   int32_t chunk, w16, buf;
   fused_geometry(d->header.max_key_len, true, &chunk, &w16, &buf);
   const size_t total_smem = 227 * 1024;
@@ -356,7 +357,9 @@ int32_t aha_b200_debug_char_scan(const uint8_t* blob, int64_t blob_bytes, const 
   std::string err;
   if (!parse_blob(blob, blob_bytes, &h, &err)) return set_err(AHA_ERR_ARG, err);
   const DfaView v = view_of(h, blob);
-  CharTableHost T = build_char_table(h, blob, (size_t)smem_budget);
+  CharTableHost T;
+  if (h.has_delta) T = build_char_table(h, blob, (size_t)smem_budget);
+  else T.why = "automaton too large";
   memset(info, 0, 8 * sizeof(int64_t));
   *n_hits = 0;
   if (!T.ok) return set_err(AHA_OK, T.why);

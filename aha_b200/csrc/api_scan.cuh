@@ -171,7 +171,11 @@ static void fill_params(ScanParams* p, const DeviceDfa* dd, const void* dev_text
   p->doc_off = static_cast<const int64_t*>(dev_doc_off);
   p->n_docs = n_docs;
   p->classmap = dd->view.classmap;
-  p->delta = dd->view.delta;
+  p->delta = dd->view.has_delta ? dd->view.delta : nullptr;
+  p->rows = reinterpret_cast<const uint4*>(dd->view.rows);
+  p->wide = dd->view.wide;
+  p->wide_fail = dd->view.wide_fail;
+  p->n_wide_first = dd->view.wide_first ? (uint32_t)dd->view.n_wide : 0u;
   p->out_off = dd->view.out_off;
   p->out_val = dd->view.out_val;
   p->key_len = dd->view.key_len;

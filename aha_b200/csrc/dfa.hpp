@@ -1,5 +1,14 @@
 // dfa.hpp -- flattening of a compiled Aha::AC (cedar double array + @fails + @output + @key_lens)
-// into the dense byte-class DFA the GPU scans, and its serialised ("blob") form.
+// into the automaton the GPU scans, and its serialised ("blob") form.
+//
+// Two forms of the same automaton live in the blob:
+//   * SPARSE ROWS (always): 16 bytes per state = {fail link, flags, up to three goto edges {label, target}}; the one
+//     state in a hundred that has more than three children (and the root) owns a dense row of `wide[]` instead.  Of the
+//     states of a 100 k-pattern dictionary 83 % have one child and 13 % none; the rows of the 1 M-pattern dictionary
+//     are 100 MB where its dense table is 3.1 GB.  The match kernel of large dictionaries walks these: one 16-byte
+//     load per state visited (goto, else the fail link's row), exactly the loop of ACX#match_ (ac.cr:176-192).
+//   * DENSE TABLE delta[s][c] (only while S * C * 4 <= 128 MB): the closure of that loop, one lookup per byte; the
+//     shared-memory character automaton is derived from it, the per-document machines and small dictionaries use it.
 //
 // delta[s][c] is the closure of the goto/fail loop of ACX#match_ (ac.cr:176-192):
 //     delta(s,b) = child(s,b)                      if the goto edge exists (cedar.cr:441-447)
@@ -25,6 +34,17 @@ constexpr uint32_t kEnd = 0x40000000u;
 constexpr uint32_t kGoto = 0x20000000u;
 constexpr uint32_t kStateMask = 0x1FFFFFFFu;
 constexpr uint64_t kBlobMagic = 0x3130414644414841ull;  // "AHADFA01"
+constexpr uint64_t kDenseMaxBytes = (uint64_t)128 << 20;  // the dense table is kept only up to this size
+constexpr uint64_t kSparseMaxStates = (uint64_t)1 << 23;  // an edge carries its target in 23 bits
+
+// sparse row of one state.  head = fail << 8 | flags; edge = target << 9 | target-has-output << 8 | label (0 = no edge)
+// wide rows: e[0] = index of the state's dense row in wide[] (entries in edge format, label field = 1 when present)
+struct SparseRow {
+  uint32_t head;
+  uint32_t e[3];
+};
+constexpr uint32_t kRowOut = 1u, kRowWide = 2u, kRowEnd = 4u;
+constexpr uint32_t kEdgeOut = 0x100u;
 
 struct BlobHeader {
   uint64_t magic;
@@ -44,6 +64,13 @@ struct BlobHeader {
   uint64_t off_depth;     // u16[n_states]: depth in bytes (diagnostics, hot-set selection)
   uint64_t off_fail;      // u32[n_states]: failure link (ac.cr:96-105) in state numbering
   uint64_t total_bytes;
+  uint64_t off_rows;      // SparseRow[n_states]
+  uint64_t off_wide;      // u32[n_wide * n_classes]
+  uint64_t n_wide;
+  uint64_t has_delta;     // 1: off_delta holds the dense table; 0: too large, the section is empty
+  uint64_t wide_first;    // 1: states are numbered wide states first (state id < n_wide <=> wide, wide row = id);
+                          //    set when there is no dense table: the walk then reads a wide state's edge with ONE load
+  uint64_t off_wide_fail; // u32[n_wide]: fail link of the wide states (wide_first only)
 };
 
 inline uint64_t align16(uint64_t x) { return (x + 15) & ~uint64_t(15); }
@@ -58,6 +85,11 @@ struct DfaView {
   const uint32_t* key_tail;
   const uint16_t* depth;
   const uint32_t* fail;
+  const SparseRow* rows;
+  const uint32_t* wide;
+  const uint32_t* wide_fail;
+  uint64_t n_wide;
+  bool has_delta, wide_first;
   uint32_t n_classes;
   uint32_t max_key_len;
   uint64_t n_states, n_keys, n_out;
@@ -73,6 +105,12 @@ inline DfaView view_of(const BlobHeader& h, const uint8_t* base) {
   v.key_tail = reinterpret_cast<const uint32_t*>(base + h.off_key_tail);
   v.depth = reinterpret_cast<const uint16_t*>(base + h.off_depth);
   v.fail = reinterpret_cast<const uint32_t*>(base + h.off_fail);
+  v.rows = reinterpret_cast<const SparseRow*>(base + h.off_rows);
+  v.wide = reinterpret_cast<const uint32_t*>(base + h.off_wide);
+  v.n_wide = h.n_wide;
+  v.has_delta = h.has_delta != 0;
+  v.wide_first = h.wide_first != 0;
+  v.wide_fail = reinterpret_cast<const uint32_t*>(base + h.off_wide_fail);
   v.n_classes = h.n_classes;
   v.max_key_len = h.max_key_len;
   v.n_states = h.n_states;
@@ -127,7 +165,7 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
     }
   }
   const uint64_t S = slot_of.size();
-  if (S > kStateMask) {
+  if (S > kStateMask || S > kSparseMaxStates) {
     *err = "too many states";
     return false;
   }
@@ -179,25 +217,149 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
     if (output[id].value >= 0) key_tail[output[id].value] = tail[s];
   }
   out_off[S] = static_cast<uint32_t>(out_val.size());
-  // 4. layout
+  // 4. sparse rows: the children of a state are contiguous in BFS numbering
+  std::vector<uint64_t> kid_begin(S + 1, S);  // smallest child id, S when the state has no child
+  for (uint64_t s = S; s-- > 1;) kid_begin[parent[s]] = s;
+  auto kids_of = [&](uint64_t s, uint64_t* lo, uint64_t* hi) {
+    *lo = kid_begin[s];
+    *hi = *lo;
+    while (*hi < S && static_cast<uint64_t>(parent[*hi]) == s) ++*hi;
+  };
+  std::vector<uint32_t> fail_state(S, 0);
+  for (uint64_t s = 1; s < S; ++s) {
+    const int32_t f = fails[slot_of[s]];
+    if (f < 0 || f >= array_size || state_of[f] < 0 || static_cast<uint64_t>(state_of[f]) >= s) {
+      *err = "fail link does not point to an earlier state";
+      return false;
+    }
+    fail_state[s] = static_cast<uint32_t>(state_of[f]);
+  }
+  std::vector<SparseRow> rows(S);
+  std::vector<uint32_t> wide;
+  uint64_t n_wide = 0;
+  auto edge_to = [&](uint64_t t, uint32_t lab) {
+    return (static_cast<uint32_t>(t) << 9) | ((sflags[t] & kOut) ? kEdgeOut : 0u) | lab;
+  };
+  for (uint64_t s = 0; s < S; ++s) {
+    uint64_t lo, hi;
+    kids_of(s, &lo, &hi);
+    SparseRow r;
+    r.head = (fail_state[s] << 8) | ((sflags[s] & kOut) ? kRowOut : 0u) | ((sflags[s] & kEnd) ? kRowEnd : 0u);
+    r.e[0] = r.e[1] = r.e[2] = 0;
+    if (s == 0 || hi - lo > 3) {
+      r.head |= kRowWide;
+      r.e[0] = static_cast<uint32_t>(n_wide);
+      wide.resize((n_wide + 1) * C, 0u);
+      for (uint64_t t = lo; t < hi; ++t) wide[n_wide * C + classmap[label[t]]] = edge_to(t, 1u);
+      ++n_wide;
+    } else {
+      for (uint64_t t = lo; t < hi; ++t) r.e[t - lo] = edge_to(t, label[t]);
+    }
+    rows[s] = r;
+  }
+  const bool dense = S * static_cast<uint64_t>(C) * 4 <= kDenseMaxBytes;
+  // 4a. no dense table: the dense rows of the wide states are completed to closure rows -- an entry without a goto edge
+  // takes what the fail chain would find (label field 2 instead of 1; 0 = back to the root).  A wide state then never
+  // misses: the walk consumes a byte with ONE load there, and the wide states are where fail chains usually end.
+  if (!dense) {
+    auto goto_of = [&](uint32_t t, uint32_t c, uint32_t byte) -> uint32_t {  // real goto edge of state t, 0 = none
+      const SparseRow& r = rows[t];
+      if (r.head & kRowWide) {
+        const uint32_t e = wide[static_cast<uint64_t>(r.e[0]) * C + c];
+        return (e & 0xFFu) == 1u ? e : 0u;
+      }
+      for (int k = 0; k < 3; ++k)
+        if (r.e[k] && (r.e[k] & 0xFFu) == byte) return r.e[k];
+      return 0u;
+    };
+    uint8_t byte_of_class[256] = {0};
+    for (int b = 1; b < 256; ++b)
+      if (classmap[b]) byte_of_class[classmap[b]] = static_cast<uint8_t>(b);
+    for (uint64_t s = 1; s < S; ++s) {  // BFS order: the wide states on the fail chain (shallower) are complete already
+      if (!(rows[s].head & kRowWide)) continue;
+      uint32_t* row = &wide[static_cast<uint64_t>(rows[s].e[0]) * C];
+      for (uint32_t c = 1; c < C; ++c) {
+        if (row[c]) continue;
+        uint32_t t = fail_state[s], e = 0;
+        for (;;) {
+          if (rows[t].head & kRowWide) {  // complete row (or the root's): its entry is the answer
+            e = wide[static_cast<uint64_t>(rows[t].e[0]) * C + c];
+            break;
+          }
+          e = goto_of(t, c, byte_of_class[c]);
+          if (e || t == 0) break;
+          t = fail_state[t];
+        }
+        row[c] = e ? ((e & ~0xFFu) | 2u) : 0u;
+      }
+    }
+  }
+  // 4b. no dense table: renumber, wide states first in BFS order, the others behind them in BFS order.  A wide state's
+  // id is then its row in wide[], and the walk reads its edge with one load instead of two (row, then wide entry):
+  // the wide states are the shallow ones the walk is in most of the time.
+  std::vector<uint32_t> wide_fail;
+  if (!dense) {
+    std::vector<uint32_t> nid(S);
+    uint32_t next_wide = 0, next_narrow = static_cast<uint32_t>(n_wide);
+    for (uint64_t s = 0; s < S; ++s) nid[s] = (rows[s].head & kRowWide) ? next_wide++ : next_narrow++;
+    auto re_edge = [&](uint32_t e) { return e ? ((nid[e >> 9] << 9) | (e & 0x1FFu)) : 0u; };
+    std::vector<SparseRow> rows2(S);
+    std::vector<uint32_t> wide2(wide.size());
+    std::vector<uint32_t> out_off2(S + 1, 0), fail2(S), cnt(S, 0);
+    std::vector<uint16_t> depth2(S);
+    wide_fail.assign(n_wide, 0);
+    for (uint64_t s = 0; s < S; ++s) {
+      const uint32_t t = nid[s];
+      SparseRow r = rows[s];
+      r.head = (nid[r.head >> 8] << 8) | (r.head & 0xFFu);
+      if (r.head & kRowWide) {
+        for (uint32_t c = 0; c < C; ++c) wide2[static_cast<uint64_t>(t) * C + c] = re_edge(wide[static_cast<uint64_t>(r.e[0]) * C + c]);
+        r.e[0] = t;
+        wide_fail[t] = r.head >> 8;
+      } else {
+        for (int k = 0; k < 3; ++k) r.e[k] = re_edge(r.e[k]);
+      }
+      rows2[t] = r;
+      fail2[t] = nid[fail_state[s]];
+      depth2[t] = depth[s];
+      cnt[t] = out_off[s + 1] - out_off[s];
+    }
+    for (uint64_t t = 0; t < S; ++t) out_off2[t + 1] = out_off2[t] + cnt[t];
+    std::vector<int32_t> out_val2(out_val.size());
+    for (uint64_t s = 0; s < S; ++s)
+      for (uint32_t j = 0; j < out_off[s + 1] - out_off[s]; ++j) out_val2[out_off2[nid[s]] + j] = out_val[out_off[s] + j];
+    rows.swap(rows2);
+    wide.swap(wide2);
+    out_off.swap(out_off2);
+    out_val.swap(out_val2);
+    fail_state.swap(fail2);
+    depth.swap(depth2);
+  }
+  // 5. layout
   BlobHeader h;
   memset(&h, 0, sizeof(h));
   h.magic = kBlobMagic;
-  h.version = 2;
+  h.version = 3;
   h.n_classes = C;
   h.n_states = S;
   h.n_keys = static_cast<uint64_t>(n_keys);
   h.n_out = out_val.size();
   h.max_key_len = max_depth;
+  h.has_delta = dense ? 1 : 0;
+  h.wide_first = dense ? 0 : 1;
+  h.n_wide = n_wide;
   uint64_t off = align16(sizeof(BlobHeader));
   h.off_classmap = off; off = align16(off + 256);
-  h.off_delta = off; off = align16(off + S * C * 4);
+  h.off_delta = off; off = align16(off + (dense ? S * C * 4 : 0));
   h.off_out_off = off; off = align16(off + (S + 1) * 4);
   h.off_out_val = off; off = align16(off + out_val.size() * 4);
   h.off_key_len = off; off = align16(off + static_cast<uint64_t>(n_keys) * 4);
   h.off_key_tail = off; off = align16(off + static_cast<uint64_t>(n_keys) * 4);
   h.off_depth = off; off = align16(off + S * 2);
   h.off_fail = off; off = align16(off + S * 4);
+  h.off_rows = off; off = align16(off + S * sizeof(SparseRow));
+  h.off_wide = off; off = align16(off + wide.size() * 4);
+  h.off_wide_fail = off; off = align16(off + wide_fail.size() * 4);
   h.total_bytes = off;
   blob->assign(off, 0);
   uint8_t* p = blob->data();
@@ -210,27 +372,24 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
     memcpy(p + h.off_key_tail, key_tail.data(), static_cast<uint64_t>(n_keys) * 4);
   }
   memcpy(p + h.off_depth, depth.data(), S * 2);
-  // 5. delta closure in BFS order: fail targets are shallower, hence already complete; the
-  //    children of a state are contiguous in BFS numbering, so one cursor finds its goto edges.
-  uint32_t* delta = reinterpret_cast<uint32_t*>(p + h.off_delta);
-  uint64_t cursor = 1;
-  for (uint64_t s = 0; s < S; ++s) {
-    uint32_t* row = delta + s * C;
-    if (s == 0) {
-      for (uint32_t c = 0; c < C; ++c) row[c] = 0;
-    } else {
-      const int32_t f = fails[slot_of[s]];
-      if (f < 0 || f >= array_size || state_of[f] < 0 || static_cast<uint64_t>(state_of[f]) >= s) {
-        *err = "fail link does not point to an earlier state";
-        return false;
+  memcpy(p + h.off_fail, fail_state.data(), S * 4);
+  memcpy(p + h.off_rows, rows.data(), S * sizeof(SparseRow));
+  if (!wide.empty()) memcpy(p + h.off_wide, wide.data(), wide.size() * 4);
+  if (!wide_fail.empty()) memcpy(p + h.off_wide_fail, wide_fail.data(), wide_fail.size() * 4);
+  // 6. dense closure in BFS order (small automata only): fail targets are shallower, hence already complete
+  if (dense) {
+    uint32_t* delta = reinterpret_cast<uint32_t*>(p + h.off_delta);
+    for (uint64_t s = 0; s < S; ++s) {
+      uint32_t* row = delta + s * C;
+      if (s == 0) {
+        for (uint32_t c = 0; c < C; ++c) row[c] = 0;
+      } else {
+        const uint32_t* frow = delta + static_cast<uint64_t>(fail_state[s]) * C;
+        for (uint32_t c = 0; c < C; ++c) row[c] = frow[c] & ~kGoto;
       }
-      const uint32_t* frow = delta + static_cast<uint64_t>(state_of[f]) * C;
-      for (uint32_t c = 0; c < C; ++c) row[c] = frow[c] & ~kGoto;
-      reinterpret_cast<uint32_t*>(p + h.off_fail)[s] = static_cast<uint32_t>(state_of[f]);
-    }
-    while (cursor < S && static_cast<uint64_t>(parent[cursor]) == s) {
-      row[classmap[label[cursor]]] = static_cast<uint32_t>(cursor) | sflags[cursor] | kGoto;
-      ++cursor;
+      uint64_t lo, hi;
+      kids_of(s, &lo, &hi);
+      for (uint64_t t = lo; t < hi; ++t) row[classmap[label[t]]] = static_cast<uint32_t>(t) | sflags[t] | kGoto;
     }
   }
   return true;
@@ -242,7 +401,7 @@ inline bool parse_blob(const uint8_t* blob, int64_t bytes, BlobHeader* h, std::s
     return false;
   }
   memcpy(h, blob, sizeof(BlobHeader));
-  if (h->magic != kBlobMagic || h->version != 2 || h->total_bytes != static_cast<uint64_t>(bytes)) {
+  if (h->magic != kBlobMagic || h->version != 3 || h->total_bytes != static_cast<uint64_t>(bytes)) {
     *err = "bad blob header";
     return false;
   }
@@ -256,7 +415,20 @@ inline bool parse_blob(const uint8_t* blob, int64_t bytes, BlobHeader* h, std::s
   auto inside = [&](uint64_t off, uint64_t n, uint64_t width) {
     return (off & 3) == 0 && off <= T && n <= (T - off) / width;
   };
-  if (!inside(h->off_classmap, 256, 1) || !inside(h->off_delta, S * C, 4) || !inside(h->off_out_off, S + 1, 4) ||
+  if (S > kSparseMaxStates || h->has_delta > 1 || h->n_wide == 0 || h->n_wide > S) {
+    *err = "bad blob header: counts out of range";
+    return false;
+  }
+  if (h->wide_first > 1 || h->wide_first == h->has_delta) {
+    *err = "bad blob header: flags";
+    return false;
+  }
+  if (!inside(h->off_rows, S, sizeof(SparseRow)) || !inside(h->off_wide, h->n_wide * C, 4) ||
+      !inside(h->off_wide_fail, h->wide_first ? h->n_wide : 0, 4)) {
+    *err = "bad blob header: section out of bounds";
+    return false;
+  }
+  if (!inside(h->off_classmap, 256, 1) || !inside(h->off_delta, h->has_delta ? S * C : 0, 4) || !inside(h->off_out_off, S + 1, 4) ||
       !inside(h->off_out_val, O, 4) || !inside(h->off_key_len, K, 4) || !inside(h->off_key_tail, K, 4) ||
       !inside(h->off_depth, S, 2) || !inside(h->off_fail, S, 4)) {
     *err = "bad blob header: section out of bounds";
@@ -272,7 +444,23 @@ inline bool parse_blob(const uint8_t* blob, int64_t bytes, BlobHeader* h, std::s
   for (uint64_t s = 0; s < S; ++s) bad |= (v.out_off[s] > v.out_off[s + 1]) | (v.fail[s] >= S);
   bad |= v.out_off[S] != O;
   for (uint64_t j = 0; j < O; ++j) bad |= (static_cast<uint64_t>(static_cast<uint32_t>(v.out_val[j])) >= K);
-  const uint64_t n_delta = S * C;
+  for (uint64_t s = 0; s < S; ++s) {  // sparse rows: fail links, inline targets, wide row indices
+    const SparseRow& r = v.rows[s];
+    bad |= (r.head >> 8) >= S;
+    if (r.head & kRowWide) bad |= r.e[0] >= h->n_wide;
+    else
+      for (int k = 0; k < 3; ++k) bad |= (r.e[k] >> 9) >= S;
+  }
+  bad |= !(v.rows[0].head & kRowWide);
+  if (h->wide_first)
+    for (uint64_t s = 0; s < S; ++s) {  // the numbering the walk relies on: id < n_wide <=> wide, and a wide row is its id
+      const SparseRow& r = v.rows[s];
+      const bool w = (r.head & kRowWide) != 0;
+      bad |= w != (s < h->n_wide);
+      if (w) bad |= (r.e[0] != s) | (s < h->n_wide && v.wide_fail[s] != (r.head >> 8));
+    }
+  for (uint64_t i = 0; i < h->n_wide * C; ++i) bad |= (v.wide[i] >> 9) >= S;
+  const uint64_t n_delta = h->has_delta ? S * C : 0;
   uint32_t worst = 0;
   for (uint64_t i = 0; i < n_delta; ++i) {
     const uint32_t t = v.delta[i] & kStateMask;

@@ -15,7 +15,11 @@ struct ScanParams {
   int64_t n_docs;
   // automaton (device pointers into the blob)
   const uint8_t* classmap;
-  const uint32_t* delta;     // [S][C] u32: state | kOut | kEnd | kGoto
+  const uint32_t* delta;     // [S][C] u32: state | kOut | kEnd | kGoto; NULL when the automaton is too large for a dense table
+  const uint4* rows;         // [S] sparse rows (dfa.hpp SparseRow): x = fail << 8 | flags, y z w = edges
+  const uint32_t* wide;      // [n_wide][C] dense rows of the states with more than three children; row 0 = the root's
+  const uint32_t* wide_fail; // [n_wide] fail links of the wide states, and
+  uint32_t n_wide_first;     // ... n_wide when states are numbered wide first (id < n_wide_first <=> wide), else 0
   const uint32_t* out_off;
   const int32_t* out_val;
   const uint32_t* key_len;
@@ -43,6 +47,41 @@ __device__ __forceinline__ bool sep_rejects(const ScanParams& p, uint32_t chr) {
 }
 __device__ __forceinline__ bool is_sep(const ScanParams& p, uint32_t chr) {
   return chr < p.sep_size && ((p.sep_bits[chr >> 5] >> (chr & 31)) & 1u);
+}
+
+// ---- the automaton through its sparse rows -----------------------------------------------------------------------
+// goto edge of state s on `byte` (edge format: target << 9 | kEdgeOut | label), 0 when there is none; *fail = fail link
+__device__ __forceinline__ uint32_t sparse_goto(const ScanParams& p, const uint8_t* cmap, uint32_t s, uint32_t byte, uint32_t* fail) {
+  if (s < p.n_wide_first) {  // wide-first numbering: the state's id is its row in wide[]
+    *fail = __ldg(p.wide_fail + s);
+    const uint32_t e = __ldg(p.wide + (uint64_t)s * p.C + cmap[byte]);
+    return (e & 0xFFu) == 1u ? e : 0u;  // label field 2: a closure entry, not a goto edge
+  }
+  const uint4 r = __ldg(p.rows + s);
+  *fail = r.x >> 8;
+  if (r.x & kRowWide) {
+    const uint32_t e = __ldg(p.wide + (uint64_t)r.y * p.C + cmap[byte]);
+    return (e & 0xFFu) == 1u ? e : 0u;
+  }
+  return (r.y & 0xFFu) == byte ? r.y : ((r.z & 0xFFu) == byte ? r.z : ((r.w & 0xFFu) == byte ? r.w : 0u));
+}
+// entry of the goto/fail closure for (s, byte) in the dense table's format: state | kOut | kEnd | kGoto.  Read from the
+// dense table when the automaton has one, else computed by the loop the table is the closure of (ac.cr:179-190).
+__device__ __forceinline__ uint32_t delta_entry(const ScanParams& p, const uint8_t* cmap, uint32_t s, uint32_t byte) {
+  if (p.delta) return p.delta[(uint64_t)s * p.C + cmap[byte]];
+  uint32_t went = kGoto;
+  for (;;) {
+    uint32_t fail;
+    const uint32_t e = byte ? sparse_goto(p, cmap, s, byte, &fail) : 0u;
+    if (e) {
+      const uint32_t t = e >> 9;
+      const uint32_t head = __ldg(&p.rows[t].x);
+      return t | ((e & kEdgeOut) ? kOut : 0u) | ((head & kRowEnd) ? kEnd : 0u) | went;
+    }
+    if (s == 0 || !byte) return 0u;
+    s = fail;
+    went = 0u;
+  }
 }
 
 // last index d in [0, n] with a[d] <= x  (a is non-decreasing, a[0] <= x)

@@ -159,63 +159,101 @@ __device__ __forceinline__ void emit_list(const ScanParams& p, Sink& sink, uint3
   }
 }
 
-// ---- policy: dense byte-class table in global memory / L2 -----------------------------------------
+// ---- policy: the byte automaton in global memory / L2 -------------------------------------------------------------
+// Small dictionaries (dense table kept, dfa.hpp): one 4-byte load per byte from the closure table.
+// Large ones: the sparse rows.  A narrow state (at most three children: 99 % of the states) is one 16-byte row -- the goto
+// edge if the row has it, else on to the fail link's row: the loop of ACX#match_ (ac.cr:179-190) itself.  A wide state
+// (numbered first: id < n_wide) owns a dense closure row and always answers with one 4-byte entry.  The dense table of
+// the 1 M-pattern dictionary is 3.1 GB (every lookup an HBM sector); its rows are 100 MB and stay in L2.
 struct ByteGlobal {
   static constexpr int kExtraWarm = 0;
   const uint8_t* cmap_g;  // class map in global memory
   const uint8_t* cmap;    // shared memory copy (set by load_tables)
   __host__ __device__ static uint32_t table_bytes(const ByteGlobal&) { return 256; }
-  __device__ __forceinline__ void load_tables(uint8_t* tables, int tid, int nthreads) {
+  __device__ __forceinline__ void load_tables(uint8_t* tables, int tid, int nthreads, const ScanParams&) {
     for (int i = tid; i < 256; i += nthreads) tables[i] = cmap_g[i];
     cmap = tables;
   }
   // Walks lane chunk [a, b) of the staged text.  sbuf[i] is absolute byte (buf_origin + i).
-  template <class Sink>
-  __device__ __forceinline__ void walk(const FusedParams& P, const uint8_t* sbuf, int64_t buf_origin, int64_t a, int64_t b,
-                                       uint32_t lead0, Sink& sink) const {
+  // ONE loop, ONE load per iteration, no branch inside it: an iteration either consumes the byte (goto edge found,
+  // or the state is a wide one -- its row is a closure row and always answers) or moves to the fail link and looks at
+  // the same byte again.  The lanes of a warp are at different bytes of their chunks: with a loop per byte inside a
+  // loop over bytes every byte would cost the warp the LONGEST fail chain of its 32 lanes, and with a branch per kind of
+  // row the load latencies of the kinds would add up instead of overlapping.
+  //   kDense: the automaton has a dense closure table (small dictionaries): every iteration consumes.
+  template <bool kDense, class Sink>
+  __device__ __forceinline__ void walk_impl(const FusedParams& P, const uint8_t* sbuf, int64_t buf_origin, int64_t a, int64_t b,
+                                            uint32_t lead0, Sink& sink) const {
     const ScanParams& p = P.sp;
-    if (a >= b) return;
     int64_t d = last_le(p.doc_off, p.n_docs, a);
     int64_t doc_start = p.doc_off[d], doc_end = p.doc_off[d + 1];
-    const uint32_t C = p.C;
     const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
     uint32_t lead = lead0;  // characters of the current document up to (excluding) position a
     if (doc_start == a) {
       for (int64_t e = first_ge(p.doc_off, p.n_docs, a); e <= d; ++e) sink.doc_start(e);
     }
+    const uint32_t C = p.C, nw = p.n_wide_first;
+    const uint4* wide4 = reinterpret_cast<const uint4*>(p.wide);
     uint32_t s = 0;
-    {
-      int64_t w = a - (int64_t)p.warm;
-      if (w < doc_start) w = doc_start;
-      for (int64_t i = w; i < a; ++i) s = __ldg(&p.delta[(uint64_t)s * C + cmap[sbuf[i - buf_origin]]]) & kStateMask;
-    }
-    int64_t pos = a;
-    while (pos < b) {
-      const int64_t seg_end = min(b, doc_end);
-      for (; pos < seg_end; ++pos) {
-        const uint8_t byte = sbuf[pos - buf_origin];
-        if (chars) lead += ((byte & 0xC0) != 0x80);
-        const uint32_t e = __ldg(&p.delta[(uint64_t)s * C + cmap[byte]]);
-        s = e & kStateMask;
-        if (e & kOut) {
-          if constexpr (Sink::kEvents) sink.event(s, chars ? (int32_t)lead : (int32_t)(pos - doc_start + 1));
-          else emit_list(p, sink, s, pos, doc_start, doc_end, lead);
+    int64_t pos64 = a - (int64_t)p.warm;  // warm-up over the bytes in front of the owned region: states only
+    if (pos64 < doc_start) pos64 = doc_start;
+    // positions relative to the staged buffer from here on (32-bit)
+    int32_t pos = (int32_t)(pos64 - buf_origin);
+    const int32_t a_rel = (int32_t)(a - buf_origin), b_rel = (int32_t)(b - buf_origin);
+    for (;;) {
+      const int32_t seg_end = (int32_t)(min(b, doc_end) - buf_origin);
+      const int32_t end_base = (int32_t)(buf_origin - doc_start) + 1;  // end offset in the document = pos + end_base
+      while (pos < seg_end) {
+        const uint32_t byte = sbuf[pos];
+        const uint32_t cls = cmap[byte];
+        uint32_t e, fail = 0;
+        bool consume;
+        if (kDense) {
+          const uint32_t t = __ldg(p.delta + (uint64_t)s * C + cls);
+          e = ((t & kStateMask) << 9) | ((t & kOut) ? kEdgeOut : 0u);
+          consume = true;
+        } else {
+          const bool is_wide = s < nw;
+          const uint32_t widx = s * C + cls;  // (< 2^32: a wide-first automaton has well under 2^32 / C wide states)
+          const uint4 v = __ldg(is_wide ? wide4 + (widx >> 2) : p.rows + s);
+          const uint32_t sel = widx & 3u;
+          const uint32_t ew = sel == 0 ? v.x : (sel == 1 ? v.y : (sel == 2 ? v.z : v.w));
+          const uint32_t en = (v.y & 0xFFu) == byte ? v.y : ((v.z & 0xFFu) == byte ? v.z : ((v.w & 0xFFu) == byte ? v.w : 0u));
+          e = is_wide ? ew : en;
+          fail = v.x >> 8;
+          consume = is_wide || e != 0u;
         }
+        const bool own = consume && pos >= a_rel;
+        if (chars) lead += (own && (byte & 0xC0u) != 0x80u) ? 1u : 0u;
+        if (own && (e & kEdgeOut)) {
+          if constexpr (Sink::kEvents) sink.event(e >> 9, chars ? (int32_t)lead : pos + end_base);
+          else emit_list(p, sink, e >> 9, buf_origin + pos, doc_start, doc_end, lead);
+        }
+        s = consume ? (e >> 9) : fail;
+        pos += consume ? 1 : 0;
       }
-      if (pos == doc_end && (pos < b || b == p.total)) {
-        s = 0;
-        lead = 0;
+      if (!(pos == (int32_t)(doc_end - buf_origin) && (pos < b_rel || b == p.total))) break;
+      // the next document starts here: reset the automaton
+      const int64_t at = doc_end;
+      s = 0;
+      lead = 0;
+      ++d;
+      while (d < p.n_docs) {
+        sink.doc_start(d);
+        if (p.doc_off[d + 1] > at) break;
         ++d;
-        while (d < p.n_docs) {
-          sink.doc_start(d);
-          if (p.doc_off[d + 1] > pos) break;
-          ++d;
-        }
-        if (d >= p.n_docs) break;
-        doc_start = p.doc_off[d];
-        doc_end = p.doc_off[d + 1];
       }
+      if (d >= p.n_docs) break;
+      doc_start = p.doc_off[d];
+      doc_end = p.doc_off[d + 1];
     }
+  }
+  template <class Sink>
+  __device__ __forceinline__ void walk(const FusedParams& P, const uint8_t* sbuf, int64_t buf_origin, int64_t a, int64_t b,
+                                       uint32_t lead0, Sink& sink) const {
+    if (a >= b) return;
+    if (P.sp.delta) walk_impl<true>(P, sbuf, buf_origin, a, b, lead0, sink);
+    else walk_impl<false>(P, sbuf, buf_origin, a, b, lead0, sink);
   }
 };
 
@@ -296,7 +334,7 @@ __global__ void __launch_bounds__(kByteWarps * 32, 1) scan_fused_kernel(const Fu
   uint8_t* tables = smem;
   const uint32_t table_bytes = Policy::table_bytes(policy_in);
   Policy policy = policy_in;
-  policy.load_tables(tables, threadIdx.x, blockDim.x);
+  policy.load_tables(tables, threadIdx.x, blockDim.x, p);
   uint8_t* wbase = smem + ((table_bytes + 127) & ~127u) + (size_t)warp * (size_t)(P.buf_bytes + 128);
   uint64_t* bar = reinterpret_cast<uint64_t*>(wbase);
   uint8_t* sbuf = wbase + 128;

@@ -50,6 +50,15 @@ __device__ __forceinline__ int utf8_encode(uint32_t c, uint8_t* o) {
   return 4;
 }
 
+// goto edge of `from` on `byte` in the dense table's format (kGoto set iff the edge exists, kOut: the target has an output
+// list); the trie walk never follows a fail link, so without a dense table one sparse row answers
+__device__ __forceinline__ uint32_t trie_goto(const ScanParams& p, const uint8_t* cmap, uint32_t from, uint32_t byte) {
+  if (p.delta) return p.delta[(uint64_t)from * p.C + cmap[byte]];
+  uint32_t fail;
+  const uint32_t e = byte ? sparse_goto(p, cmap, from, byte, &fail) : 0u;
+  return e ? ((e >> 9) | ((e & kEdgeOut) ? kOut : 0u) | kGoto) : 0u;
+}
+
 template <bool EMIT>
 __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams p) {
   __shared__ uint8_t cmap[256];
@@ -72,14 +81,14 @@ __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams 
   // last edge (target state | flags: kOut tells whether the target has an output list, so out_off[] is only read then)
   auto jump = [&](uint32_t cp, uint32_t from) -> int64_t {
     if (cp < 0x80) {  // one byte, one edge
-      const uint32_t e = p.delta[(uint64_t)from * C + cmap[cp]];
+      const uint32_t e = trie_goto(p, cmap, from, cp);
       return (!(e & kGoto) || cp == 0) ? -1 : (int64_t)e;
     }
     uint8_t buf[4];
     const int k = utf8_encode(cp, buf);
     uint32_t e = from;
     for (int j = 0; j < k; ++j) {
-      e = p.delta[(uint64_t)(e & kStateMask) * C + cmap[buf[j]]];
+      e = trie_goto(p, cmap, e & kStateMask, buf[j]);
       if (!(e & kGoto) || buf[j] == 0) return -1;
     }
     return (int64_t)e;

@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(128) scan_v1_kernel(const ScanParams p) {
   {
     int64_t w = a - (int64_t)p.warm;
     if (w < doc_start) w = doc_start;
-    for (int64_t i = w; i < a; ++i) s = p.delta[(uint64_t)s * C + cmap[p.text[i]]] & kStateMask;
+    for (int64_t i = w; i < a; ++i) s = delta_entry(p, cmap, s, p.text[i]) & kStateMask;
   }
   int64_t pos = a;
   while (pos < b) {
@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(128) scan_v1_kernel(const ScanParams p) {
     for (; pos < seg_end; ++pos) {
       const uint8_t byte = p.text[pos];
       lead += ((byte & 0xC0) != 0x80);
-      const uint32_t e = p.delta[(uint64_t)s * C + cmap[byte]];
+      const uint32_t e = delta_entry(p, cmap, s, byte);
       s = e & kStateMask;
       if (e & kOut) run += emit_state<EMIT>(p, s, pos, doc_start, doc_end, lead, doc_lead, run);
     }
@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(128) longest_doc_kernel(const ScanParams p) {
   for (int64_t pos = doc_start; pos < doc_end; ++pos) {
     const uint8_t byte = p.text[pos];
     lead += ((byte & 0xC0) != 0x80);
-    const uint32_t e = p.delta[(uint64_t)s * C + cmap[byte]];
+    const uint32_t e = delta_entry(p, cmap, s, byte);
     if (e & kGoto) {
       s = e & kStateMask;
       if (e & kEnd) { prev_i = pos; prev_s = s; prev_lead = lead; }

@@ -421,6 +421,34 @@ def test_large_c3_properties():
     assert np.array_equal(r.doc_hit_off(), want_off) and r.hits().tobytes() == want.tobytes()
 
 
+def test_large_dictionary_without_dense_table():
+    """BASELINE config C3's dictionary has no dense table (722 k states x 121 classes > 128 MB): every mode walks the
+    sparse rows -- match (all three device paths of the fixture), sep, both longest modes, character units, and the trie
+    path -- on a few documents, every hit against the oracle"""
+    keys = synth.patterns_mix(100000)
+    D = synth.doc_bytes(1 << 15)
+    text = synth.gen_host(synth.MIX, synth.SEED_TEXT + 2, 0, 6 * D)
+    docs = _split_docs(text, D) + [b"", b"ab"]
+    g = aha_b200.AC.compile(keys)
+    o = O.AC.compile(keys)
+    assert g.info()["n_states"] * g.info()["n_classes"] * 4 > (128 << 20)
+    for mode, sep in ((0, None), (0, [" "]), (aha_b200.LONGEST, None), (aha_b200.LONGEST | aha_b200.INTERSECTABLE, None),
+                      (aha_b200.UNITS_CHAR, None)):
+        res = g.scan_batch(docs, mode, sep)
+        want, want_off = oracle_batch(o, docs, mode, sep)
+        assert np.array_equal(res.doc_hit_off(), want_off), mode
+        assert res.hits().tobytes() == want.tobytes(), mode
+    gt, ot = aha_b200.Cedar(), O.Cedar()
+    for k in keys[:30000]:
+        assert gt.insert(k) == ot.insert(k)
+    sdocs = [d.decode("utf-8") for d in docs[:3]]
+    for icase, sep in ((True, [" "]), (False, None)):
+        res = gt.match_longest_batch(sdocs, icase, sep)
+        want = [ot.match_longest(d, icase, sep) for d in sdocs]
+        assert np.array_equal(res.doc_hit_off(), np.cumsum([0] + [len(w) for w in want]))
+        assert res.hits().tobytes() == np.concatenate(want).tobytes()
+
+
 @pytest.mark.heavy
 def test_scaled_c5_million_patterns():
     """BASELINE config C5's dictionary (1 M mixed patterns: a 3.2 GB byte automaton, far beyond L2) over 256 MiB of

@@ -25,11 +25,16 @@ def _sources():
     return out
 
 
+def _units():
+    """translation units of the library: the scan paths (api.cu) and the allocation-free entry point (noalloc.cu)"""
+    return [os.path.join(CSRC, "api.cu"), os.path.join(CSRC, "noalloc.cu")]
+
+
 def build(force=False, verbose=False, out=None, extra_flags=()):
     """nvcc cross-compiles for sm_100a (no GPU needed).  Rebuilds when any source is newer."""
     if out is not None:
         nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-        subprocess.check_call([nvcc] + NVCC_FLAGS + list(extra_flags) + ["-o", out, os.path.join(CSRC, "api.cu")],
+        subprocess.check_call([nvcc] + NVCC_FLAGS + list(extra_flags) + ["-o", out] + _units(),
                               stderr=subprocess.DEVNULL)
         return out
     if os.environ.get("AHA_B200_SO"):
@@ -40,7 +45,7 @@ def build(force=False, verbose=False, out=None, extra_flags=()):
             return SO_PATH
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     extra = os.environ.get("AHA_B200_NVCC_EXTRA", "").split()  # e.g. -DAHA_B200_PHASES (per-phase cycle counters on stderr)
-    cmd = [nvcc] + NVCC_FLAGS + extra + ["-o", SO_PATH, os.path.join(CSRC, "api.cu")]
+    cmd = [nvcc] + NVCC_FLAGS + extra + ["-o", SO_PATH] + _units()
     if verbose:
         print(" ".join(cmd))
     subprocess.check_call(cmd)
@@ -66,6 +71,7 @@ EXPORTS = [
     "aha_b200_dfa_blob", "aha_b200_dfa_from_blob", "aha_b200_dfa_from_device_blob", "aha_b200_dfa_info",
     "aha_b200_dfa_free", "aha_b200_scan", "aha_b200_scan_device", "aha_b200_hits_free",
     "aha_b200_gen_text_host", "aha_b200_gen_text_device", "aha_b200_debug_char_scan", "aha_b200_debug_set",
+    "aha_b200_scan_device_noalloc",
 ]
 
 _lib = None
@@ -103,6 +109,7 @@ def lib():
     L.aha_b200_dfa_free.restype = None
     L.aha_b200_scan.argtypes = [vp, vp, vp, i64, u32, C.c_char_p, i32, P(P(Hits))]
     L.aha_b200_scan_device.argtypes = [vp, vp, vp, i64, i64, u32, C.c_char_p, i32, vp, P(P(Hits))]
+    L.aha_b200_scan_device_noalloc.argtypes = [vp, vp, vp, i64, i64, vp, i64, vp, vp, vp]
     L.aha_b200_hits_free.argtypes = [P(Hits)]
     L.aha_b200_hits_free.restype = None
     L.aha_b200_debug_char_scan.argtypes = [vp, i64, vp, i64, i32, i64, vp, i64, P(i64), P(i64)]

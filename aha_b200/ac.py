@@ -348,6 +348,18 @@ class AC:
                                          text.numel(), mode, bits, size, stream, C.byref(ph)))
         return ScanResult(ph)
 
+    def scan_device_noalloc(self, text, doc_off, hits_out, doc_hit_off_out, n_hits_out, stream=None):
+        """aha_b200_scan_device_noalloc: ACX#match (byte offsets) into caller-provided CUDA tensors, no allocation,
+        no host wait.  hits_out: int32 [cap, 3]; doc_hit_off_out: int64 [n_docs + 1]; n_hits_out: int64 [1].  At most
+        64 MiB of text per call (static scratch); calls on one device must not overlap on the GPU."""
+        if stream is None:
+            import torch
+            stream = torch.cuda.current_stream().cuda_stream
+        check(lib().aha_b200_scan_device_noalloc(self._dfa, text.data_ptr(), doc_off.data_ptr(), doc_off.numel() - 1,
+                                                 text.numel(), hits_out.data_ptr() if hits_out is not None else None,
+                                                 hits_out.shape[0] if hits_out is not None else 0,
+                                                 doc_hit_off_out.data_ptr(), n_hits_out.data_ptr(), stream))
+
     def _one(self, seq, mode, sep=None):
         if isinstance(seq, str):
             mode |= UNITS_CHAR

@@ -129,6 +129,23 @@ int32_t aha_b200_scan_device(const aha_dfa* d, const void* dev_text, const void*
                              int64_t total_bytes, uint32_t mode, const uint8_t* sep_bits, int32_t sep_size,
                              void* stream, aha_hits** out);
 void aha_b200_hits_free(aha_hits* h);
+/* ACX#match (byte offsets, mode 0) over a batch on the current device WITHOUT any allocation.  No counterpart in
+ * the reference: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  The caller passes every buffer:
+ *   dev_hits         aha_hit[hit_cap] (device); hits beyond hit_cap are counted but not written
+ *   dev_doc_hit_off  int64[n_docs + 1] (device), as aha_hits.doc_hit_off
+ *   dev_n_hits       int64[1] (device): total hits; > hit_cap means the buffer was too small
+ * The per-chunk scratch of the two-pass scan is a static __device__ array of about 1.5 MiB that every GPU which
+ * loads the library holds until exit: at most 64 MiB of text per call (AHA_ERR_ARG beyond that).  The call
+ * enqueues three kernels on `stream` and returns without waiting (results are complete when the stream reaches
+ * that point); it makes no cudaMalloc / cudaFree / cudaMallocHost, creates no stream or event, and calls no
+ * allocating library routine.  doc_off must satisfy the contract of aha_b200_scan_device (it is NOT validated
+ * here: there is no host wait to report it through).  All calls on one device share the scratch: calls that
+ * overlap on the GPU (different streams, concurrently launched graphs) race; serialise them.  The first call
+ * on a device resolves the scratch's address (cudaGetSymbolAddress) and should be made outside capture.       */
+int32_t aha_b200_scan_device_noalloc(const aha_dfa* d, const void* dev_text, const void* dev_doc_off, int64_t n_docs,
+                                     int64_t total_bytes, void* dev_hits, int64_t hit_cap, void* dev_doc_hit_off,
+                                     void* dev_n_hits, void* stream);
 
 /* ---- diagnostics ------------------------------------------------------------------------- */
 /* Test knobs (also read once from the environment): 0 = AHA_B200_NO_CHAR (byte automaton even when

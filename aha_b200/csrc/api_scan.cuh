@@ -372,6 +372,7 @@ static int32_t run_char_split(ScanParams p, ScanCall& c) {
   fp.n_tiles = (p.total + fp.tile - 1) / fp.tile;
   const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
   const bool count_only = (p.mode & AHA_COUNT_ONLY) != 0;
+  const bool sep = (p.mode & AHA_SEP) != 0;  // byte offsets only (scan_on_device)
   const HotTable& h = c.dd->hot;
   fill_char_tables(&cp.t, h);
   cp.cmap_g = p.classmap;
@@ -404,7 +405,9 @@ static int32_t run_char_split(ScanParams p, ScanCall& c) {
   static std::once_flag attr_once[64];
   cudaError_t attr_err = cudaSuccess;
   std::call_once(attr_once[c.dd->device & 63], [&] {
-    attr_err = cudaFuncSetAttribute(char_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    attr_err = cudaFuncSetAttribute(char_walk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(char_walk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   });
   AHA_CUDA(attr_err);
 
@@ -425,15 +428,21 @@ static int32_t run_char_split(ScanParams p, ScanCall& c) {
     tile_doc_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(p.doc_off, p.n_docs, fp.tile, nt, tile_doc);
     count_launch();
     AHA_CUDA(cudaEventRecord(ws->evw0, st));
-    char_walk_kernel<<<n_sm, kFusedWarps * 32, smem, st>>>(sp);
+    if (sep) char_walk_kernel<true><<<n_sm, kFusedWarps * 32, smem, st>>>(sp);
+    else char_walk_kernel<false><<<n_sm, kFusedWarps * 32, smem, st>>>(sp);
     count_launch();
     AHA_CUDA(cudaEventRecord(ws->evw1, st));
     AHA_CUDA(cudaGetLastError());
   }
 #if !AHA_W_COUNT
   if (nt > 0) {
-    const unsigned grid = (unsigned)std::min<int64_t>((nt + 7) / 8, (int64_t)n_sm * 8);
-    char_count_kernel<<<grid, 256, (size_t)h.n_mwords * 4, st>>>(sp);
+    if (sep) {  // the vetoes decide how many hits an event has: counted by the expansion's own loop
+      const unsigned grid = (unsigned)std::min<int64_t>((nt + 7) / 8, (int64_t)n_sm * 64);
+      char_expand_kernel<true, true><<<grid, 256, 0, st>>>(sp);
+    } else {
+      const unsigned grid = (unsigned)std::min<int64_t>((nt + 7) / 8, (int64_t)n_sm * 8);
+      char_count_kernel<<<grid, 256, (size_t)h.n_mwords * 4, st>>>(sp);
+    }
     count_launch();
   }
 #endif
@@ -446,7 +455,8 @@ static int32_t run_char_split(ScanParams p, ScanCall& c) {
     if (nt > 0) {
       const unsigned grid = (unsigned)std::min<int64_t>((nt + 7) / 8, (int64_t)n_sm * 64);
       if (timed) AHA_CUDA(cudaEventRecord(ws->evx0, st));
-      char_expand_kernel<<<grid, 256, 0, st>>>(sp);
+      if (sep) char_expand_kernel<true, false><<<grid, 256, 0, st>>>(sp);
+      else char_expand_kernel<false, false><<<grid, 256, 0, st>>>(sp);
       count_launch();
       if (timed) AHA_CUDA(cudaEventRecord(ws->evx1, st));
       // tiles the walk handed over (normally none: the kernel reads the list length on the device and leaves)
@@ -621,7 +631,10 @@ static int32_t scan_on_device(const aha_dfa* d, const void* dev_text, const void
   fill_params(&p, dd, dev_text, dev_doc_off, n_docs, total, mode, sep_bits, sep_size);
   const Knobs& k = knobs();
   const bool tiled_ok = !k.force_v1 && !(mode & (AHA_LONGEST | AHA_TRIE_LONGEST)) && dd->view.max_key_len <= 1024;
-  const bool split = tiled_ok && dd->hot.ok && !k.no_char && !(mode & AHA_SEP);
+  // sep with character offsets stays on the byte kernel: the neighbour tests need byte positions, the character path's
+  // events carry character positions in that mode
+  const bool sep_chars = (mode & AHA_SEP) && (mode & AHA_UNITS_CHAR);
+  const bool split = tiled_ok && dd->hot.ok && !k.no_char && !sep_chars;
   if (split) rc = run_char_split(p, c);
   else if (tiled_ok) rc = run_fused(p, c);
   else rc = run_v1(p, c);

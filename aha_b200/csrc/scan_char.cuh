@@ -87,6 +87,11 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
   asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
   return v;
 }
+__device__ __forceinline__ uint32_t lds_u8(uint32_t addr) {
+  uint32_t v;
+  asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
 __device__ __forceinline__ uint32_t lds_u16(uint32_t addr) {
   uint16_t v;
   asm("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
@@ -229,7 +234,10 @@ constexpr int kChains = 2;              // independent automata per lane: the la
 // and never reset at a document boundary -- the expansion subtracts the document's base.
 // Returns false (warp-uniform) when the text is not structurally valid UTF-8: the caller rescans the tile with the
 // byte automaton.
-template <bool kChars, int kStride, class OnDoc>
+// kSep (byte offsets only): ACX#match(seq, sep)'s veto of the byte AFTER a match (ac.cr:326) is applied here, where the text
+// is in shared memory: an event whose next byte rejects (and lies in the same document) is never stored.  With token
+// separators that is nearly every event, so the store, the count and the expansion shrink to what can still become a hit.
+template <bool kChars, int kStride, bool kSep, class OnDoc>
 __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanParams& p, const uint8_t* sbuf, int64_t origin, int64_t a,
                                                int64_t b, int32_t sub, int32_t stage_end, int32_t warmc, bool one_doc, int64_t cd,
                                                int64_t cdoc_start, int64_t cdoc_end, int32_t rel_base, const uint32_t (&rel0)[kChains],
@@ -290,7 +298,8 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
     f1[c] = (v >> 16) & 0x7FFFu;
     deep[c] = (v >> 31) != 0u;
     if (kChars) k[c] += (cs >= a_seg[c]) ? 1u : 0u;
-    const bool fire = (v & 0x8000u) && (uint32_t)(last - a_seg[c]) < (uint32_t)(rb[c] - a_seg[c]);
+    bool fire = (v & 0x8000u) && (uint32_t)(last - a_seg[c]) < (uint32_t)(rb[c] - a_seg[c]);
+    if (kSep && fire && last + 1 < de[c] && sep_rejects(p, sbuf[last + 1])) fire = false;
     if (fire) {  // n_ev[c] counts in steps of 64 = the slot-major element stride (see multi_step)
       if (n_ev[c] < (uint32_t)kStride * 64u) my_ev[n_ev[c] + c] = (kChars ? k[c] : (uint32_t)(last + rel_base)) * 65536u + ref;
       n_ev[c] += 64u;
@@ -338,6 +347,11 @@ __device__ __forceinline__ bool char_tile_walk(const CharSmem& S, const ScanPara
       int32_t vs;
       asm("shl.b32 %0, %1, 16;" : "=r"(vs) : "r"(v));
       fire[c] = kFast ? (vs < 0) : ((uint32_t)rl[c] < span[c] && vs < 0);
+      if (kSep) {
+        const int32_t nx = a_seg[c] + rl[c] + 1;  // the byte after the character (staged: the tile's 16 bytes of slack)
+        const uint32_t chr = lds_u8(sbuf_s + (uint32_t)max(nx, 0));
+        fire[c] = fire[c] && !(nx < de[c] && sep_rejects(p, chr));
+      }
     }
     // branch-free: a handful of predicated instructions per sub-chunk cost less than the divergent branches around them
 #pragma unroll

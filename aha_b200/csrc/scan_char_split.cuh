@@ -70,6 +70,8 @@ __global__ void tile_doc_kernel(const int64_t* doc_off, int64_t n_docs, int64_t 
 }
 
 // ---- 1. walk ---------------------------------------------------------------------------------------------
+// kSep: byte offsets with a separator set; the walk drops the events the byte after the match vetoes (char_tile_walk).
+template <bool kSep>
 __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __grid_constant__ SplitParams Q) {
   extern __shared__ __align__(128) uint8_t smem[];
   const CharParams& P = Q.c;
@@ -195,10 +197,15 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
     };
     const int32_t stage_end = (int32_t)(want_end - origin);
     const int32_t rel_base = 1 - (int32_t)(tile_start - origin);
-    const bool ok = chars ? char_tile_walk<true, kStoreSlotsC>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start,
-                                                                cdoc_end, rel_base, rel0, my_ev, n_ev, n_hits, lookup, on_doc)
-                          : char_tile_walk<false, kStoreSlotsC>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start,
-                                                                 cdoc_end, rel_base, rel0, my_ev, n_ev, n_hits, lookup, on_doc);
+    bool ok;
+    if constexpr (kSep)
+      ok = char_tile_walk<false, kStoreSlotsC, true>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start, cdoc_end,
+                                                     rel_base, rel0, my_ev, n_ev, n_hits, lookup, on_doc);
+    else
+      ok = chars ? char_tile_walk<true, kStoreSlotsC, false>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start,
+                                                             cdoc_end, rel_base, rel0, my_ev, n_ev, n_hits, lookup, on_doc)
+                 : char_tile_walk<false, kStoreSlotsC, false>(S, p, sbuf, origin, a, b, sub, stage_end, warmc, one_doc, cd, cdoc_start,
+                                                              cdoc_end, rel_base, rel0, my_ev, n_ev, n_hits, lookup, on_doc);
     n_ev[0] >>= 6;
     n_ev[1] >>= 6;
     const bool bad = __any_sync(0xffffffffu, !ok);
@@ -344,20 +351,31 @@ __global__ void __launch_bounds__(256) char_count_kernel(const __grid_constant__
 // Measured and dropped: the table in shared memory -- 8-byte entries, one CTA of 32 warps per SM: 0.83 ms; single-key
 // entries packed into 4 bytes, two CTAs of 24 warps: 0.74 ms -- against 0.63 ms from L1 at 64 warps per SM: the kernel
 // lives on occupancy.  (16-byte ref_rec entries through L1: 0.73 ms.)
+//
+// kSep: ACX#match(seq, sep) (ac.cr:321-340) with byte offsets.  An event's absolute end is tile start + rel, so both
+// neighbour bytes are one global load away: the byte after the match vetoes the whole event (ac.cr:326), the byte in
+// front of a key's start vetoes that key (ac.cr:333); neither test looks across a document boundary.  The hits of a
+// tile then depend on the text, not only on the events: kCount = true is the same loop without the writes and takes the
+// place of char_count_kernel (tile_hits[] for the prefix sum).
+template <bool kSep, bool kCount>
 __global__ void __launch_bounds__(256, 4) char_expand_kernel(const __grid_constant__ SplitParams Q) {
   const CharParams& P = Q.c;
   const FusedParams& F = P.f;
   const ScanParams& p = F.sp;
-  const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
+  const bool chars = !kSep && (p.mode & AHA_UNITS_CHAR) != 0;
   const int lane = threadIdx.x & 31;
   const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   for (int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < F.n_tiles; t += n_warps) {
     if (Q.tile_hits[t] & kTileDirect) continue;
     TileEvents te;
     te.init(Q, t, lane);
-    if (te.E == 0) continue;
-    const unsigned long long prefix = Q.tile_prefix[t];
+    if (te.E == 0) {
+      if (kCount && lane == 0) Q.tile_hits[t] = 0u;
+      continue;
+    }
+    const unsigned long long prefix = kCount ? 0ull : Q.tile_prefix[t];
     const TileDoc td = Q.tile_doc[t];
+    int64_t doc_lo = td.doc_start, doc_hi = td.doc_start + td.doc_len;  // kSep: bounds of the current document (carried like delta)
     // bases as 64-bit differences: end = rel + (tile base - document base)
     const int64_t tile_base = chars ? (int64_t)F.tile_lead[t] : t * (int64_t)F.tile;
     int64_t delta = tile_base - (chars ? (int64_t)p.doc_lead_base[td.doc] : td.doc_start);  // warp-uniform, updated at markers
@@ -368,8 +386,8 @@ __global__ void __launch_bounds__(256, 4) char_expand_kernel(const __grid_consta
       const bool mark = live && (ev & kEvMark);
       uint2 r8 = make_uint2(0u, 0u);
       if (live && !mark) r8 = Q.ref8_g[ev & 0xFFFFu];
-      const uint32_t n = (r8.y & 0x80000000u) ? (r8.y & 0x7FFFFFFFu) : (r8.y != 0u ? 1u : 0u);
-      int64_t my_delta = delta;
+      uint32_t n = (r8.y & 0x80000000u) ? (r8.y & 0x7FFFFFFFu) : (r8.y != 0u ? 1u : 0u);
+      int64_t my_delta = delta, my_lo = doc_lo, my_hi = doc_hi;
       if (__any_sync(0xffffffffu, mark)) {
         // document of every event of this round: the last marker at or in front of it, else the carried one
         int64_t d_here = mark ? (int64_t)(ev & ~kEvMark) : -1;
@@ -377,8 +395,34 @@ __global__ void __launch_bounds__(256, 4) char_expand_kernel(const __grid_consta
           const int64_t v = __shfl_up_sync(0xffffffffu, d_here, o);
           if (lane >= o && d_here < 0) d_here = v;
         }
-        if (d_here >= 0) my_delta = tile_base - (chars ? (int64_t)p.doc_lead_base[d_here] : p.doc_off[d_here]);
+        if (d_here >= 0) {
+          my_delta = tile_base - (chars ? (int64_t)p.doc_lead_base[d_here] : p.doc_off[d_here]);
+          if (kSep) {
+            my_lo = p.doc_off[d_here];
+            my_hi = p.doc_off[d_here + 1];
+          }
+        }
         delta = __shfl_sync(0xffffffffu, my_delta, 31);
+        if (kSep) {
+          doc_lo = __shfl_sync(0xffffffffu, my_lo, 31);
+          doc_hi = __shfl_sync(0xffffffffu, my_hi, 31);
+        }
+      }
+      const int64_t abs_end = t * (int64_t)F.tile + (int64_t)((ev >> 16) & 0x7FFFu);  // kSep: first byte after the match
+      if (kSep && n != 0) {
+        if (abs_end < my_hi && sep_rejects(p, __ldg(p.text + abs_end))) {
+          n = 0;
+        } else if (!(r8.y & 0x80000000u)) {
+          const int64_t start = abs_end - (int64_t)(r8.y >> 16);
+          if (start > my_lo && sep_rejects(p, __ldg(p.text + start - 1))) n = 0;
+        } else {
+          uint32_t keep = 0;
+          for (uint32_t j = r8.x; j < r8.x + n; ++j) {
+            const int64_t start = abs_end - (int64_t)p.key_len[p.out_val[j]];
+            keep += (start > my_lo && sep_rejects(p, __ldg(p.text + start - 1))) ? 0u : 1u;
+          }
+          n = keep;
+        }
       }
       uint32_t len_incl = n;
       for (int o = 1; o < 32; o <<= 1) {
@@ -386,13 +430,25 @@ __global__ void __launch_bounds__(256, 4) char_expand_kernel(const __grid_consta
         if (lane >= o) len_incl += v;
       }
       int64_t at = (int64_t)prefix + run + (len_incl - n);
-      if (mark) {
+      if (kCount) {
+        // nothing is written: the tile's total is all that is wanted
+      } else if (mark) {
         p.doc_hit_off[ev & ~kEvMark] = at;
       } else if (n != 0 && p.hits) {
         const int32_t end = (int32_t)((int64_t)((ev >> 16) & 0x7FFFu) + my_delta);
         if (!(r8.y & 0x80000000u)) {
           if (at < F.hit_cap)
             p.hits[at] = chars ? aha_hit{end - 1 - (int32_t)(r8.y & 0xFFFFu), end, (int32_t)r8.x} : aha_hit{end - (int32_t)(r8.y >> 16), end, (int32_t)r8.x};
+        } else if (kSep) {
+          const uint32_t n_all = r8.y & 0x7FFFFFFFu;
+          for (uint32_t j = r8.x; j < r8.x + n_all; ++j) {
+            const int32_t v = p.out_val[j];
+            const int32_t len = (int32_t)p.key_len[v];
+            const int64_t start = abs_end - len;
+            if (start > my_lo && sep_rejects(p, __ldg(p.text + start - 1))) continue;
+            if (at < F.hit_cap) p.hits[at] = aha_hit{end - len, end, v};
+            ++at;
+          }
         } else {
           for (uint32_t j = r8.x; j < r8.x + n; ++j, ++at) {
             const int32_t v = p.out_val[j];
@@ -402,6 +458,7 @@ __global__ void __launch_bounds__(256, 4) char_expand_kernel(const __grid_consta
       }
       run += __shfl_sync(0xffffffffu, len_incl, 31);
     }
+    if (kCount && lane == 0) Q.tile_hits[t] = run;
   }
 }
 

@@ -146,11 +146,15 @@ class CpuSide:
     def count(self, text, off, threads):
         if self.name == "c4":
             return self.trie.match_longest_count_mt(text, off, True, self.w["sep"], threads)
+        if self.w["mode"] or self.w["sep"]:
+            return self.ac.scan_mode_mt(text, off, threads, self.w["mode"], self.w["sep"])[0]
         return self.ac.scan_count_mt(text, off, threads)
 
     def stream_hash(self, text, off, threads):
         if self.name == "c4":
             return self.trie.match_longest_hash_mt(text, off, True, self.w["sep"], threads)
+        if self.w["mode"] or self.w["sep"]:
+            return self.ac.scan_mode_mt(text, off, threads, self.w["mode"], self.w["sep"])
         return self.ac.scan_hash_mt(text, off, threads)
 
     def timed(self, threads, budget_s, n_docs=None):
@@ -239,8 +243,16 @@ def main():
     ap.add_argument("--bytes", type=int, default=0, help="override bytes per GPU (testing)")
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--mode", default=None, choices=["match", "sep", "longest", "longest-intersectable"],
+                    help="another entry point of the same dictionary and text (AC workloads): ACX#match(seq, sep=[' ']), "
+                         "ACX#match_longest, match_longest(seq, true); default = the workload's own")
     ap.add_argument("--gather", action="store_true", help="also concatenate the ranks' hit streams on rank 0 (shard.gather_hits)")
     args = ap.parse_args()
+    if args.mode and args.workload != "c4":
+        m = {"match": (0, None), "sep": (0, [" "]), "longest": (LONGEST, None),
+             "longest-intersectable": (LONGEST | INTERSECTABLE, None)}[args.mode]
+        w0 = WORKLOADS[args.workload]
+        WORKLOADS[args.workload] = dict(w0, mode=m[0], sep=m[1], desc=w0["desc"] + " [" + args.mode + "]")
     if args.impl == "reference":
         return run_reference(args)
 

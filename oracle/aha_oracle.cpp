@@ -827,6 +827,59 @@ int64_t orc_ac_scan_hash_mt(void* a, const uint8_t* text, const int64_t* doc_off
   return total.load();
 }
 
+// Any mode of orc_ac_scan over a batch, document-parallel: ACX#match / match(sep) / match_longest (+ intersectable), byte
+// or character offsets.  Returns the hit count; *hash_out = the order-sensitive checksum of orc_ac_scan_hash_mt.
+int64_t orc_ac_scan_mode_mt(void* a, const uint8_t* text, const int64_t* doc_off, int64_t n_docs, uint32_t mode,
+                            const uint8_t* sep_bits, int32_t sep_size, int32_t threads, uint64_t* hash_out) {
+  AC* ac = (AC*)a;
+  Sep sep{sep_bits, sep_size};
+  std::atomic<int64_t> next(0), total(0);
+  std::atomic<uint64_t> hash(0);
+  auto work = [&]() {
+    int64_t local = 0;
+    uint64_t hsum = 0;
+    std::vector<Hit> out;
+    std::vector<int32_t> cob;
+    for (;;) {
+      const int64_t d = next.fetch_add(1);
+      if (d >= n_docs) break;
+      const uint8_t* seq = text + doc_off[d];
+      const int64_t n = doc_off[d + 1] - doc_off[d];
+      out.clear();
+      if (mode & ORC_LONGEST) {
+        match_longest_(ac, seq, n, (mode & ORC_INTERSECTABLE) != 0, [&](int32_t idx, int32_t nid) {
+          fetch_one(ac, idx, nid, [&](Hit h) { out.push_back(h); });
+        });
+      } else if (mode & ORC_SEP) {
+        match_(ac, seq, n, [&](int32_t idx, int32_t nid) {
+          if ((int64_t)idx + 1 < n && sep.rejects(seq[idx + 1])) return;
+          fetch(ac, idx, nid, [&](Hit h) {
+            if (h.start > 0 && sep.rejects(seq[h.start - 1])) return;
+            out.push_back(h);
+          });
+        });
+      } else {
+        match_(ac, seq, n, [&](int32_t idx, int32_t nid) { fetch(ac, idx, nid, [&](Hit h) { out.push_back(h); }); });
+      }
+      if (mode & ORC_UNITS_CHAR) {
+        char_map(seq, n, cob);
+        for (Hit& h : out) h = Hit{cob[h.start], cob[h.end - 1] + 1, h.value};
+      }
+      int64_t j = 0;
+      for (const Hit& h : out) hsum += mix_hit(d, j++, h);
+      local += j;
+    }
+    total += local;
+    hash += hsum;
+  };
+  std::vector<std::thread> pool;
+  for (int t = 1; t < threads; t++) pool.emplace_back(work);
+  work();
+  for (auto& t : pool) t.join();
+  if (hash_out) *hash_out = hash.load();
+  return total.load();
+}
+
 // synthetic corpus text (include/aha_synth.h): the reference arm of bench.py generates its own input
 int32_t orc_gen_text(int32_t corpus, uint64_t seed, int64_t first, int64_t bytes, uint8_t* out, int32_t threads) {
   if (corpus < 0 || corpus > 2 || first < 0 || bytes < 0) return -1;

@@ -66,6 +66,8 @@ def lib():
         L.orc_ac_scan_count_mt.restype = i64
         L.orc_ac_scan_hash_mt.argtypes = [vp, vp, vp, i64, i32, C.POINTER(C.c_uint64)]
         L.orc_ac_scan_hash_mt.restype = i64
+        L.orc_ac_scan_mode_mt.argtypes = [vp, vp, vp, i64, C.c_uint32, C.c_char_p, i32, i32, C.POINTER(C.c_uint64)]
+        L.orc_ac_scan_mode_mt.restype = i64
         L.orc_gen_text.argtypes = [i32, C.c_uint64, i64, i64, vp, i32]
         L.orc_gen_text.restype = i32
         L.orc_cedar_match_longest.argtypes = [vp, vp, i64, i32, i32, C.c_char_p, i32, i32]
@@ -286,6 +288,17 @@ class AC:
         a = _as_u8(text)
         off = np.ascontiguousarray(doc_off, dtype=np.int64)
         return self._L.orc_ac_scan_count_mt(self._h, a.ctypes.data, off.ctypes.data, len(off) - 1, threads)
+
+    def scan_mode_mt(self, text, doc_off, threads, mode=0, sep=None, sep_size=256):
+        """any mode of scan() over a batch: (hit count, order-sensitive checksum of the per-document hit streams)"""
+        a = _as_u8(text)
+        off = np.ascontiguousarray(doc_off, dtype=np.int64)
+        bits, size = (sep_bits(sep, sep_size) if sep is not None else (bytes(32), 0))
+        if sep is not None:
+            mode |= SEP
+        h = C.c_uint64()
+        n = self._L.orc_ac_scan_mode_mt(self._h, a.ctypes.data, off.ctypes.data, len(off) - 1, mode, bits, size, threads, C.byref(h))
+        return n, h.value
 
     def scan_hash_mt(self, text, doc_off, threads):
         """(hit count, order-sensitive 64-bit checksum of the per-document hit streams)"""

@@ -361,6 +361,60 @@ def test_full_size_c2_properties():
     assert (ha + hb) % (1 << 64) == whole % (1 << 64)
 
 
+def _doc_stream_hash(res):
+    """(hits, checksum) of a device result in the oracle's batch formula (bench.gpu_stream_hash: mix of document,
+    index in the document, start, end, value)"""
+    import bench
+    return bench.gpu_stream_hash(res.hits_tensor(), res.doc_hit_off_tensor(), res.n_docs)
+
+
+@pytest.mark.heavy
+@pytest.mark.parametrize("cfg", ["c2", "c3"])
+def test_modes_at_config_scale(cfg):
+    """ACX#match(sep), match_longest (+ intersectable) and the String forms on inputs of the configurations' shape
+    (64 documents of 1 MiB, the configuration's dictionary): hit count and order-sensitive checksum of every
+    document's stream against the oracle's document-parallel batch scan."""
+    import torch
+    if cfg == "c2":
+        keys, corpus, seed = synth.patterns_zh_ngrams(10000), synth.ZH, synth.SEED_TEXT + 1
+    else:
+        keys, corpus, seed = synth.patterns_mix(100000), synth.MIX, synth.SEED_TEXT + 2
+    g = aha_b200.AC.compile(keys)
+    o = O.AC.compile(keys)
+    D = synth.doc_bytes(1 << 20)
+    n_docs = 64
+    dev = synth.gen_device(corpus, seed, 0, n_docs * D)
+    doc_off = torch.arange(0, n_docs + 1, dtype=torch.int64, device="cuda") * D
+    host = dev.cpu().numpy()
+    host_off = np.arange(n_docs + 1, dtype=np.int64) * D
+    threads = os.cpu_count() or 4
+    L, I, U = aha_b200.LONGEST, aha_b200.INTERSECTABLE, aha_b200.UNITS_CHAR
+    for mode, sep in [(0, [" "]), (0, ["\n", " "]), (U, [" "]), (L, None), (L | I, None), (L | U, None), (U, None)]:
+        res = g.scan_device(dev, doc_off, mode, sep)
+        want_n, want_h = o.scan_mode_mt(host, host_off, threads, mode, sep)
+        got_n, got_h = _doc_stream_hash(res)
+        assert (res.n_hits, got_n, got_h) == (want_n, want_n, want_h), "mode %d sep %r" % (mode, sep)
+
+
+def test_sep_on_the_character_path():
+    """ACX#match(seq, sep) with byte offsets runs on the shared-memory character automaton: the vetoes are applied by
+    the expansion.  Neighbours across document boundaries never veto; sep sizes below 256 (Q7); dense nested hits."""
+    keys = ["的", "的的", "一的", "ab", "b", "abc", "c d"]
+    docs = ["的的 的一的 的", "的", "", "的的", " 的 ", "ab abc b", "abc", "c d c d", "xab", "ab的", "的ab 的"]
+    for sep, size in [([" "], 256), ([" "], 33), ([" "], 32), ([" ", "a"], 128), ([], 256), ([" "], 0)]:
+        check_batch(keys, docs, sep=sep, sep_size=size)
+    # a hit that ends a document followed by a document that starts with a non-separator, many tiny documents
+    check_batch(keys, ["的", "的的", "ab", "b", ""] * 700, sep=[" "])
+    # dense hits: event slots overflow -> direct pass with the same vetoes
+    check_batch(keys, ["的" * 6000, "的 " * 3000, "ab " * 2000 + "的一的" * 800], sep=[" "])
+    rng = random.Random(77)
+    alpha = ZH[:5] + "ab  "
+    big = _utf8_keys(rng, alpha, 3000, 5)
+    docs = ["".join(rng.choice(alpha) for _ in range(rng.choice([0, 5, 700, 9000]))) for _ in range(120)]
+    check_batch(big, docs, sep=[" "])
+    check_batch(big, docs, sep=[" ", "a"], sep_size=200)
+
+
 def test_hit_density_swings_between_calls():
     """One dictionary, batches whose hit density swings by orders of magnitude between calls: the hit buffer is sized
     per call after the walk has counted, whatever the previous call looked like."""

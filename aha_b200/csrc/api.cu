@@ -14,6 +14,7 @@
 #include "scan_common.cuh"
 #include "scan_v1.cuh"
 #include "scan_trie.cuh"
+#include "scan_longest.cuh"
 #include "scan_fused.cuh"
 #include "scan_char.cuh"
 #include "scan_char_split.cuh"

@@ -109,6 +109,9 @@ enum WsSlot {
   kWsOffsets,
   kWsDocScratch,
   kWsAligned,        // aligned copy of a text whose device pointer is not 16-byte aligned
+  kWsLongA,          // match_longest in chunks: exit states (two rounds) and the entry state of every chunk's last walk
+  kWsLongB,
+  kWsLongEntry,
   kWsSlots
 };
 

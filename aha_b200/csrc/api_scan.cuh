@@ -343,6 +343,86 @@ static int32_t run_v1(ScanParams p, ScanCall& c) {
   return read_status(c, status, ws->evw1);
 }
 
+// ACX#match_longest in parallel inside documents: speculative chunks (scan_longest.cuh)
+static int32_t run_longest_chunks(ScanParams p, ScanCall& c) {
+  cudaStream_t st = c.st;
+  Workspace* ws = c.ws;
+  const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
+  p.chunk = kLongChunk;
+  p.n_chunks = (p.total + kLongChunk - 1) / kLongChunk;
+  const int64_t n = p.n_chunks;
+  uint32_t* counts = nullptr;
+  uint64_t* offsets = nullptr;
+  ScanStatus* status = nullptr;
+  LongParams q;
+  memset(&q, 0, sizeof(q));
+  LongState *xa = nullptr, *xb = nullptr;
+  AHA_CUDA(ws->get(kWsCounts, (size_t)n + 1, &counts));
+  AHA_CUDA(ws->get(kWsOffsets, (size_t)n + 1, &offsets));
+  AHA_CUDA(ws->get(kWsStatus, 4, &status));
+  AHA_CUDA(ws->get(kWsLongA, (size_t)n + 1, &xa));
+  AHA_CUDA(ws->get(kWsLongB, (size_t)n + 1, &xb));
+  AHA_CUDA(ws->get(kWsLongEntry, (size_t)n + 1, &q.entry_used));
+  int32_t rc = alloc_doc_hit_off(c, p.n_docs, &p.doc_hit_off);
+  if (rc) return rc;
+  AHA_CUDA(cudaMemsetAsync(counts, 0, (n + 1) * sizeof(uint32_t), st));
+  AHA_CUDA(cudaMemsetAsync(p.doc_hit_off, 0, (p.n_docs + 1) * sizeof(int64_t), st));
+  AHA_CUDA(cudaMemsetAsync(status, 0, 2 * sizeof(ScanStatus), st));
+  p.counts = counts;
+  p.offsets = offsets;
+  q.changed = &status[1].n_direct;
+  AHA_CUDA(cudaEventRecord(ws->ev0, st));
+  if (!c.validated) {
+    validate_docs_kernel<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(p.doc_off, p.n_docs, p.total, status);
+    count_launch();
+  }
+  if (chars && p.total > 0) {
+    const uint64_t* lead_prefix = nullptr;
+    rc = lead_prepass(c, p, kLongChunk, n, &lead_prefix);
+    if (rc) return rc;
+    p.lead_prefix = lead_prefix;
+  }
+  const unsigned grid = (unsigned)((n + 127) / 128);
+  if (n > 0) {
+    q.sp = p;
+    q.exit_prev = xb;
+    q.exit_next = xa;
+    longest_chunk_kernel<0><<<grid, 128, 0, st>>>(q);
+    count_launch();
+    // settle: until a round finds every chunk walked from its predecessor's exit (one small read-back per round)
+    for (int64_t round = 0; round <= n; ++round) {
+      std::swap(q.exit_prev, q.exit_next);
+      AHA_CUDA(cudaMemsetAsync(q.changed, 0, sizeof(unsigned int), st));
+      longest_chunk_kernel<1><<<grid, 128, 0, st>>>(q);
+      count_launch();
+      AHA_CUDA(cudaMemcpyAsync(&ws->h_status->n_direct, q.changed, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
+      AHA_CUDA(cudaStreamSynchronize(st));
+      if (ws->h_status->n_direct == 0) break;
+    }
+  }
+  rc = exclusive_sum_u32_to_u64(ws, counts, offsets, n + 1, st);
+  if (rc) return rc;
+  AHA_CUDA(cudaMemcpyAsync(&ws->h_status->total_hits, offsets + n, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+  AHA_CUDA(cudaStreamSynchronize(st));
+  const unsigned long long total_hits = ws->h_status->total_hits;
+  c.res->n_hits = (int64_t)total_hits;
+  if (!(p.mode & AHA_COUNT_ONLY)) {
+    rc = alloc_hits(c, (int64_t)total_hits, &p.hits);
+    if (rc) return rc;
+  }
+  if (n > 0) {
+    q.sp = p;
+    longest_chunk_kernel<2><<<grid, 128, 0, st>>>(q);
+    count_launch();
+  }
+  // documents that start at the very end of the text (and the sentinel) when the last chunk did not reach them
+  finalize_doc_off_kernel<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(p.doc_off, p.n_docs, p.total, reinterpret_cast<const unsigned long long*>(offsets + n), p.doc_hit_off);
+  count_launch();
+  AHA_CUDA(cudaEventRecord(ws->ev1, st));
+  AHA_CUDA(cudaGetLastError());
+  return read_status(c, status, ws->evw1);
+}
+
 static void fill_char_tables(CharDeviceTables* t, const HotTable& h) {
   t->root_g = reinterpret_cast<const uint16_t*>(h.dev + h.off_root);
   t->val_g = reinterpret_cast<const uint32_t*>(h.dev + h.off_val);
@@ -635,8 +715,11 @@ static int32_t scan_on_device(const aha_dfa* d, const void* dev_text, const void
   // events carry character positions in that mode
   const bool sep_chars = (mode & AHA_SEP) && (mode & AHA_UNITS_CHAR);
   const bool split = tiled_ok && dd->hot.ok && !k.no_char && !sep_chars;
+  // match_longest: speculative chunks inside documents (knob 1 keeps the one-thread-per-document machine)
+  const bool long_chunks = (mode & AHA_LONGEST) && !(mode & AHA_TRIE_LONGEST) && !k.force_v1;
   if (split) rc = run_char_split(p, c);
   else if (tiled_ok) rc = run_fused(p, c);
+  else if (long_chunks) rc = run_longest_chunks(p, c);
   else rc = run_v1(p, c);
   if (rc == AHA_OK) {
     float ms = 0;

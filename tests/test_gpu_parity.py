@@ -415,6 +415,24 @@ def test_sep_on_the_character_path():
     check_batch(big, docs, sep=[" ", "a"], sep_size=200)
 
 
+def test_match_longest_inside_long_documents():
+    """ACX#match_longest runs as speculative 512-byte chunks inside a document: long documents (many chunks), document
+    ends inside and exactly at chunk borders, pending ends carried across chunks, and texts on which the machine never
+    re-synchronises with a guessed start (periodic text: the settle rounds walk the document chunk by chunk)."""
+    L, I, U = aha_b200.LONGEST, aha_b200.INTERSECTABLE, aha_b200.UNITS_CHAR
+    rng = random.Random(5)
+    keys = ["a", "aa", "aaa", "aaaaa", "ab", "abab", "b", "ba" * 20, "的", "的的的", "的一", "一" * 7, "x" * 300]
+    docs = ["a" * 5000, "ab" * 3000, "a" * 512, "b" * 511, "a", "", "a" * 1024, "的" * 2000, "的一" * 1500 + "的的的的",
+            "x" * 299 + "ab" + "x" * 700, "ba" * 400 + "a" * 300, "a" * 513]
+    docs += ["".join(rng.choice("ab的一x ") for _ in range(rng.choice([0, 7, 511, 512, 513, 4000]))) for _ in range(60)]
+    for mode in (L, L | I, L | U, L | I | U):
+        check_batch(keys, docs, mode)
+    big = _utf8_keys(rng, ZH[:12] + "ab", 3000, 6)
+    docs = ["".join(rng.choice(ZH[:12] + "ab") for _ in range(rng.choice([100, 3000, 20000]))) for _ in range(40)]
+    for mode in (L, L | I, L | U):
+        check_batch(big, docs, mode)
+
+
 def test_hit_density_swings_between_calls():
     """One dictionary, batches whose hit density swings by orders of magnitude between calls: the hit buffer is sized
     per call after the walk has counted, whatever the previous call looked like."""

@@ -14,7 +14,7 @@ import numpy as np
 from . import _lib
 from ._lib import AhaError, Hits, check, lib
 
-UNITS_CHAR, SEP, LONGEST, INTERSECTABLE, TRIE_LONGEST, IGNORE_CASE, COUNT_ONLY = 1, 2, 4, 8, 16, 32, 64
+UNITS_CHAR, SEP, LONGEST, INTERSECTABLE, TRIE_LONGEST, IGNORE_CASE, COUNT_ONLY, SEP_CODEPOINT = 1, 2, 4, 8, 16, 32, 64, 128
 
 HIT_DTYPE = np.dtype([("start", "<i4"), ("end", "<i4"), ("value", "<i4")])
 NODE_DTYPE = np.dtype([("value", "<i4"), ("check", "<i4"), ("sibling", "u1"), ("child", "u1"), ("flags", "<u2")])
@@ -85,9 +85,14 @@ class Cedar:
         character offsets.  Runs on the GPU over the trie part of the flattened automaton."""
         return self.match_longest_batch([text], ignore_case, sep).hits()
 
-    def match_longest_batch(self, docs, ignore_case=False, sep=None):
+    def to_gpu(self):
+        """CedarX#to_gpu (src/aha_gpu.cr): the trie alone on the GPU, through ACX.compile(da) (ac.cr:71-112)."""
         if self._ac is None:
             self._ac = AC.compile(self)
+        return self._ac
+
+    def match_longest_batch(self, docs, ignore_case=False, sep=None):
+        self.to_gpu()
         return self._ac.scan_batch(docs, TRIE_LONGEST | (IGNORE_CASE if ignore_case else 0), sep)
 
     def gsub(self, text, ignore_case=False, sep=None, block=None):
@@ -361,8 +366,14 @@ class AC:
                                                  doc_hit_off_out.data_ptr(), n_hits_out.data_ptr(), stream))
 
     def _one(self, seq, mode, sep=None):
+        """seq: bytes (byte offsets), str (String overloads: character offsets), or a list / tuple of 1-character strings
+        (the Array(Char) / Slice(Char) overloads, ac.cr:288-295, 312-319, 342-364: character offsets, and with `sep` the
+        neighbour test on the neighbouring character's code point)."""
         if isinstance(seq, str):
             mode |= UNITS_CHAR
+        elif isinstance(seq, (list, tuple)) and all(isinstance(c, str) for c in seq):
+            seq = "".join(seq)
+            mode |= UNITS_CHAR | (SEP_CODEPOINT if sep is not None else 0)
         return self.scan_batch([seq], mode, sep).hits()
 
     def match(self, seq, sep=None):

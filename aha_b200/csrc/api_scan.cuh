@@ -713,7 +713,7 @@ static int32_t scan_on_device(const aha_dfa* d, const void* dev_text, const void
   const bool tiled_ok = !k.force_v1 && !(mode & (AHA_LONGEST | AHA_TRIE_LONGEST)) && dd->view.max_key_len <= 1024;
   // sep with character offsets stays on the byte kernel: the neighbour tests need byte positions, the character path's
   // events carry character positions in that mode
-  const bool sep_chars = (mode & AHA_SEP) && (mode & AHA_UNITS_CHAR);
+  const bool sep_chars = (mode & AHA_SEP) && (mode & (AHA_UNITS_CHAR | AHA_SEP_CODEPOINT));
   const bool split = tiled_ok && dd->hot.ok && !k.no_char && !sep_chars;
   // match_longest: speculative chunks inside documents (knob 1 keeps the one-thread-per-document machine)
   const bool long_chunks = (mode & AHA_LONGEST) && !(mode & AHA_TRIE_LONGEST) && !k.force_v1;

@@ -49,6 +49,31 @@ __device__ __forceinline__ bool is_sep(const ScanParams& p, uint32_t chr) {
   return chr < p.sep_size && ((p.sep_bits[chr >> 5] >> (chr & 31)) & 1u);
 }
 
+// The two neighbour tests of ACX#match(seq, sep).  Bytes / String forms (ac.cr:324-336): the neighbouring BYTE.
+// Array(Char) / Slice(Char) forms (ac.cr:346-360, AHA_SEP_CODEPOINT): the code point of the neighbouring CHARACTER --
+// only code points below sep.size <= 256 can veto, i.e. an ASCII byte or a two-byte unit led by 0xC2 / 0xC3.
+// `next` = absolute index of the first byte after the match; `start` = absolute index of the key's first byte.
+__device__ __forceinline__ bool sep_veto_after(const ScanParams& p, int64_t next, int64_t doc_end) {
+  if (next >= doc_end) return false;
+  uint32_t chr = p.text[next];
+  if ((p.mode & AHA_SEP_CODEPOINT) && chr >= 0x80u) {
+    if ((chr == 0xC2u || chr == 0xC3u) && next + 1 < doc_end) chr = ((chr & 0x1Fu) << 6) | (p.text[next + 1] & 0x3Fu);
+    else return false;
+  }
+  return sep_rejects(p, chr);
+}
+__device__ __forceinline__ bool sep_veto_before(const ScanParams& p, int64_t start, int64_t doc_start) {
+  if (start <= doc_start) return false;
+  uint32_t chr = p.text[start - 1];
+  if ((p.mode & AHA_SEP_CODEPOINT) && chr >= 0x80u) {
+    if ((chr & 0xC0u) != 0x80u || start - 2 < doc_start) return false;
+    const uint32_t b0 = p.text[start - 2];
+    if (b0 != 0xC2u && b0 != 0xC3u) return false;
+    chr = ((b0 & 0x1Fu) << 6) | (chr & 0x3Fu);
+  }
+  return sep_rejects(p, chr);
+}
+
 // ---- the automaton through its sparse rows -----------------------------------------------------------------------
 // goto edge of state s on `byte` (edge format: target << 9 | kEdgeOut | label), 0 when there is none; *fail = fail link
 __device__ __forceinline__ uint32_t sparse_goto(const ScanParams& p, const uint8_t* cmap, uint32_t s, uint32_t byte, uint32_t* fail) {

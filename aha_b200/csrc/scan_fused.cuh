@@ -147,13 +147,13 @@ struct TallySink {
 template <class Sink>
 __device__ __forceinline__ void emit_list(const ScanParams& p, Sink& sink, uint32_t state, int64_t pos, int64_t doc_start,
                                           int64_t doc_end, uint32_t end_char) {
-  if ((p.mode & AHA_SEP) && pos + 1 < doc_end && sep_rejects(p, p.text[pos + 1])) return;
+  if ((p.mode & AHA_SEP) && sep_veto_after(p, pos + 1, doc_end)) return;
   const uint32_t j1 = p.out_off[state + 1];
   const int32_t end = (int32_t)(pos - doc_start + 1);
   for (uint32_t j = p.out_off[state]; j < j1; ++j) {
     const int32_t v = p.out_val[j];
     const int32_t start = end - (int32_t)p.key_len[v];
-    if ((p.mode & AHA_SEP) && start > 0 && sep_rejects(p, p.text[doc_start + start - 1])) continue;
+    if ((p.mode & AHA_SEP) && sep_veto_before(p, doc_start + start, doc_start)) continue;
     if (p.mode & AHA_UNITS_CHAR) sink.hit((int32_t)end_char - 1 - (int32_t)p.key_tail[v], (int32_t)end_char, v);
     else sink.hit(start, end, v);
   }

@@ -12,14 +12,14 @@ namespace aha {
 template <bool EMIT>
 __device__ __forceinline__ uint32_t emit_state(const ScanParams& p, uint32_t state, int64_t pos, int64_t doc_start,
                                                 int64_t doc_end, uint64_t lead_incl, uint64_t doc_lead, uint64_t out_at) {
-  if ((p.mode & AHA_SEP) && pos + 1 < doc_end && sep_rejects(p, p.text[pos + 1])) return 0;
+  if ((p.mode & AHA_SEP) && sep_veto_after(p, pos + 1, doc_end)) return 0;
   uint32_t n = 0;
   const uint32_t j1 = p.out_off[state + 1];
   const int32_t end = (int32_t)(pos - doc_start + 1);
   for (uint32_t j = p.out_off[state]; j < j1; ++j) {
     const int32_t v = p.out_val[j];
     const int32_t start = end - (int32_t)p.key_len[v];
-    if ((p.mode & AHA_SEP) && start > 0 && sep_rejects(p, p.text[doc_start + start - 1])) continue;
+    if ((p.mode & AHA_SEP) && sep_veto_before(p, doc_start + start, doc_start)) continue;
     if (EMIT && p.hits) {
       aha_hit h;
       if (p.mode & AHA_UNITS_CHAR) {

@@ -57,7 +57,11 @@ enum aha_mode {
   AHA_INTERSECTABLE = 8,  /* match_longest(seq, true)        (ac.cr:131-137)                           */
   AHA_TRIE_LONGEST = 16,  /* CedarX#match_longest(String, ignore_case, sep) (cedar.cr:1075-1121)       */
   AHA_IGNORE_CASE = 32,   /* with AHA_TRIE_LONGEST           (cedar.cr:995-996)                        */
-  AHA_COUNT_ONLY = 64     /* no hit records, only doc_hit_off (bench / sizing)                         */
+  AHA_COUNT_ONLY = 64,    /* no hit records, only doc_hit_off (bench / sizing)                         */
+  AHA_SEP_CODEPOINT = 128 /* with AHA_SEP: the Array(Char) / Slice(Char) forms of match(seq, sep) (ac.cr:342-364):
+                             the neighbour test is on the CODE POINT of the neighbouring character, not on
+                             its byte, so a neighbour >= U+0100 (>= sep.size) never vetoes; used with
+                             AHA_UNITS_CHAR (those forms yield character offsets)                        */
 };
 
 /* ---- library / devices ------------------------------------------------------------------- */

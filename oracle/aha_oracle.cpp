@@ -673,6 +673,26 @@ void trie_longest(const Cedar* da, const uint32_t* s, int64_t size, bool ignore_
 }  // namespace
 
 // ------------------------------- C ABI for ctypes ---------------------------------
+// ACX#match(seq : Array(Char) | Slice(Char), sep) (ac.cr:342-364): the walk is over the characters' bytes, the two
+// neighbour tests look at the neighbouring CHARACTER's code point (`chr.ord < sep.size && !sep[chr.ord]`).  Hits come out
+// in byte offsets here; the caller remaps them (the reference yields character offsets from this overload).
+template <class F>
+inline void match_sep_chars_(const AC* ac, const uint8_t* seq, int64_t n, const Sep& sep, F yield) {
+  std::vector<uint32_t> chars;   // seq as Array(Char)
+  std::vector<int32_t> cob;      // char_of_byte (matcher.cr:24-32)
+  decode_utf8(seq, n, chars);
+  char_map(seq, n, cob);
+  const int64_t n_chars = (int64_t)chars.size();
+  match_(ac, seq, n, [&](int32_t idx, int32_t nid) {
+    const int64_t chr_idx = cob[idx];
+    if (chr_idx + 1 < n_chars && sep.rejects(chars[chr_idx + 1])) return;
+    fetch(ac, idx, nid, [&](Hit h) {
+      if (h.start > 0 && cob[h.start] > 0 && sep.rejects(chars[cob[h.start] - 1])) return;  // (keys are whole characters)
+      yield(h);
+    });
+  });
+}
+
 extern "C" {
 
 void* orc_cedar_new() { return new Cedar(); }
@@ -719,7 +739,7 @@ const int32_t* orc_ac_output(void* a) { return (const int32_t*)((AC*)a)->output.
 const uint32_t* orc_ac_key_lens(void* a) { return ((AC*)a)->key_lens.data(); }
 const Hit* orc_ac_hits(void* a) { return ((AC*)a)->hits.data(); }
 
-enum { ORC_UNITS_CHAR = 1, ORC_SEP = 2, ORC_LONGEST = 4, ORC_INTERSECTABLE = 8 };
+enum { ORC_UNITS_CHAR = 1, ORC_SEP = 2, ORC_LONGEST = 4, ORC_INTERSECTABLE = 8, ORC_SEP_CODEPOINT = 128 };
 
 // ACX#match / match(sep) / match_longest on Bytes, optionally remapped to character
 // offsets like the String overloads (ac.cr:280-340, 297-310; matcher.cr:34-46).
@@ -733,6 +753,8 @@ int64_t orc_ac_scan(void* a, const uint8_t* seq, int64_t n, uint32_t mode, const
     match_longest_(ac, seq, n, (mode & ORC_INTERSECTABLE) != 0, [&](int32_t idx, int32_t nid) {
       fetch_one(ac, idx, nid, [&](Hit h) { out.push_back(h); });
     });
+  } else if ((mode & ORC_SEP) && (mode & ORC_SEP_CODEPOINT)) {
+    match_sep_chars_(ac, seq, n, sep, [&](Hit h) { out.push_back(h); });
   } else if (mode & ORC_SEP) {
     match_(ac, seq, n, [&](int32_t idx, int32_t nid) {
       if ((int64_t)idx + 1 < n && sep.rejects(seq[idx + 1])) return;
@@ -850,6 +872,8 @@ int64_t orc_ac_scan_mode_mt(void* a, const uint8_t* text, const int64_t* doc_off
         match_longest_(ac, seq, n, (mode & ORC_INTERSECTABLE) != 0, [&](int32_t idx, int32_t nid) {
           fetch_one(ac, idx, nid, [&](Hit h) { out.push_back(h); });
         });
+      } else if ((mode & ORC_SEP) && (mode & ORC_SEP_CODEPOINT)) {
+        match_sep_chars_(ac, seq, n, sep, [&](Hit h) { out.push_back(h); });
       } else if (mode & ORC_SEP) {
         match_(ac, seq, n, [&](int32_t idx, int32_t nid) {
           if ((int64_t)idx + 1 < n && sep.rejects(seq[idx + 1])) return;

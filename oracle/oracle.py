@@ -16,7 +16,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "libaha_oracle.so")
 
-UNITS_CHAR, SEP, LONGEST, INTERSECTABLE = 1, 2, 4, 8
+UNITS_CHAR, SEP, LONGEST, INTERSECTABLE, SEP_CODEPOINT = 1, 2, 4, 8, 128
 
 HIT_DTYPE = np.dtype([("start", "<i4"), ("end", "<i4"), ("value", "<i4")])
 
@@ -272,9 +272,13 @@ class AC:
 
     # reference-shaped entry points; str -> character offsets, bytes -> byte offsets
     def match(self, seq, sep=None):
+        if isinstance(seq, (list, tuple)):  # Array(Char) / Slice(Char) (ac.cr:288-295, 342-364)
+            return self.scan("".join(seq), UNITS_CHAR | (SEP_CODEPOINT if sep is not None else 0), sep)
         return self.scan(seq, UNITS_CHAR if isinstance(seq, str) else 0, sep)
 
     def match_longest(self, seq, intersectable=False):
+        if isinstance(seq, (list, tuple)):  # ac.cr:312-319
+            seq = "".join(seq)
         m = LONGEST | (INTERSECTABLE if intersectable else 0) | (UNITS_CHAR if isinstance(seq, str) else 0)
         return self.scan(seq, m)
 

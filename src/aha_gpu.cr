@@ -37,6 +37,7 @@ lib LibAhaB200
   INTERSECTABLE =  8_u32
   TRIE_LONGEST  = 16_u32
   IGNORE_CASE   = 32_u32
+  SEP_CODEPOINT = 128_u32 # Array(Char) / Slice(Char) forms of match(seq, sep): neighbour test on code points (ac.cr:342-364)
 
   fun init = aha_b200_init(devices : Int32*, n : Int32) : Int32
   fun last_error = aha_b200_last_error : UInt8*
@@ -46,6 +47,10 @@ lib LibAhaB200
   fun scan = aha_b200_scan(dfa : Void*, text : UInt8*, doc_off : Int64*, n_docs : Int64, mode : UInt32,
                            sep_bits : UInt8*, sep_size : Int32, out : Hits**) : Int32
   fun hits_free = aha_b200_hits_free(hits : Hits*) : Void
+  # text and results already on the device, no allocation, no host wait (no counterpart in the reference)
+  fun scan_device_noalloc = aha_b200_scan_device_noalloc(dfa : Void*, dev_text : Void*, dev_doc_off : Void*, n_docs : Int64,
+                                                         total_bytes : Int64, dev_hits : Void*, hit_cap : Int64,
+                                                         dev_doc_hit_off : Void*, dev_n_hits : Void*, stream : Void*) : Int32
 end
 
 module Aha
@@ -114,6 +119,23 @@ module Aha
       scan_batch([seq.to_slice], LibAhaB200::UNITS_CHAR, sep) { |_, h| yield h }
     end
 
+    # Array(Char) / Slice(Char) overloads: character offsets (ac.cr:288-295); with `sep` the neighbour test is made on
+    # the neighbouring character's code point (ac.cr:342-364), which the library does under SEP_CODEPOINT
+    def match(seq : Array(Char) | Slice(Char), &block)
+      scan_batch([String.build { |sb| seq.each { |c| sb << c } }.to_slice], LibAhaB200::UNITS_CHAR) { |_, h| yield h }
+    end
+
+    def match(seq : Array(Char) | Slice(Char), sep : BitArray, &block)
+      m = LibAhaB200::UNITS_CHAR | LibAhaB200::SEP_CODEPOINT
+      scan_batch([String.build { |sb| seq.each { |c| sb << c } }.to_slice], m, sep) { |_, h| yield h }
+    end
+
+    # ac.cr:312-319
+    def match_longest(seq : Array(Char) | Slice(Char), intersectable = false, &block)
+      m = LibAhaB200::LONGEST | LibAhaB200::UNITS_CHAR | (intersectable ? LibAhaB200::INTERSECTABLE : 0_u32)
+      scan_batch([String.build { |sb| seq.each { |c| sb << c } }.to_slice], m) { |_, h| yield h }
+    end
+
     # ac.cr:297-310
     def match_longest(seq : Bytes, intersectable = false, &block)
       m = LibAhaB200::LONGEST | (intersectable ? LibAhaB200::INTERSECTABLE : 0_u32)
@@ -160,6 +182,12 @@ module Aha
   end
 
   class CedarX(T)
+    # A trie alone on the GPU (for trie_match_longest / trie_gsub, cedar.cr:1075-1177): the flattener wants the arrays of
+    # a compiled automaton, so the trie goes through ACX.compile(da) (ac.cr:71-112), which leaves the trie itself untouched.
+    def to_gpu : GpuAC
+      ACX(T).compile(self).to_gpu
+    end
+
     # raw views for the flattener: Node(Int32)[array_size], 12 bytes each (cedar.cr:29-36)
     def gpu_nodes : Void*
       @array.as(Void*)

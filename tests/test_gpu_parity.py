@@ -396,6 +396,28 @@ def test_modes_at_config_scale(cfg):
         assert (res.n_hits, got_n, got_h) == (want_n, want_n, want_h), "mode %d sep %r" % (mode, sep)
 
 
+def test_char_array_overloads_and_code_point_sep():
+    """Array(Char) / Slice(Char) overloads (ac.cr:288-295, 312-319, 342-364): character offsets, and with `sep` the
+    neighbour test on the neighbouring character's code point (AHA_SEP_CODEPOINT)."""
+    g = aha_b200.AC.compile(["我", "我是", "是中"])  # spec/ac_spec.cr:36-43
+    assert [(int(h["end"]), int(h["value"])) for h in g.match(list("我是中国人"))] == [(1, 0), (2, 1), (3, 2)]
+    g = aha_b200.AC.compile(["a", "aa"])  # spec/ac_spec.cr:45-54
+    assert [(int(h["end"]), int(h["value"])) for h in g.match(list("a aaa"), sep=[" "])] == [(1, 0)]
+    keys = ["我", "a", "é", "éa", "的的", "ab", "b "]
+    g, o = aha_b200.AC.compile(keys), O.AC.compile(keys)
+    for text in ["我a是", "éa", "a é", "我 a", "aé的的é ab", "é", "", "的的a的的 éa b ", "ÿaÿ þa", "a\u0100a \u00ffa"]:
+        for sep, size in [([" "], 256), ([" ", "é"], 256), ([" "], 0xE9), ([" "], 0x61), ([], 256)]:
+            assert as_tuples(g.scan_batch([text], aha_b200.UNITS_CHAR | aha_b200.SEP_CODEPOINT, sep, size).hits()) == \
+                as_tuples(o.scan(text, aha_b200.UNITS_CHAR | aha_b200.SEP_CODEPOINT, sep, size)), (text, sep, size)
+            assert as_tuples(g.match(list(text), sep=sep)) == as_tuples(o.match(list(text), sep=sep))
+    rng = random.Random(9)
+    alpha = "ab é的我ÿ"
+    big = _utf8_keys(rng, alpha, 300, 4)
+    docs = ["".join(rng.choice(alpha) for _ in range(rng.choice([0, 3, 40, 900]))) for _ in range(200)]
+    check_batch(big, docs, aha_b200.UNITS_CHAR | aha_b200.SEP_CODEPOINT, sep=[" "])
+    check_batch(big, docs, aha_b200.SEP_CODEPOINT, sep=[" ", "é"], sep_size=240)
+
+
 def test_sep_on_the_character_path():
     """ACX#match(seq, sep) with byte offsets runs on the shared-memory character automaton: the vetoes are applied by
     the expansion.  Neighbours across document boundaries never veto; sep sizes below 256 (Q7); dense nested hits."""

@@ -29,6 +29,25 @@ def test_ac_spec_sep():  # spec/ac_spec.cr:25-34, 45-54
     assert ev(m.match("a aaa", sep=[" "])) == [(1, 0)]
 
 
+def test_ac_spec_char_array():  # spec/ac_spec.cr:36-43, 45-54: the Array(Char) overloads
+    m = O.AC.compile(["我", "我是", "是中"])
+    assert ev(m.match(list("我是中国人"))) == [(1, 0), (2, 1), (3, 2)]
+    m = O.AC.compile(["a", "aa"])
+    assert ev(m.match(list("a aaa"), sep=[" "])) == [(1, 0)]
+
+
+def test_ac_char_array_sep_tests_code_points():
+    """ac.cr:342-364 against ac.cr:321-340, derived from the source: the Array(Char) form asks `chr.ord < sep.size`, so a
+    neighbour at or above U+0100 can never veto, while the Bytes / String form sees its UTF-8 bytes (0x80..0xFF < 256,
+    none of them a separator) and vetoes.  A Latin-1 neighbour (U+00E9 < 256) vetoes in both forms."""
+    m = O.AC.compile(["我", "a"])
+    assert sev(m.match(list("我a是"), sep=[" "])) == [(1, 2, 1)]   # 'a' between two CJK characters passes; "我" is vetoed by 'a'
+    assert sev(m.match("我a是", sep=[" "])) == []                   # bytes: every neighbour vetoes
+    assert sev(m.match(list("éa"), sep=[" "])) == []                # U+00E9 in front of 'a' vetoes
+    assert sev(m.match(list("a é"), sep=[" "])) == [(0, 1, 1)]
+    assert sev(m.match(list("我 a"), sep=[" "])) == [(0, 1, 0), (2, 3, 1)]
+
+
 def test_ac_longest_not_intersectable():  # spec/ac_longest_match_spec.cr:5-18, 35-48
     t = O.Cedar()
     assert [t.insert(s) for s in ["Ruby", "ruby", "rub"]] == [0, 1, 2]

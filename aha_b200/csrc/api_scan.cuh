@@ -663,6 +663,17 @@ static int32_t run_fused(ScanParams p, ScanCall& c) {
     AHA_CUDA(cudaEventRecord(ws->ev1, st));
     rc = read_status(c, status, ws->ev1);
     if (rc) return rc;
+#ifdef AHA_B200_PHASES
+    {
+      unsigned long long ph[8], zero[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      cudaMemcpyFromSymbol(ph, g_phase_cycles, sizeof(ph));
+      cudaMemcpyToSymbol(g_phase_cycles, zero, sizeof(zero));
+      double sum = 0;
+      for (int i = 0; i < 5; ++i) sum += (double)ph[i];
+      fprintf(stderr, "phases (share of warp cycles): stage %.3f walk %.3f count %.3f look-back %.3f deliver %.3f  [%.0f Mcycles per warp]\n",
+              ph[0] / sum, ph[1] / sum, ph[2] / sum, ph[3] / sum, ph[4] / sum, sum / ((double)n_warps * 1e6));
+    }
+#endif
     total_hits = ws->h_status->total_hits;
     if (count_only || (int64_t)total_hits <= cap) break;
     if (attempt == 1) return set_err(AHA_ERR_STATE, "hit buffer sizing did not converge");

@@ -20,6 +20,8 @@
 //     kEnd  target is_end? (raw flag bits, cedar.cr:657-660, Q2/Q4) -- drives match_longest
 //     kGoto the edge is a real goto edge (not derived through fail links)
 #pragma once
+#include <chrono>
+#include <cstdio>
 #include <cstdint>
 #include <cstring>
 #include <string>
@@ -128,6 +130,16 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
     *err = "array_size < 256";
     return false;
   }
+#ifdef AHA_FLATTEN_TIMES  // -DAHA_FLATTEN_TIMES: seconds per phase on stderr (tools/blob_stats.py)
+  auto t_last = std::chrono::steady_clock::now();
+  auto lap = [&](const char* what) {
+    auto now = std::chrono::steady_clock::now();
+    fprintf(stderr, "flatten %-28s %.3f s\n", what, std::chrono::duration<double>(now - t_last).count());
+    t_last = now;
+  };
+#else
+  auto lap = [](const char*) {};
+#endif
   // 1. BFS renumbering over the sibling lists (cedar.cr:450-463), same order ACX.compile walks
   std::vector<int32_t> slot_of;              // state -> cedar slot
   std::vector<int32_t> parent;               // state -> parent state
@@ -169,6 +181,7 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
     *err = "too many states";
     return false;
   }
+  lap("1 bfs");
   // 2. byte classes: every byte used as a label is its own class; all others (incl. NUL, Q6) share class 0
   uint8_t classmap[256];
   uint32_t C = 1;
@@ -217,6 +230,7 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
     if (output[id].value >= 0) key_tail[output[id].value] = tail[s];
   }
   out_off[S] = static_cast<uint32_t>(out_val.size());
+  lap("3 facts + output lists");
   // 4. sparse rows: the children of a state are contiguous in BFS numbering
   std::vector<uint64_t> kid_begin(S + 1, S);  // smallest child id, S when the state has no child
   for (uint64_t s = S; s-- > 1;) kid_begin[parent[s]] = s;
@@ -257,6 +271,7 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
     }
     rows[s] = r;
   }
+  lap("4 rows");
   const bool dense = S * static_cast<uint64_t>(C) * 4 <= kDenseMaxBytes;
   // 4a. no dense table: the dense rows of the wide states are completed to closure rows -- an entry without a goto edge
   // takes what the fail chain would find (label field 2 instead of 1; 0 = back to the root).  A wide state then never
@@ -294,6 +309,7 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
       }
     }
   }
+  lap("4a wide closure");
   // 4b. no dense table: renumber, wide states first in BFS order, the others behind them in BFS order.  A wide state's
   // id is then its row in wide[], and the walk reads its edge with one load instead of two (row, then wide entry):
   // the wide states are the shallow ones the walk is in most of the time.
@@ -335,6 +351,7 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
     fail_state.swap(fail2);
     depth.swap(depth2);
   }
+  lap("4b renumber");
   // 5. layout
   BlobHeader h;
   memset(&h, 0, sizeof(h));
@@ -376,6 +393,7 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
   memcpy(p + h.off_rows, rows.data(), S * sizeof(SparseRow));
   if (!wide.empty()) memcpy(p + h.off_wide, wide.data(), wide.size() * 4);
   if (!wide_fail.empty()) memcpy(p + h.off_wide_fail, wide_fail.data(), wide_fail.size() * 4);
+  lap("5 layout + copies");
   // 6. dense closure in BFS order (small automata only): fail targets are shallower, hence already complete
   if (dense) {
     uint32_t* delta = reinterpret_cast<uint32_t*>(p + h.off_delta);

@@ -325,6 +325,18 @@ __device__ __forceinline__ unsigned long long tile_exclusive_prefix(const FusedP
   return resolve_prefix(P, t, lane);
 }
 
+// -DAHA_B200_PHASES: cycles per phase of scan_fused_kernel summed over warps (printed by run_fused to stderr)
+#ifdef AHA_B200_PHASES
+__device__ unsigned long long g_phase_cycles[8];
+#define AHA_PHASE_DECL long long ph_t = clock64(); unsigned long long ph_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#define AHA_PHASE(i) { const long long ph_n = clock64(); ph_acc[i] += (unsigned long long)(ph_n - ph_t); ph_t = ph_n; }
+#define AHA_PHASE_FLUSH if (lane == 0) { for (int ph_i = 0; ph_i < 8; ++ph_i) atomicAdd(&g_phase_cycles[ph_i], ph_acc[ph_i]); }
+#else
+#define AHA_PHASE_DECL
+#define AHA_PHASE(i)
+#define AHA_PHASE_FLUSH
+#endif
+
 template <class Policy, bool EV>
 __global__ void __launch_bounds__(kByteWarps * 32, 1) scan_fused_kernel(const FusedParams P, const Policy policy_in) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -346,6 +358,7 @@ __global__ void __launch_bounds__(kByteWarps * 32, 1) scan_fused_kernel(const Fu
   aha_hit* my_rec = P.scratch + (gwarp * 32 + lane) * kLaneCap;
   int2* my_mark = P.marks + (gwarp * 32 + lane) * kMarkCap;
   uint32_t parity = 0;
+  AHA_PHASE_DECL
 
   for (;;) {
     unsigned int t = 0;
@@ -370,6 +383,7 @@ __global__ void __launch_bounds__(kByteWarps * 32, 1) scan_fused_kernel(const Fu
       parity ^= 1u;
     }
     __syncwarp();
+    AHA_PHASE(0)  // ticket + staging
 
     const int64_t a = min(tile_start + (int64_t)lane * P.chunk, tile_end);
     const int64_t b = min(a + (int64_t)P.chunk, tile_end);
@@ -398,6 +412,8 @@ __global__ void __launch_bounds__(kByteWarps * 32, 1) scan_fused_kernel(const Fu
       es.ev = my_ev;
       es.mark = my_mark;
       policy.walk(P, sbuf, origin, a, b, lead0, es);
+      __syncwarp();
+      AHA_PHASE(1)  // walk
       const uint32_t ne = es.n, nm = es.n_mark;
       const bool any_over = __any_sync(0xffffffffu, ne > (uint32_t)kByteEvCap || nm > (uint32_t)kMarkCap);
       uint32_t n_lane = 0;
@@ -426,7 +442,9 @@ __global__ void __launch_bounds__(kByteWarps * 32, 1) scan_fused_kernel(const Fu
       }
       const uint32_t excl_lane = incl - n_lane;
       const uint32_t T = __shfl_sync(0xffffffffu, incl, 31);
+      AHA_PHASE(2)  // count
       const unsigned long long prefix = tile_exclusive_prefix(P, t, T, lane);
+      AHA_PHASE(3)  // look-back
       if ((int64_t)t == P.n_tiles - 1 && lane == 0) *P.total_hits = prefix + T;
       if (!any_over) {
         // every lane expands its own events to their final positions (a lane's hits are consecutive in the stream)
@@ -535,7 +553,9 @@ __global__ void __launch_bounds__(kByteWarps * 32, 1) scan_fused_kernel(const Fu
     }
     __syncwarp();
     fence_proxy_async();  // reads of sbuf are done before the next bulk copy overwrites it
+    AHA_PHASE(4)  // expansion / delivery
   }
+  AHA_PHASE_FLUSH
 }
 
 // documents that start at the very end of the text (trailing empty documents and the n_docs sentinel)

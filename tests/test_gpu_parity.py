@@ -418,6 +418,15 @@ def test_char_array_overloads_and_code_point_sep():
     check_batch(big, docs, aha_b200.SEP_CODEPOINT, sep=[" ", "é"], sep_size=240)
 
 
+def test_deeply_nested_keys_on_constant_text():
+    """700 nested keys a, aa, ..., a^700 over a^n: every position ends up to 700 keys, a lane of a tile that goes through
+    the direct pass counts far more than 65 535 hits (tile_meta holds a full 32-bit count per lane for such tiles)."""
+    keys = ["a" * k for k in range(1, 701)]
+    res = check_batch(keys, ["a" * 9000, "", "a" * 3, "的" + "a" * 2500])
+    assert res.n_hits > 6_000_000
+    check_batch(keys, ["a" * 5000], aha_b200.UNITS_CHAR)
+
+
 def test_sep_on_the_character_path():
     """ACX#match(seq, sep) with byte offsets runs on the shared-memory character automaton: the vetoes are applied by
     the expansion.  Neighbours across document boundaries never veto; sep sizes below 256 (Q7); dense nested hits."""

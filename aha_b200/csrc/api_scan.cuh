@@ -1089,7 +1089,13 @@ int32_t aha_b200_scan(const aha_dfa* d, const uint8_t* text, const int64_t* doc_
   // runs of whole documents
   S.cut.assign(1, 0);
   {
-    const int64_t target = (int64_t)knobs().e2e_chunk_mb << 20;
+    int64_t target = (int64_t)knobs().e2e_chunk_mb << 20;
+    // the trie-longest machine is one thread per document: a run must hold enough documents to fill the device
+    // (a 64 MB run of 4 KiB documents is 16 k threads on a GPU that holds 300 k)
+    if ((mode & AHA_TRIE_LONGEST) && n_docs > 0 && knobs().e2e_chunk_mb >= 16) {
+      const int64_t avg = std::max<int64_t>(1, doc_off[n_docs] / n_docs);
+      target = std::min<int64_t>(std::max<int64_t>(target, avg * ((int64_t)1 << 18)), (int64_t)2 << 30);
+    }
     int64_t start = 0;
     for (int64_t i = 0; i < n_docs; ++i) {
       if (doc_off[i + 1] - doc_off[start] >= target) {

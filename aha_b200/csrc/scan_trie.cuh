@@ -77,6 +77,7 @@ __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams 
   const bool use_sep = (p.mode & AHA_SEP) != 0;
   const uint32_t C = p.C;
   uint64_t run = EMIT ? p.offsets[d] : 0;
+  (void)C;
   // jump(chr, from): walk the character's UTF-8 bytes over goto edges only; -1 == no path, else the table entry of the
   // last edge (target state | flags: kOut tells whether the target has an output list, so out_off[] is only read then)
   auto jump = [&](uint32_t cp, uint32_t from) -> int64_t {
@@ -93,94 +94,105 @@ __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams 
     }
     return (int64_t)e;
   };
-  uint32_t node[kTrieMaxChars + 1];
-  int32_t bpos[kTrieMaxChars + 1];
-  uint8_t var[kTrieMaxChars + 1];
+  // ONE loop, one micro-step per iteration, so that the 32 documents of a warp stay in step (the nested loops of the
+  // reference -- skip separators / depth-first walk / skip the rest of the token -- ran with 6.7 of 32 lanes active):
+  //   phase 0  top of the reference loop: skip separators; the first other character starts a walk in the same iteration
+  //   phase 1  one step of the depth-first walk: the character at c_bpos, its exact edge and its case-swapped edge
+  //   phase 2  no key started here: on to the next separator
+  // The walk keeps no per-level arrays: when the swapped edge of a level exists it is pushed as a pending branch (entry,
+  // position, depth) and popped when the exact branch is exhausted -- last in, first out, i.e. depth-first preorder, the
+  // order of the reference's frontier (cedar.cr:993-1019); with mixed-case keys a pending branch is rare, so the
+  // stack is almost never touched.
+  uint2 stk[kTrieMaxChars];  // x = table entry of the branch's first edge, y = (byte offset behind its character - pos) | depth << 16
+  int sp = 0;
   int64_t pos = 0;
   int32_t cidx = 0;
-  uint32_t cp;
-  while (pos < n) {
-    if (use_sep) {
-      while (pos < n) {
-        const int l = utf8_decode(s, pos, n, &cp);
-        if (!is_sep(p, cp)) break;
+  int phase = 0, depth = 0;
+  uint32_t c_node = 0;
+  int64_t c_bpos = 0;
+  int32_t best_n = 0, best_v = 0, best_bytes = 0;
+  while (phase != 3) {
+    const int64_t cur = phase == 1 ? c_bpos : pos;
+    const bool have = cur < n;
+    uint32_t cp = 0;
+    int l = 1;
+    if (have) l = utf8_decode(s, cur, n, &cp);
+    if (phase == 2) {
+      if (!have) { phase = 3; continue; }
+      if (is_sep(p, cp)) phase = 0;  // ... and consumed like any separator at the top of the loop
+      pos += l;
+      ++cidx;
+      continue;
+    }
+    if (phase == 0) {
+      if (!have) { phase = 3; continue; }
+      if (use_sep && is_sep(p, cp)) {
         pos += l;
         ++cidx;
-      }
-    }
-    int32_t best_n = 0, best_v = 0, best_bytes = 0;
-    // depth-first walk; the level being tried lives in registers (c_*), the arrays only hold the levels above it:
-    // they are written on the way down and read on the way back, not at every candidate
-    int depth = 0;
-    uint32_t c_node = 0, c_var = 0;
-    int32_t c_bpos = (int32_t)pos;
-    while (depth >= 0) {
-      if (c_var >= 2 || c_bpos >= n || depth >= kTrieMaxChars) {
-        if (--depth >= 0) {
-          c_node = node[depth];
-          c_bpos = bpos[depth];
-          c_var = var[depth];
-        }
         continue;
       }
-      const int l = utf8_decode(s, c_bpos, n, &cp);
-      const uint32_t v = c_var++;
-      uint32_t cc = cp;
-      if (v == 1) {
-        if (!icase) { c_var = 2; continue; }
-        cc = cp_other(cp);
-        if (cc == cp) continue;
-      }
-      const int64_t je = jump(cc, c_node);
-      if (je < 0) continue;
-      const uint32_t nn = (uint32_t)je & kStateMask;
-      if (((uint32_t)je & kOut) && depth + 1 > best_n) {
-        const uint32_t j = p.out_off[nn];
-        bool ok = true;
-        if (use_sep) {
-          const int64_t after = c_bpos + l;
-          if (after < n) {
-            uint32_t ncp;
-            utf8_decode(s, after, n, &ncp);
-            ok = is_sep(p, ncp);
-          }
-        }
-        if (ok) {
-          best_n = depth + 1;
-          best_v = p.out_val[j];
-          best_bytes = c_bpos + l - (int32_t)pos;
-        }
-      }
-      node[depth] = c_node;
-      bpos[depth] = c_bpos;
-      var[depth] = (uint8_t)c_var;
-      c_node = nn;
-      c_bpos += l;
-      c_var = 0;
-      ++depth;
+      phase = 1;  // a walk starts at this character (this iteration is its first step)
+      depth = 0;
+      c_node = 0;
+      c_bpos = pos;
+      sp = 0;
+      best_n = 0;
     }
-    if (best_n == 0) {
-      if (pos < n) {
-        pos += utf8_decode(s, pos, n, &cp);
-        ++cidx;
+    int64_t e0 = -1, e1 = -1;
+    if (have && depth < kTrieMaxChars) {
+      e0 = jump(cp, c_node);
+      if (icase) {
+        const uint32_t cc = cp_other(cp);  // chr.uppercase? ? chr.downcase : chr.upcase (cedar.cr:995-996)
+        if (cc != cp) e1 = jump(cc, c_node);
       }
-      if (use_sep) {
-        while (pos < n) {
-          const int l = utf8_decode(s, pos, n, &cp);
-          if (is_sep(p, cp)) break;
-          pos += l;
+    }
+    if (e1 >= 0) stk[sp++] = make_uint2((uint32_t)e1, (uint32_t)(c_bpos + l - pos) | ((uint32_t)(depth + 1) << 16));
+    uint32_t arrived;
+    if (e0 >= 0) {
+      arrived = (uint32_t)e0;
+      c_bpos += l;
+      ++depth;
+    } else if (sp > 0) {
+      const uint2 t = stk[--sp];
+      arrived = t.x;
+      c_bpos = pos + (int64_t)(t.y & 0xFFFFu);
+      depth = (int)(t.y >> 16);
+    } else {
+      // every branch from this start is exhausted: the strictly longest candidate, first in preorder, wins
+      if (best_n == 0) {
+        if (pos < n) {
+          uint32_t skip;
+          pos += utf8_decode(s, pos, n, &skip);
           ++cidx;
         }
+        phase = use_sep ? 2 : 0;
+      } else {
+        if (EMIT) {
+          if (p.hits) p.hits[run] = aha_hit{cidx, cidx + best_n, best_v};
+        } else if ((int64_t)run < sc_cap) {
+          p.doc_scratch[sc_base + (int64_t)run] = aha_hit{cidx, cidx + best_n, best_v};
+        }
+        ++run;
+        pos += best_bytes;
+        cidx += best_n;
+        phase = 0;
       }
-    } else {
-      if (EMIT) {
-        if (p.hits) p.hits[run] = aha_hit{cidx, cidx + best_n, best_v};
-      } else if ((int64_t)run < sc_cap) {
-        p.doc_scratch[sc_base + (int64_t)run] = aha_hit{cidx, cidx + best_n, best_v};
+      continue;
+    }
+    // arrival at a node `depth` characters deep, the text cursor behind its last character
+    c_node = arrived & kStateMask;
+    if ((arrived & kOut) && depth > best_n) {
+      bool ok = true;
+      if (use_sep && c_bpos < n) {
+        uint32_t ncp;
+        utf8_decode(s, c_bpos, n, &ncp);
+        ok = is_sep(p, ncp);
       }
-      ++run;
-      pos += best_bytes;
-      cidx += best_n;
+      if (ok) {
+        best_n = depth;
+        best_v = p.out_val[p.out_off[c_node]];
+        best_bytes = (int32_t)(c_bpos - pos);
+      }
     }
   }
   if (!EMIT) p.counts[d] = (uint32_t)run;

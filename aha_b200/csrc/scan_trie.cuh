@@ -62,10 +62,20 @@ __device__ __forceinline__ uint32_t trie_goto(const ScanParams& p, const uint8_t
 template <bool EMIT>
 __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams p) {
   __shared__ uint8_t cmap[256];
+  __shared__ uint32_t s_sep[8];  // is_sep? as one bit test: the BitArray with the bits at or above sep.size cleared
   for (int i = threadIdx.x; i < 256; i += blockDim.x) cmap[i] = p.classmap[i];
+  if (threadIdx.x < 8) {
+    uint32_t w = p.sep_bits[threadIdx.x];
+    const uint32_t lo = threadIdx.x * 32u;
+    if (p.sep_size <= lo) w = 0u;
+    else if (p.sep_size < lo + 32u) w &= (1u << (p.sep_size - lo)) - 1u;
+    s_sep[threadIdx.x] = w;
+  }
   __syncthreads();
   const int64_t d = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (d >= p.n_docs) return;
+  auto sep_at = [&](uint32_t chr) -> bool { return chr < 256u && ((s_sep[chr >> 5] >> (chr & 31u)) & 1u); };  // cedar.cr:1067-1069
+  const uint32_t* const delta = p.delta;  // dense goto table when the automaton has one (32-bit index: it is <= 128 MB)
   const uint8_t* s = p.text + p.doc_off[d];
   const int64_t n = p.doc_off[d + 1] - p.doc_off[d];
   // The count pass also records: a document keeps one scratch slot per four bytes of text, which holds every hit
@@ -77,12 +87,11 @@ __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams 
   const bool use_sep = (p.mode & AHA_SEP) != 0;
   const uint32_t C = p.C;
   uint64_t run = EMIT ? p.offsets[d] : 0;
-  (void)C;
   // jump(chr, from): walk the character's UTF-8 bytes over goto edges only; -1 == no path, else the table entry of the
   // last edge (target state | flags: kOut tells whether the target has an output list, so out_off[] is only read then)
   auto jump = [&](uint32_t cp, uint32_t from) -> int64_t {
     if (cp < 0x80) {  // one byte, one edge
-      const uint32_t e = trie_goto(p, cmap, from, cp);
+      const uint32_t e = delta ? __ldg(delta + (from * C + cmap[cp])) : trie_goto(p, cmap, from, cp);
       return (!(e & kGoto) || cp == 0) ? -1 : (int64_t)e;
     }
     uint8_t buf[4];
@@ -113,20 +122,28 @@ __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams 
   int32_t best_n = 0, best_v = 0, best_bytes = 0;
   while (phase != 3) {
     const int64_t cur = phase == 1 ? c_bpos : pos;
-    const bool have = cur < n;
+    bool have = cur < n;
     uint32_t cp = 0;
     int l = 1;
     if (have) l = utf8_decode(s, cur, n, &cp);
     if (phase == 2) {
-      if (!have) { phase = 3; continue; }
-      if (is_sep(p, cp)) phase = 0;  // ... and consumed like any separator at the top of the loop
-      pos += l;
-      ++cidx;
+      // up to eight characters per iteration: a walk step of the neighbouring lanes waits for two table lookups, the
+      // skipping costs a byte load from L1 each
+      for (int k = 0;;) {
+        if (!have) { phase = 3; break; }
+        const bool at_sep = sep_at(cp);
+        pos += l;
+        ++cidx;
+        if (at_sep) { phase = 0; break; }  // ... consumed like any separator at the top of the loop
+        if (++k == 8) break;
+        have = pos < n;
+        if (have) l = utf8_decode(s, pos, n, &cp);
+      }
       continue;
     }
     if (phase == 0) {
       if (!have) { phase = 3; continue; }
-      if (use_sep && is_sep(p, cp)) {
+      if (use_sep && sep_at(cp)) {
         pos += l;
         ++cidx;
         continue;
@@ -186,7 +203,7 @@ __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams 
       if (use_sep && c_bpos < n) {
         uint32_t ncp;
         utf8_decode(s, c_bpos, n, &ncp);
-        ok = is_sep(p, ncp);
+        ok = sep_at(ncp);
       }
       if (ok) {
         best_n = depth;

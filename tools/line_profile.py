@@ -7,8 +7,11 @@ src_csv, fn = sys.argv[1], sys.argv[2]
 top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
 d = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath("aha_b200/libaha_b200.so")], cwd=d, capture_output=True)
-cub = [f for f in os.listdir(d) if f.endswith(".cubin")][0]
-txt = subprocess.run(["nvdisasm", "--print-line-info", os.path.join(d, cub)], capture_output=True, text=True).stdout.splitlines()
+txt = []
+for cub in sorted(f for f in os.listdir(d) if f.endswith(".cubin")):  # one cubin per translation unit
+    t = subprocess.run(["nvdisasm", "--print-line-info", os.path.join(d, cub)], capture_output=True, text=True).stdout.splitlines()
+    if any(l.startswith(".text." + fn + ":") for l in t):
+        txt = t
 # find the function's text section
 start = max(i for i, l in enumerate(txt) if l.startswith(".text." + fn + ":"))
 lines, cur = [], None

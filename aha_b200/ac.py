@@ -92,6 +92,10 @@ class Cedar:
         return self._ac
 
     def match_longest_batch(self, docs, ignore_case=False, sep=None):
+        if sep is not None and any((ord(c) if isinstance(c, str) else int(c)) >= 256 for c in sep):
+            # cedar.cr:1071-1073 takes any Array(Char); the kernel's separator set is 256 bits: refuse instead of
+            # silently ignoring the character
+            raise AhaError(-1, "CedarX#match_longest on the GPU: separators must be code points below U+0100")
         self.to_gpu()
         return self._ac.scan_batch(docs, TRIE_LONGEST | (IGNORE_CASE if ignore_case else 0), sep)
 

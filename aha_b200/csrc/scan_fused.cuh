@@ -22,7 +22,10 @@
 namespace aha {
 
 constexpr int kLaneCap = 32;      // scratch records per lane per tile (record mode: sep scans)
-constexpr int kByteEvCap = 64;        // events (end position, state) per lane per tile (event mode: everything else)
+#ifndef AHA_BYTE_EVCAP
+#define AHA_BYTE_EVCAP 64
+#endif
+constexpr int kByteEvCap = AHA_BYTE_EVCAP;  // events (end position, state) per lane per tile (event mode: everything else)
 constexpr int kMarkCap = 4;       // document-start markers per lane per tile
 constexpr int kMarkCapC = 2;      // ... per sub-chunk (scan_char.cuh walks two sub-chunks per lane)
 #ifndef AHA_B200_CHAR_WARPS

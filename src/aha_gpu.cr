@@ -153,6 +153,14 @@ module Aha
       scan_batch([seq.to_slice], m, sep) { |_, h| yield h }
     end
 
+    # sep : Array(Char) (cedar.cr:1071-1073): the kernel's separator set has 256 bits, wider characters are refused
+    def trie_match_longest(seq : String, ignore_case : Bool, sep : Array(Char) | Slice(Char), &block)
+      raise "aha_gpu: separators must be code points below U+0100" if sep.any? { |c| c.ord >= 256 }
+      bits = BitArray.new(256)
+      sep.each { |c| bits[c.ord] = true }
+      trie_match_longest(seq, ignore_case, bits) { |h| yield h }
+    end
+
     # CedarX#gsub(String, ignore_case, sep) { |hit| replacement } (cedar.cr:1123-1177): the reference loop is the
     # match_longest loop with `sb <<` on every branch, so the string is rebuilt from the GPU's hit stream.
     def trie_gsub(seq : String, ignore_case = false, sep : BitArray? = nil, &block)

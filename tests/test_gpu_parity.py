@@ -208,6 +208,13 @@ def test_cedar_match_longest_spec_vectors():  # spec/cedar_match_spec.cr:4-30, 5
     assert got == [(0, 4, "Ruby"), (20, 24, "ruby")]
 
 
+def test_cedar_wide_separator_is_refused():
+    t = aha_b200.Cedar()
+    t.insert("ruby")
+    with pytest.raises(aha_b200.AhaError):
+        t.match_longest("ruby，ruby", sep=["，"])  # cedar.cr:1071-1073 would accept it; a 256-bit set cannot hold it
+
+
 def test_cedar_gsub_spec_vectors():  # spec/cedar_match_spec.cr:32-49, 65-81
     t = _trie3()
     names = {"ruby": "crystal", "Ruby": "Crystal"}

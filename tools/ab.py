@@ -28,17 +28,21 @@ def main():
             print("build", tag, flags, flush=True)
             _lib.build(out=so(tag), extra_flags=flags)
         return
-    workload, reps = "c2", 2
+    workload, reps, nbytes, steps = "c2", 2, "0", "20"
     while args and args[0].startswith("--"):
         if args[0] == "--workload":
             workload = args[1]
         elif args[0] == "--reps":
             reps = int(args[1])
+        elif args[0] == "--bytes":
+            nbytes = args[1]
+        elif args[0] == "--steps":
+            steps = args[1]
         args = args[2:]
     for rep in range(reps):
         for tag in args:
             env = dict(os.environ, AHA_B200_SO=so(tag))
-            out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--workload", workload, "--steps", "20", "--warmup", "3",
+            out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--workload", workload, "--bytes", nbytes, "--steps", steps, "--warmup", "3",
                                   "--no-cpu", "--e2e-steps", "0"], env=env, capture_output=True, text=True)
             try:
                 d = json.loads(out.stdout.strip().splitlines()[-1])

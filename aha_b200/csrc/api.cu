@@ -168,6 +168,7 @@ static void free_dfa(aha_dfa* d) {
     dd.idle.clear();  // workspaces (their destructor frees on dd.device)
     if (dd.blob) cudaFree(dd.blob);
     if (dd.hot.dev) cudaFree(dd.hot.dev);
+    if (dd.folded_dev) cudaFree(dd.folded_dev);
   }
   delete d;
 }

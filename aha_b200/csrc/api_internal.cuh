@@ -11,6 +11,7 @@
 
 #include "../../include/aha_b200.h"
 #include "dfa.hpp"
+#include "folded_trie.hpp"
 #include "host_cedar.hpp"
 
 namespace aha {
@@ -153,6 +154,11 @@ struct DeviceDfa {
   // scan workspaces that are not in use (guarded by pool_mu of the owning aha_dfa)
   std::vector<std::unique_ptr<Workspace>> idle;
   double hits_per_byte = -1.0;  // largest hit density seen so far on this device: sizes the hit buffer up front
+  // case-folded trie of the dictionary (folded_trie.hpp): built and uploaded at the first ignore_case scan
+  int folded_state = 0;         // 0 = not tried yet, 1 = on the device, -1 = the dictionary does not qualify
+  uint8_t* folded_dev = nullptr;  // one allocation: fdelta | fcand_off | fcand | fcmap
+  size_t off_fcand_off = 0, off_fcand = 0, off_fcmap = 0;
+  uint32_t folded_classes = 0;
 };
 
 // Result buffers (hits, doc_hit_off) are handed to the caller and come back through aha_b200_hits_free: they are

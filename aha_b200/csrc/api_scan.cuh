@@ -262,6 +262,47 @@ static int32_t lead_prepass(ScanCall& c, ScanParams& p, int32_t tile, int64_t n_
   return AHA_OK;
 }
 
+// case-folded trie of the dictionary on this device (folded_trie.hpp): built from the host blob and uploaded at the first
+// ignore_case scan; a dictionary that does not qualify keeps the depth-first kernel
+static bool ensure_folded(const aha_dfa* d, DeviceDfa* dd) {
+  std::lock_guard<std::mutex> lk(d->pool_mu);
+  if (dd->folded_state != 0) return dd->folded_state > 0;
+  dd->folded_state = -1;
+  FoldedTrieHost F = build_folded_trie(d->header, d->blob.data());
+  if (!F.ok) return false;
+  auto place = [](size_t& cursor, size_t bytes) { size_t at = cursor; cursor = (cursor + bytes + 255) & ~size_t(255); return at; };
+  size_t cursor = 0;
+  const size_t off_delta = place(cursor, F.delta.size() * 4);
+  dd->off_fcand_off = place(cursor, F.cand_off.size() * 4);
+  dd->off_fcand = place(cursor, (F.cand.size() + 1) * 16);
+  dd->off_fcmap = place(cursor, 256);
+  std::vector<uint8_t> img(cursor, 0);
+  memcpy(img.data() + off_delta, F.delta.data(), F.delta.size() * 4);
+  memcpy(img.data() + dd->off_fcand_off, F.cand_off.data(), F.cand_off.size() * 4);
+  uint32_t* c = reinterpret_cast<uint32_t*>(img.data() + dd->off_fcand);
+  for (size_t i = 0; i < F.cand.size(); ++i) {
+    c[4 * i] = (uint32_t)F.cand[i].value;
+    c[4 * i + 1] = F.cand[i].n_chars;
+    c[4 * i + 2] = (uint32_t)F.cand[i].mask;
+    c[4 * i + 3] = (uint32_t)(F.cand[i].mask >> 32);
+  }
+  memcpy(img.data() + dd->off_fcmap, F.cmap, 256);
+  if (cudaMalloc(&dd->folded_dev, img.size()) != cudaSuccess) {
+    cudaGetLastError();
+    dd->folded_dev = nullptr;
+    return false;
+  }
+  if (cudaMemcpy(dd->folded_dev, img.data(), img.size(), cudaMemcpyHostToDevice) != cudaSuccess) {
+    cudaGetLastError();
+    cudaFree(dd->folded_dev);
+    dd->folded_dev = nullptr;
+    return false;
+  }
+  dd->folded_classes = F.n_classes;
+  dd->folded_state = 1;
+  return true;
+}
+
 // per-document machines (match_longest, trie longest) and the two-pass checker: count -> exclusive sum -> emit
 static int32_t run_v1(ScanParams p, ScanCall& c) {
   cudaStream_t st = c.st;
@@ -303,9 +344,20 @@ static int32_t run_v1(ScanParams p, ScanCall& c) {
     if (rc) return rc;
     p.lead_prefix = lead_prefix;
   }
+  // ignore_case: the case-folded trie (one lookup per character) when the dictionary qualifies; knob 1 keeps the
+  // depth-first walk with the frontier
+  const bool folded = trie && (p.mode & AHA_IGNORE_CASE) && !knobs().force_v1 && ensure_folded(c.dfa, c.dd);
+  if (folded) {
+    p.fdelta = reinterpret_cast<const uint32_t*>(c.dd->folded_dev);
+    p.fcand_off = reinterpret_cast<const uint32_t*>(c.dd->folded_dev + c.dd->off_fcand_off);
+    p.fcand = reinterpret_cast<const uint4*>(c.dd->folded_dev + c.dd->off_fcand);
+    p.fcmap = c.dd->folded_dev + c.dd->off_fcmap;
+    p.fC = c.dd->folded_classes;
+  }
   const unsigned grid = (unsigned)((units + tpb - 1) / tpb);
   if (units > 0) {
-    if (trie) trie_longest_doc_kernel<false><<<grid, tpb, 0, st>>>(p);
+    if (folded) trie_folded_doc_kernel<false><<<grid, tpb, 0, st>>>(p);
+    else if (trie) trie_longest_doc_kernel<false><<<grid, tpb, 0, st>>>(p);
     else if (longest) longest_doc_kernel<false><<<grid, tpb, 0, st>>>(p);
     else scan_v1_kernel<false><<<grid, tpb, 0, st>>>(p);
     count_launch();
@@ -328,7 +380,8 @@ static int32_t run_v1(ScanParams p, ScanCall& c) {
         trie_compact_kernel<<<(unsigned)((p.n_docs + 7) / 8), 256, 0, st>>>(p);
         count_launch();
       }
-      if (trie) trie_longest_doc_kernel<true><<<grid, tpb, 0, st>>>(p);  // with a scratch: only documents that overflowed it
+      if (folded) trie_folded_doc_kernel<true><<<grid, tpb, 0, st>>>(p);
+      else if (trie) trie_longest_doc_kernel<true><<<grid, tpb, 0, st>>>(p);  // with a scratch: only documents that overflowed it
       else longest_doc_kernel<true><<<grid, tpb, 0, st>>>(p);
       count_launch();
       offsets_to_doc_hit_off<<<(unsigned)((p.n_docs + 1 + 255) / 256), 256, 0, st>>>(offsets, p.n_docs, p.doc_hit_off);

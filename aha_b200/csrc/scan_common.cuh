@@ -39,6 +39,12 @@ struct ScanParams {
   const uint64_t* lead_prefix;   // [n_chunks + 1] non-continuation bytes before each chunk (AHA_UNITS_CHAR)
   const uint64_t* doc_lead_base; // [n_docs + 1]  non-continuation bytes before each document
   aha_hit* doc_scratch;          // trie path: hits of document d at [doc_off[d] / 4, doc_off[d + 1] / 4) during the count pass
+  // case-folded trie (folded_trie.hpp), ignore_case scans of the trie path; fdelta == NULL: not available
+  const uint32_t* fdelta;        // [n_fstates][fC]: target | kFoldCand, 0 = no edge
+  const uint8_t* fcmap;          // [256] classes of the folded bytes
+  const uint32_t* fcand_off;     // [n_fstates + 1]
+  const uint4* fcand;            // {value, characters, mask low, mask high}
+  uint32_t fC;
 };
 
 // "chr < sep.size && !sep[chr]" (ac.cr:326,333): neighbour byte vetoes the hit

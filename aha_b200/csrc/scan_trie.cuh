@@ -9,6 +9,7 @@
 // Offsets are character indices.  Characters are decoded structurally (lead byte -> length), mapped,
 // re-encoded and walked byte by byte like CedarX#jump(Char) (cedar.cr:946-952).
 #pragma once
+#include "folded_trie.hpp"
 #include "scan_common.cuh"
 
 namespace aha {
@@ -208,6 +209,145 @@ __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams 
       if (ok) {
         best_n = depth;
         best_v = p.out_val[p.out_off[c_node]];
+        best_bytes = (int32_t)(c_bpos - pos);
+      }
+    }
+  }
+  if (!EMIT) p.counts[d] = (uint32_t)run;
+}
+
+// ---- ignore_case over the case-folded trie (folded_trie.hpp): one lookup per character, no frontier ------------------
+// Same flat state machine and the same count / record / compact / emit scheme as trie_longest_doc_kernel.  A walk step
+// folds the text character, follows ONE edge of the folded trie and shifts the character's case into the window mask;
+// a node with candidates settles which original key the reference's frontier would have reached first.
+template <bool EMIT>
+__global__ void __launch_bounds__(128) trie_folded_doc_kernel(const ScanParams p) {
+  __shared__ uint8_t fcmap[256];
+  __shared__ uint32_t s_sep[8];
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) fcmap[i] = p.fcmap[i];
+  if (threadIdx.x < 8) {
+    uint32_t w = p.sep_bits[threadIdx.x];
+    const uint32_t lo = threadIdx.x * 32u;
+    if (p.sep_size <= lo) w = 0u;
+    else if (p.sep_size < lo + 32u) w &= (1u << (p.sep_size - lo)) - 1u;
+    s_sep[threadIdx.x] = w;
+  }
+  __syncthreads();
+  const int64_t d = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= p.n_docs) return;
+  auto sep_at = [&](uint32_t chr) -> bool { return chr < 256u && ((s_sep[chr >> 5] >> (chr & 31u)) & 1u); };
+  const uint8_t* s = p.text + p.doc_off[d];
+  const int64_t n = p.doc_off[d + 1] - p.doc_off[d];
+  const int64_t sc_base = p.doc_off[d] >> 2, sc_cap = p.doc_scratch ? (p.doc_off[d + 1] >> 2) - sc_base : 0;
+  if (EMIT && p.doc_scratch && (int64_t)p.counts[d] <= sc_cap) return;
+  const bool use_sep = (p.mode & AHA_SEP) != 0;
+  const uint32_t* const fdelta = p.fdelta;
+  const uint32_t fC = p.fC;
+  uint64_t run = EMIT ? p.offsets[d] : 0;
+  int64_t pos = 0, c_bpos = 0;
+  int32_t cidx = 0;
+  int phase = 0, depth = 0;
+  uint32_t node = 0;
+  uint64_t tmask = 0;  // bit j = the character j places behind the cursor is upper case
+  int32_t best_n = 0, best_v = 0, best_bytes = 0;
+  while (phase != 3) {
+    const int64_t cur = phase == 1 ? c_bpos : pos;
+    bool have = cur < n;
+    uint32_t cp = 0;
+    int l = 1;
+    if (have) l = utf8_decode(s, cur, n, &cp);
+    if (phase == 2) {
+      for (int k = 0;;) {
+        if (!have) { phase = 3; break; }
+        const bool at_sep = sep_at(cp);
+        pos += l;
+        ++cidx;
+        if (at_sep) { phase = 0; break; }
+        if (++k == 8) break;
+        have = pos < n;
+        if (have) l = utf8_decode(s, pos, n, &cp);
+      }
+      continue;
+    }
+    if (phase == 0) {
+      if (!have) { phase = 3; continue; }
+      if (use_sep && sep_at(cp)) {
+        pos += l;
+        ++cidx;
+        continue;
+      }
+      phase = 1;
+      depth = 0;
+      node = 0;
+      c_bpos = pos;
+      tmask = 0;
+      best_n = 0;
+    }
+    // one step: the folded character's edge (a multi-byte character walks its bytes)
+    uint32_t e = 0;
+    bool upper = false;
+    if (have && depth < 64) {
+      upper = cp_upper(cp);
+      const uint32_t fc = upper ? cp + 32u : cp;
+      if (fc < 0x80u) {
+        e = fc ? __ldg(fdelta + (node * fC + fcmap[fc])) : 0u;
+      } else {
+        uint8_t buf[4];
+        const int k = utf8_encode(fc, buf);
+        e = node;
+        for (int j = 0; j < k; ++j) {
+          e = __ldg(fdelta + ((e & ~kFoldCand) * fC + fcmap[buf[j]]));
+          if (e == 0u) break;
+        }
+      }
+    }
+    if (e == 0u) {
+      // the walk from this start is over: the deepest candidate that passed the separator test wins
+      if (best_n == 0) {
+        if (pos < n) {
+          uint32_t skip;
+          pos += utf8_decode(s, pos, n, &skip);
+          ++cidx;
+        }
+        phase = use_sep ? 2 : 0;
+      } else {
+        if (EMIT) {
+          if (p.hits) p.hits[run] = aha_hit{cidx, cidx + best_n, best_v};
+        } else if ((int64_t)run < sc_cap) {
+          p.doc_scratch[sc_base + (int64_t)run] = aha_hit{cidx, cidx + best_n, best_v};
+        }
+        ++run;
+        pos += best_bytes;
+        cidx += best_n;
+        phase = 0;
+      }
+      continue;
+    }
+    node = e & ~kFoldCand;
+    c_bpos += l;
+    ++depth;
+    tmask = (tmask << 1) | (upper ? 1ull : 0ull);
+    if (e & kFoldCand) {
+      bool ok = true;
+      if (use_sep && c_bpos < n) {
+        uint32_t ncp;
+        utf8_decode(s, c_bpos, n, &ncp);
+        ok = sep_at(ncp);
+      }
+      if (ok) {
+        // the candidate the frontier reaches first: smallest (key mask XOR text mask) with character 0 most significant
+        const uint64_t window = depth >= 64 ? tmask : (tmask & ((1ull << depth) - 1ull));
+        const uint32_t j0 = __ldg(p.fcand_off + node), j1 = __ldg(p.fcand_off + node + 1);
+        uint64_t best_x = ~0ull;
+        for (uint32_t j = j0; j < j1; ++j) {
+          const uint4 c = __ldg(p.fcand + j);
+          const uint64_t x = (((uint64_t)c.w << 32) | c.z) ^ window;
+          if (x < best_x || j == j0) {
+            best_x = x;
+            best_v = (int32_t)c.x;
+          }
+        }
+        best_n = depth;
         best_bytes = (int32_t)(c_bpos - pos);
       }
     }

@@ -260,6 +260,32 @@ def test_cedar_match_longest_random(seed):
             assert res.hits().tobytes() == np.concatenate(want).tobytes()
 
 
+@pytest.mark.parametrize("seed", range(4))
+def test_cedar_ignore_case_variant_order(seed):
+    """ignore_case runs over the case-folded trie: many keys that differ only in case (several original nodes behind one
+    folded node), so the reference's choice -- the first candidate of the greatest length in frontier order, i.e. "as the
+    text stands" before "case swapped", character by character -- decides nearly every hit.  ASCII, Latin-1, Greek and
+    Cyrillic pairs, uncased characters in between, keys up to 64 characters."""
+    rng = random.Random(400 + seed)
+    base = ["ab", "aB", "Ab", "AB", "abc", "ABC", "Abc", "aBc", "éa", "Éa", "éA", "ÉA", "жд", "Жд", "жД", "αβ", "Αβ", "αΒ", "a日b", "A日B", "a日B",
+            "x" * 40 + "Y" * 24, "X" * 64, "q" * 63 + "Q"]
+    alpha = "abABcC éÉжЖдДαΑβΒ日"
+    words = base + ["".join(rng.choice(alpha.replace(" ", "")) for _ in range(rng.randint(1, 4))) for _ in range(300)]
+    words = list(dict.fromkeys(words))
+    rng.shuffle(words)
+    gt, ot = aha_b200.Cedar(), O.Cedar()
+    for w in words:
+        assert gt.insert(w) == ot.insert(w)
+    docs = ["".join(rng.choice(alpha) for _ in range(rng.randint(0, 400))) for _ in range(40)]
+    docs += ["AB ab Ab aB ABC abc aBC", "ÉA éa Éa", "ЖД жд", "ΑΒ αβ", "A日b a日b", "x" * 64 + " " + "X" * 64 + " " + "x" * 40 + "y" * 24, "Q" * 64 + "q" * 64, ""]
+    for sep in (None, [" "]):
+        res = gt.match_longest_batch(docs, True, sep)
+        want = [ot.match_longest(d, True, sep) for d in docs]
+        off = np.cumsum([0] + [len(w) for w in want])
+        assert np.array_equal(res.doc_hit_off(), off)
+        assert res.hits().tobytes() == np.concatenate(want).tobytes()
+
+
 def test_cedar_match_longest_long_documents():
     """documents of several windows of the warp-per-document kernel: multi-byte characters and matches across window
     boundaries, keys that contain the separator, with and without sep / ignore_case, one very long document"""

@@ -220,6 +220,11 @@ __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams 
 // Same flat state machine and the same count / record / compact / emit scheme as trie_longest_doc_kernel.  A walk step
 // folds the text character, follows ONE edge of the folded trie and shifts the character's case into the window mask;
 // a node with candidates settles which original key the reference's frontier would have reached first.
+#ifndef AHA_TRIE_SKIP
+#define AHA_TRIE_SKIP 1     // characters per iteration of the skip phase (measured on C4: 1 -> 55.4, 2 -> 52.9, 4 -> 50.6, 8 -> 48.7 GB/s)
+#endif
+// (measured: asking the compiler for a minimum number of resident blocks -- 1, 12 or 16 -- is slower than its own choice of
+// 54 registers: 29 / 40 / 33 GB/s against 50)
 template <bool EMIT>
 __global__ void __launch_bounds__(128) trie_folded_doc_kernel(const ScanParams p) {
   __shared__ uint8_t fcmap[256];
@@ -249,7 +254,10 @@ __global__ void __launch_bounds__(128) trie_folded_doc_kernel(const ScanParams p
   int phase = 0, depth = 0;
   uint32_t node = 0;
   uint64_t tmask = 0;  // bit j = the character j places behind the cursor is upper case
-  int32_t best_n = 0, best_v = 0, best_bytes = 0;
+  // the deepest node with candidates that passed the separator test; WHICH candidate is settled once, when the walk is over
+  int32_t best_n = 0, best_bytes = 0;
+  uint32_t best_node = 0;
+  uint64_t best_window = 0;
   while (phase != 3) {
     const int64_t cur = phase == 1 ? c_bpos : pos;
     bool have = cur < n;
@@ -263,7 +271,7 @@ __global__ void __launch_bounds__(128) trie_folded_doc_kernel(const ScanParams p
         pos += l;
         ++cidx;
         if (at_sep) { phase = 0; break; }
-        if (++k == 8) break;
+        if (++k == AHA_TRIE_SKIP) break;
         have = pos < n;
         if (have) l = utf8_decode(s, pos, n, &cp);
       }
@@ -311,6 +319,20 @@ __global__ void __launch_bounds__(128) trie_folded_doc_kernel(const ScanParams p
         }
         phase = use_sep ? 2 : 0;
       } else {
+        // the candidate the frontier reaches first: smallest (key mask XOR text mask) with character 0 most significant
+        const uint32_t j0 = __ldg(p.fcand_off + best_node), j1 = __ldg(p.fcand_off + best_node + 1);
+        int32_t best_v = (int32_t)__ldg(p.fcand + j0).x;
+        if (j1 - j0 > 1u) {
+          uint64_t best_x = ~0ull;
+          for (uint32_t j = j0; j < j1; ++j) {
+            const uint4 c = __ldg(p.fcand + j);
+            const uint64_t x = (((uint64_t)c.w << 32) | c.z) ^ best_window;
+            if (x < best_x || j == j0) {
+              best_x = x;
+              best_v = (int32_t)c.x;
+            }
+          }
+        }
         if (EMIT) {
           if (p.hits) p.hits[run] = aha_hit{cidx, cidx + best_n, best_v};
         } else if ((int64_t)run < sc_cap) {
@@ -335,18 +357,8 @@ __global__ void __launch_bounds__(128) trie_folded_doc_kernel(const ScanParams p
         ok = sep_at(ncp);
       }
       if (ok) {
-        // the candidate the frontier reaches first: smallest (key mask XOR text mask) with character 0 most significant
-        const uint64_t window = depth >= 64 ? tmask : (tmask & ((1ull << depth) - 1ull));
-        const uint32_t j0 = __ldg(p.fcand_off + node), j1 = __ldg(p.fcand_off + node + 1);
-        uint64_t best_x = ~0ull;
-        for (uint32_t j = j0; j < j1; ++j) {
-          const uint4 c = __ldg(p.fcand + j);
-          const uint64_t x = (((uint64_t)c.w << 32) | c.z) ^ window;
-          if (x < best_x || j == j0) {
-            best_x = x;
-            best_v = (int32_t)c.x;
-          }
-        }
+        best_node = node;
+        best_window = depth >= 64 ? tmask : (tmask & ((1ull << depth) - 1ull));
         best_n = depth;
         best_bytes = (int32_t)(c_bpos - pos);
       }

@@ -20,8 +20,12 @@
 //     kEnd  target is_end? (raw flag bits, cedar.cr:657-660, Q2/Q4) -- drives match_longest
 //     kGoto the edge is a real goto edge (not derived through fail links)
 #pragma once
+#include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
+#include <thread>
 #include <cstdint>
 #include <cstring>
 #include <string>
@@ -121,6 +125,30 @@ inline DfaView view_of(const BlobHeader& h, const uint8_t* base) {
   return v;
 }
 
+// Static chunks of [0, n) on up to `threads` host threads: fn(begin, end, thread index).  The flatten of a large
+// dictionary is a handful of passes over millions of states whose cost is the random reads of the cedar arrays.
+template <class F>
+inline void parallel_chunks(uint64_t n, int threads, F fn) {
+  if (threads <= 1 || n < 8192) {
+    fn((uint64_t)0, n, 0);
+    return;
+  }
+  std::vector<std::thread> pool;
+  const uint64_t per = (n + (uint64_t)threads - 1) / (uint64_t)threads;
+  for (int t = 0; t < threads; ++t) {
+    const uint64_t b = (uint64_t)t * per, e = std::min<uint64_t>(n, b + per);
+    if (b >= e) break;
+    pool.emplace_back([=] { fn(b, e, t); });
+  }
+  for (auto& th : pool) th.join();
+}
+// AHA_B200_FLATTEN_THREADS (1 = the sequential passes); default: the host's hardware threads, at most 16
+inline int flatten_threads() {
+  if (const char* e = getenv("AHA_B200_FLATTEN_THREADS")) return std::max(1, atoi(e));
+  const unsigned hc = std::thread::hardware_concurrency();
+  return (int)std::min<unsigned>(hc ? hc : 1u, 16u);
+}
+
 // Flatten.  Returns false + err on malformed input.
 inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* fails, const CedarOut* output,
                     const uint32_t* key_lens, int64_t n_keys, std::vector<uint8_t>* blob, std::string* err) {
@@ -150,7 +178,76 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
   label.push_back(0);
   state_of[0] = 0;
   bool used[256] = {false};
-  for (size_t s = 0; s < slot_of.size(); ++s) {
+  const int T = array_size >= (1 << 18) ? flatten_threads() : 1;
+  if (T > 1) {
+    // the same breadth-first order, one level at a time: count the children of every state of the level, prefix, place
+    std::atomic<int> bad(0);
+    std::vector<uint8_t> used_t((size_t)T * 256, 0);
+    std::vector<uint32_t> first;  // first[i] = children of the level's states in front of state i
+    size_t lo = 0;
+    auto first_sibling = [&](int32_t id, int32_t* b_out) -> int {  // -1: corrupt
+      const int32_t b = base_of(id);
+      *b_out = b;
+      uint8_t sib = nodes[id].child;
+      if (sib == 0 && b > 0) {
+        if (b >= array_size) return -1;
+        sib = nodes[b].sibling;
+      }
+      return sib;
+    };
+    while (lo < slot_of.size() && !bad.load()) {
+      const size_t hi = slot_of.size(), n_level = hi - lo;
+      first.assign(n_level + 1, 0);
+      parallel_chunks(n_level, T, [&](uint64_t b0, uint64_t e0, int) {
+        for (uint64_t i = b0; i < e0; ++i) {
+          int32_t b;
+          int sib = first_sibling(slot_of[lo + i], &b);
+          if (sib < 0) { bad.store(1); return; }
+          uint32_t n = 0;
+          while (sib != 0) {
+            const int32_t to = b ^ sib;
+            if (to < 0) break;
+            if (to >= array_size || ++n > 256) { bad.store(2); return; }
+            sib = nodes[to].sibling;
+          }
+          first[i + 1] = n;
+        }
+      });
+      if (bad.load()) break;
+      for (size_t i = 0; i < n_level; ++i) first[i + 1] += first[i];
+      const size_t total = first[n_level];
+      if (total == 0) break;
+      slot_of.resize(hi + total);
+      parent.resize(hi + total);
+      label.resize(hi + total);
+      parallel_chunks(n_level, T, [&](uint64_t b0, uint64_t e0, int t) {
+        for (uint64_t i = b0; i < e0; ++i) {
+          int32_t b;
+          int sib = first_sibling(slot_of[lo + i], &b);
+          size_t at = hi + first[i];
+          while (sib != 0) {
+            const int32_t to = b ^ sib;
+            if (to < 0) break;
+            if (__atomic_exchange_n(&state_of[to], (int32_t)at, __ATOMIC_RELAXED) >= 0) { bad.store(2); return; }
+            slot_of[at] = to;
+            parent[at] = (int32_t)(lo + i);
+            label[at] = (uint8_t)sib;
+            used_t[(size_t)t * 256 + sib] = 1;
+            ++at;
+            sib = nodes[to].sibling;
+          }
+        }
+      });
+      lo = hi;
+    }
+    if (bad.load()) {
+      *err = bad.load() == 1 ? "corrupt node: base out of range" : "corrupt sibling list";
+      return false;
+    }
+    for (int t = 0; t < T; ++t)
+      for (int b = 0; b < 256; ++b) used[b] = used[b] || used_t[(size_t)t * 256 + b];
+  }
+  for (size_t s = 0; T <= 1 && s < slot_of.size(); ++s) {
     const int32_t id = slot_of[s];
     const int32_t b = base_of(id);
     uint8_t sib = nodes[id].child;
@@ -200,53 +297,78 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
     tail[s] = tail[parent[s]] + ((d >= 2 && (label[s] & 0xC0) != 0x80) ? 1u : 0u);
   }
   std::vector<uint32_t> key_tail(n_keys > 0 ? n_keys : 1, 0);
-  for (uint64_t s = 0; s < S; ++s) {
-    out_off[s] = static_cast<uint32_t>(out_val.size());
-    if (s == 0) continue;
-    const int32_t id = slot_of[s];
-    if (is_end(id)) sflags[s] |= kEnd;
-    // ACX#fetch (ac.cr:265-278): walk while value >= 0, follow next while >= 0
-    int32_t e = id;
+  // ACX#fetch (ac.cr:265-278): walk while value >= 0, follow next while >= 0.  Two passes (count, prefix, fill) so that the
+  // states can be handled independently; returns 0 or an error code, emit(v) for every value that is kept.
+  auto walk_outputs = [&](uint64_t st, auto emit) -> int {
+    int32_t e = slot_of[st];
     int guard = 0;
     while (output[e].value >= 0) {
       const int32_t v = output[e].value;
-      if (v >= n_keys) {
-        *err = "output value out of range";
-        return false;
-      }
-      if (key_lens[v] < 0x7FFFFFFFu) out_val.push_back(v);
+      if (v >= n_keys) return 1;
+      if (key_lens[v] < 0x7FFFFFFFu) emit(v);
       if (!(output[e].next >= 0)) break;
       e = output[e].next;
-      if (e >= array_size) {
-        *err = "output chain leaves the array";
-        return false;
-      }
-      if (++guard > 1 << 20) {
-        *err = "output chain loop";
-        return false;
-      }
+      if (e >= array_size) return 2;
+      if (++guard > 1 << 20) return 3;
     }
-    if (out_val.size() > out_off[s]) sflags[s] |= kOut;
-    if (output[id].value >= 0) key_tail[output[id].value] = tail[s];
+    return 0;
+  };
+  {
+    std::atomic<int> bad(0);
+    parallel_chunks(S, T, [&](uint64_t b0, uint64_t e0, int) {
+      for (uint64_t st = std::max<uint64_t>(b0, 1); st < e0; ++st) {
+        uint32_t n = 0;
+        const int rc = walk_outputs(st, [&](int32_t) { ++n; });
+        if (rc) { bad.store(rc); return; }
+        out_off[st + 1] = n;
+      }
+    });
+    if (bad.load()) {
+      *err = bad.load() == 1 ? "output value out of range" : (bad.load() == 2 ? "output chain leaves the array" : "output chain loop");
+      return false;
+    }
+    out_off[0] = 0;
+    out_off[1] = 0;  // the root has no output list
+    for (uint64_t st = 1; st < S; ++st) out_off[st + 1] += out_off[st];
+    out_val.resize(out_off[S]);
+    parallel_chunks(S, T, [&](uint64_t b0, uint64_t e0, int) {
+      for (uint64_t st = std::max<uint64_t>(b0, 1); st < e0; ++st) {
+        const int32_t id = slot_of[st];
+        if (is_end(id)) sflags[st] |= kEnd;
+        uint32_t at = out_off[st];
+        walk_outputs(st, [&](int32_t v) { out_val[at++] = v; });
+        if (at > out_off[st]) sflags[st] |= kOut;
+        if (output[id].value >= 0) key_tail[output[id].value] = tail[st];  // a key id belongs to one state
+      }
+    });
   }
   out_off[S] = static_cast<uint32_t>(out_val.size());
   lap("3 facts + output lists");
   // 4. sparse rows: the children of a state are contiguous in BFS numbering
   std::vector<uint64_t> kid_begin(S + 1, S);  // smallest child id, S when the state has no child
-  for (uint64_t s = S; s-- > 1;) kid_begin[parent[s]] = s;
+  parallel_chunks(S, T, [&](uint64_t b0, uint64_t e0, int) {  // a state's children are consecutive: the first one of each run
+    for (uint64_t st = std::max<uint64_t>(b0, 1); st < e0; ++st)
+      if (st == 1 || parent[st] != parent[st - 1]) kid_begin[parent[st]] = st;
+  });
   auto kids_of = [&](uint64_t s, uint64_t* lo, uint64_t* hi) {
     *lo = kid_begin[s];
     *hi = *lo;
     while (*hi < S && static_cast<uint64_t>(parent[*hi]) == s) ++*hi;
   };
   std::vector<uint32_t> fail_state(S, 0);
-  for (uint64_t s = 1; s < S; ++s) {
-    const int32_t f = fails[slot_of[s]];
-    if (f < 0 || f >= array_size || state_of[f] < 0 || static_cast<uint64_t>(state_of[f]) >= s) {
+  {
+    std::atomic<int> bad(0);
+    parallel_chunks(S, T, [&](uint64_t b0, uint64_t e0, int) {
+      for (uint64_t st = std::max<uint64_t>(b0, 1); st < e0; ++st) {
+        const int32_t f = fails[slot_of[st]];
+        if (f < 0 || f >= array_size || state_of[f] < 0 || static_cast<uint64_t>(state_of[f]) >= st) { bad.store(1); return; }
+        fail_state[st] = static_cast<uint32_t>(state_of[f]);
+      }
+    });
+    if (bad.load()) {
       *err = "fail link does not point to an earlier state";
       return false;
     }
-    fail_state[s] = static_cast<uint32_t>(state_of[f]);
   }
   std::vector<SparseRow> rows(S);
   std::vector<uint32_t> wide;
@@ -254,23 +376,38 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
   auto edge_to = [&](uint64_t t, uint32_t lab) {
     return (static_cast<uint32_t>(t) << 9) | ((sflags[t] & kOut) ? kEdgeOut : 0u) | lab;
   };
-  for (uint64_t s = 0; s < S; ++s) {
-    uint64_t lo, hi;
-    kids_of(s, &lo, &hi);
-    SparseRow r;
-    r.head = (fail_state[s] << 8) | ((sflags[s] & kOut) ? kRowOut : 0u) | ((sflags[s] & kEnd) ? kRowEnd : 0u);
-    r.e[0] = r.e[1] = r.e[2] = 0;
-    if (s == 0 || hi - lo > 3) {
-      r.head |= kRowWide;
-      r.e[0] = static_cast<uint32_t>(n_wide);
-      wide.resize((n_wide + 1) * C, 0u);
-      for (uint64_t t = lo; t < hi; ++t) wide[n_wide * C + classmap[label[t]]] = edge_to(t, 1u);
-      ++n_wide;
-    } else {
-      for (uint64_t t = lo; t < hi; ++t) r.e[t - lo] = edge_to(t, label[t]);
-    }
-    rows[s] = r;
+  // which states are wide (the root, and more than three children), their rows in wide[] in state order
+  std::vector<uint32_t> wide_row(S, 0xFFFFFFFFu);
+  {
+    std::vector<uint8_t> is_wide(S, 0);
+    parallel_chunks(S, T, [&](uint64_t b0, uint64_t e0, int) {
+      for (uint64_t st = b0; st < e0; ++st) {
+        uint64_t lo, hi;
+        kids_of(st, &lo, &hi);
+        is_wide[st] = (st == 0 || hi - lo > 3) ? 1 : 0;
+      }
+    });
+    for (uint64_t st = 0; st < S; ++st)
+      if (is_wide[st]) wide_row[st] = static_cast<uint32_t>(n_wide++);
   }
+  wide.assign(n_wide * C, 0u);
+  parallel_chunks(S, T, [&](uint64_t b0, uint64_t e0, int) {
+    for (uint64_t st = b0; st < e0; ++st) {
+      uint64_t lo, hi;
+      kids_of(st, &lo, &hi);
+      SparseRow r;
+      r.head = (fail_state[st] << 8) | ((sflags[st] & kOut) ? kRowOut : 0u) | ((sflags[st] & kEnd) ? kRowEnd : 0u);
+      r.e[0] = r.e[1] = r.e[2] = 0;
+      if (wide_row[st] != 0xFFFFFFFFu) {
+        r.head |= kRowWide;
+        r.e[0] = wide_row[st];
+        for (uint64_t t = lo; t < hi; ++t) wide[static_cast<uint64_t>(wide_row[st]) * C + classmap[label[t]]] = edge_to(t, 1u);
+      } else {
+        for (uint64_t t = lo; t < hi; ++t) r.e[t - lo] = edge_to(t, label[t]);
+      }
+      rows[st] = r;
+    }
+  });
   lap("4 rows");
   const bool dense = S * static_cast<uint64_t>(C) * 4 <= kDenseMaxBytes;
   // 4a. no dense table: the dense rows of the wide states are completed to closure rows -- an entry without a goto edge
@@ -324,26 +461,30 @@ inline bool flatten(const CedarNode* nodes, int64_t array_size, const int32_t* f
     std::vector<uint32_t> out_off2(S + 1, 0), fail2(S), cnt(S, 0);
     std::vector<uint16_t> depth2(S);
     wide_fail.assign(n_wide, 0);
-    for (uint64_t s = 0; s < S; ++s) {
-      const uint32_t t = nid[s];
-      SparseRow r = rows[s];
-      r.head = (nid[r.head >> 8] << 8) | (r.head & 0xFFu);
-      if (r.head & kRowWide) {
-        for (uint32_t c = 0; c < C; ++c) wide2[static_cast<uint64_t>(t) * C + c] = re_edge(wide[static_cast<uint64_t>(r.e[0]) * C + c]);
-        r.e[0] = t;
-        wide_fail[t] = r.head >> 8;
-      } else {
-        for (int k = 0; k < 3; ++k) r.e[k] = re_edge(r.e[k]);
+    parallel_chunks(S, T, [&](uint64_t b0, uint64_t e0, int) {
+      for (uint64_t s = b0; s < e0; ++s) {
+        const uint32_t t = nid[s];
+        SparseRow r = rows[s];
+        r.head = (nid[r.head >> 8] << 8) | (r.head & 0xFFu);
+        if (r.head & kRowWide) {
+          for (uint32_t c = 0; c < C; ++c) wide2[static_cast<uint64_t>(t) * C + c] = re_edge(wide[static_cast<uint64_t>(r.e[0]) * C + c]);
+          r.e[0] = t;
+          wide_fail[t] = r.head >> 8;
+        } else {
+          for (int k = 0; k < 3; ++k) r.e[k] = re_edge(r.e[k]);
+        }
+        rows2[t] = r;
+        fail2[t] = nid[fail_state[s]];
+        depth2[t] = depth[s];
+        cnt[t] = out_off[s + 1] - out_off[s];
       }
-      rows2[t] = r;
-      fail2[t] = nid[fail_state[s]];
-      depth2[t] = depth[s];
-      cnt[t] = out_off[s + 1] - out_off[s];
-    }
+    });
     for (uint64_t t = 0; t < S; ++t) out_off2[t + 1] = out_off2[t] + cnt[t];
     std::vector<int32_t> out_val2(out_val.size());
-    for (uint64_t s = 0; s < S; ++s)
-      for (uint32_t j = 0; j < out_off[s + 1] - out_off[s]; ++j) out_val2[out_off2[nid[s]] + j] = out_val[out_off[s] + j];
+    parallel_chunks(S, T, [&](uint64_t b0, uint64_t e0, int) {
+      for (uint64_t s = b0; s < e0; ++s)
+        for (uint32_t j = 0; j < out_off[s + 1] - out_off[s]; ++j) out_val2[out_off2[nid[s]] + j] = out_val[out_off[s] + j];
+    });
     rows.swap(rows2);
     wide.swap(wide2);
     out_off.swap(out_off2);

@@ -228,3 +228,16 @@ def test_char_automaton_c2_dictionary_fits_shared_memory():
     assert info[0] == 1 and info[1] == 1, info
     want = O.AC.compile(keys).scan(text)
     assert got.tobytes() == want.tobytes()
+
+
+def test_threaded_flatten_is_byte_identical(monkeypatch):
+    """the level-synchronous / two-pass flatten on several host threads (large dictionaries) writes the same blob as the
+    sequential passes; both with a dense table (small class count) and without one (sparse rows only)"""
+    rng = random.Random(31)
+    for alpha, n_keys, lens in (("abcdefghijklmnopqrstuvwxyz", 70000, (3, 12)), ("的一是在不了有和人这中大为上个国我以要他时来用们生到作地于出就分对成会可主发年动同工也能下过子说产种面而方后多定行学法所民得经abcdefgh ", 120000, (2, 9))):
+        keys = list(dict.fromkeys("".join(rng.choice(alpha) for _ in range(rng.randint(*lens))) for _ in range(n_keys)))
+        monkeypatch.setenv("AHA_B200_FLATTEN_THREADS", "1")
+        one = _blob_of(keys)
+        monkeypatch.setenv("AHA_B200_FLATTEN_THREADS", "7")
+        many = _blob_of(keys)
+        assert len(one) > (1 << 22) and one == many

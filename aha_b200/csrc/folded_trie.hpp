@@ -86,6 +86,7 @@ inline FoldedTrieHost build_folded_trie(const BlobHeader& h, const uint8_t* blob
   const DfaView v = view_of(h, blob);
   const uint64_t S = h.n_states;
   const uint32_t C = h.n_classes;
+  if (S > ((uint64_t)1 << 21)) return F;  // a folded table of that many states would not pass the size test below: do not build it
   uint8_t byte_of_class[256] = {0};
   for (int b = 1; b < 256; ++b)
     if (v.classmap[b]) byte_of_class[v.classmap[b]] = (uint8_t)b;

@@ -251,45 +251,51 @@ __global__ void __launch_bounds__(128) trie_folded_doc_kernel(const ScanParams p
   uint64_t run = EMIT ? p.offsets[d] : 0;
   int64_t pos = 0, c_bpos = 0;
   int32_t cidx = 0;
-  int phase = 0, depth = 0;
+  int phase = 0, depth = 0, first_l = 1;
   uint32_t node = 0;
   uint64_t tmask = 0;  // bit j = the character j places behind the cursor is upper case
+  bool pending = false;  // the node just reached has candidates: they stand if what follows is a separator (or the end)
   // the deepest node with candidates that passed the separator test; WHICH candidate is settled once, when the walk is over
   int32_t best_n = 0, best_bytes = 0;
   uint32_t best_node = 0;
   uint64_t best_window = 0;
+  // Every iteration decodes ONE character -- at the walk's cursor, or at `pos` in the other two phases -- and every
+  // decision of the iteration is taken from it: the separator test serves the skip phases AND the candidate reached by
+  // the previous step (the character behind a candidate is the one the next step decodes anyway), and the length of the
+  // walk's first character is kept for the miss.  Nothing is decoded twice and the phases share one instruction stream.
   while (phase != 3) {
-    const int64_t cur = phase == 1 ? c_bpos : pos;
-    bool have = cur < n;
+    const bool walking = phase == 1;
+    const int64_t cur = walking ? c_bpos : pos;
+    const bool have = cur < n;
     uint32_t cp = 0;
     int l = 1;
     if (have) l = utf8_decode(s, cur, n, &cp);
-    if (phase == 2) {
-      for (int k = 0;;) {
-        if (!have) { phase = 3; break; }
-        const bool at_sep = sep_at(cp);
-        pos += l;
-        ++cidx;
-        if (at_sep) { phase = 0; break; }
-        if (++k == AHA_TRIE_SKIP) break;
-        have = pos < n;
-        if (have) l = utf8_decode(s, pos, n, &cp);
-      }
-      continue;
+    const bool sep = have && sep_at(cp);
+    if (pending && (!use_sep || !have || sep)) {
+      best_node = node;
+      best_window = depth >= 64 ? tmask : (tmask & ((1ull << depth) - 1ull));
+      best_n = depth;
+      best_bytes = (int32_t)(c_bpos - pos);
     }
-    if (phase == 0) {
-      if (!have) { phase = 3; continue; }
-      if (use_sep && sep_at(cp)) {
-        pos += l;
-        ++cidx;
+    pending = false;
+    if (!walking) {
+      if (!have) {
+        phase = 3;
         continue;
       }
-      phase = 1;
+      if (phase == 2 || (use_sep && sep)) {  // phase 2 runs up to (and over) the next separator, phase 0 over all of them
+        pos += l;
+        ++cidx;
+        if (sep) phase = 0;
+        continue;
+      }
+      phase = 1;  // a walk starts at this character (this iteration is its first step)
       depth = 0;
       node = 0;
       c_bpos = pos;
       tmask = 0;
       best_n = 0;
+      first_l = l;
     }
     // one step: the folded character's edge (a multi-byte character walks its bytes)
     uint32_t e = 0;
@@ -309,59 +315,45 @@ __global__ void __launch_bounds__(128) trie_folded_doc_kernel(const ScanParams p
         }
       }
     }
-    if (e == 0u) {
-      // the walk from this start is over: the deepest candidate that passed the separator test wins
-      if (best_n == 0) {
-        if (pos < n) {
-          uint32_t skip;
-          pos += utf8_decode(s, pos, n, &skip);
-          ++cidx;
-        }
-        phase = use_sep ? 2 : 0;
-      } else {
-        // the candidate the frontier reaches first: smallest (key mask XOR text mask) with character 0 most significant
-        const uint32_t j0 = __ldg(p.fcand_off + best_node), j1 = __ldg(p.fcand_off + best_node + 1);
-        int32_t best_v = (int32_t)__ldg(p.fcand + j0).x;
-        if (j1 - j0 > 1u) {
-          uint64_t best_x = ~0ull;
-          for (uint32_t j = j0; j < j1; ++j) {
-            const uint4 c = __ldg(p.fcand + j);
-            const uint64_t x = (((uint64_t)c.w << 32) | c.z) ^ best_window;
-            if (x < best_x || j == j0) {
-              best_x = x;
-              best_v = (int32_t)c.x;
-            }
-          }
-        }
-        if (EMIT) {
-          if (p.hits) p.hits[run] = aha_hit{cidx, cidx + best_n, best_v};
-        } else if ((int64_t)run < sc_cap) {
-          p.doc_scratch[sc_base + (int64_t)run] = aha_hit{cidx, cidx + best_n, best_v};
-        }
-        ++run;
-        pos += best_bytes;
-        cidx += best_n;
-        phase = 0;
-      }
+    if (e != 0u) {
+      node = e & ~kFoldCand;
+      c_bpos += l;
+      ++depth;
+      tmask = (tmask << 1) | (upper ? 1ull : 0ull);
+      pending = (e & kFoldCand) != 0u;
       continue;
     }
-    node = e & ~kFoldCand;
-    c_bpos += l;
-    ++depth;
-    tmask = (tmask << 1) | (upper ? 1ull : 0ull);
-    if (e & kFoldCand) {
-      bool ok = true;
-      if (use_sep && c_bpos < n) {
-        uint32_t ncp;
-        utf8_decode(s, c_bpos, n, &ncp);
-        ok = sep_at(ncp);
+    // the walk from this start is over: the deepest candidate that passed the separator test wins
+    if (best_n == 0) {
+      pos += first_l;
+      ++cidx;
+      phase = use_sep ? 2 : 0;
+      continue;
+    }
+    {
+      // the candidate the frontier reaches first: smallest (key mask XOR text mask) with character 0 most significant
+      const uint32_t j0 = __ldg(p.fcand_off + best_node), j1 = __ldg(p.fcand_off + best_node + 1);
+      int32_t best_v = (int32_t)__ldg(p.fcand + j0).x;
+      if (j1 - j0 > 1u) {
+        uint64_t best_x = ~0ull;
+        for (uint32_t j = j0; j < j1; ++j) {
+          const uint4 c = __ldg(p.fcand + j);
+          const uint64_t x = (((uint64_t)c.w << 32) | c.z) ^ best_window;
+          if (x < best_x || j == j0) {
+            best_x = x;
+            best_v = (int32_t)c.x;
+          }
+        }
       }
-      if (ok) {
-        best_node = node;
-        best_window = depth >= 64 ? tmask : (tmask & ((1ull << depth) - 1ull));
-        best_n = depth;
-        best_bytes = (int32_t)(c_bpos - pos);
+      if (EMIT) {
+        if (p.hits) p.hits[run] = aha_hit{cidx, cidx + best_n, best_v};
+      } else if ((int64_t)run < sc_cap) {
+        p.doc_scratch[sc_base + (int64_t)run] = aha_hit{cidx, cidx + best_n, best_v};
       }
+      ++run;
+      pos += best_bytes;
+      cidx += best_n;
+      phase = 0;
     }
   }
   if (!EMIT) p.counts[d] = (uint32_t)run;

@@ -157,7 +157,7 @@ struct DeviceDfa {
   // case-folded trie of the dictionary (folded_trie.hpp): built and uploaded at the first ignore_case scan
   int folded_state = 0;         // 0 = not tried yet, 1 = on the device, -1 = the dictionary does not qualify
   uint8_t* folded_dev = nullptr;  // one allocation: fdelta | fcand_off | fcand | fcmap
-  size_t off_fcand_off = 0, off_fcand = 0, off_fcmap = 0;
+  size_t off_fcand_off = 0, off_fcand = 0, off_fcmap = 0, off_frec = 0;
   uint32_t folded_classes = 0;
 };
 

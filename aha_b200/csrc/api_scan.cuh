@@ -276,6 +276,7 @@ static bool ensure_folded(const aha_dfa* d, DeviceDfa* dd) {
   dd->off_fcand_off = place(cursor, F.cand_off.size() * 4);
   dd->off_fcand = place(cursor, (F.cand.size() + 1) * 16);
   dd->off_fcmap = place(cursor, 256);
+  dd->off_frec = place(cursor, F.rec.size() * 4);
   std::vector<uint8_t> img(cursor, 0);
   memcpy(img.data() + off_delta, F.delta.data(), F.delta.size() * 4);
   memcpy(img.data() + dd->off_fcand_off, F.cand_off.data(), F.cand_off.size() * 4);
@@ -287,6 +288,7 @@ static bool ensure_folded(const aha_dfa* d, DeviceDfa* dd) {
     c[4 * i + 3] = (uint32_t)(F.cand[i].mask >> 32);
   }
   memcpy(img.data() + dd->off_fcmap, F.cmap, 256);
+  memcpy(img.data() + dd->off_frec, F.rec.data(), F.rec.size() * 4);
   if (cudaMalloc(&dd->folded_dev, img.size()) != cudaSuccess) {
     cudaGetLastError();
     dd->folded_dev = nullptr;
@@ -352,6 +354,7 @@ static int32_t run_v1(ScanParams p, ScanCall& c) {
     p.fcand_off = reinterpret_cast<const uint32_t*>(c.dd->folded_dev + c.dd->off_fcand_off);
     p.fcand = reinterpret_cast<const uint4*>(c.dd->folded_dev + c.dd->off_fcand);
     p.fcmap = c.dd->folded_dev + c.dd->off_fcmap;
+    p.frec = reinterpret_cast<const uint4*>(c.dd->folded_dev + c.dd->off_frec);
     p.fC = c.dd->folded_classes;
   }
   const unsigned grid = (unsigned)((units + tpb - 1) / tpb);

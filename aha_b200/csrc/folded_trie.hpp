@@ -43,6 +43,9 @@ struct FoldedTrieHost {
   std::vector<uint32_t> delta;     // [n_states][n_classes]: target | kFoldCand (target has candidates); 0 = no edge
   std::vector<uint32_t> cand_off;  // [n_states + 1]
   std::vector<FoldedCand> cand;
+  // the common case in one 32-byte sector per node: up to three candidates whose masks fit 32 bits,
+  // {n, value 0, value 1, value 2, mask 0, mask 1, mask 2, 0}; n = 0xFFFFFFFF: look at cand[] (more candidates, longer keys)
+  std::vector<uint32_t> rec;       // [n_states][8]
 };
 constexpr uint32_t kFoldCand = 0x80000000u;
 constexpr uint64_t kFoldedMaxBytes = (uint64_t)256 << 20;
@@ -187,6 +190,22 @@ inline FoldedTrieHost build_folded_trie(const BlobHeader& h, const uint8_t* blob
     for (const auto& kv : n.kid) {
       const uint32_t to = nid[kv.second];
       F.delta[i * Cf + F.cmap[kv.first]] = to | (nodes[kv.second].cand.empty() ? 0u : kFoldCand);
+    }
+  }
+  F.rec.assign(Sf * 8, 0u);
+  for (size_t i = 0; i < Sf; ++i) {
+    const uint32_t j0 = F.cand_off[i], nc = F.cand_off[i + 1] - j0;
+    uint32_t* r = &F.rec[i * 8];
+    bool small = nc <= 3;
+    for (uint32_t j = 0; j < nc && small; ++j) small = F.cand[j0 + j].n_chars <= 32;
+    if (!small) {
+      r[0] = 0xFFFFFFFFu;
+      continue;
+    }
+    r[0] = nc;
+    for (uint32_t j = 0; j < nc; ++j) {
+      r[1 + j] = (uint32_t)F.cand[j0 + j].value;
+      r[4 + j] = (uint32_t)F.cand[j0 + j].mask;
     }
   }
   F.ok = true;

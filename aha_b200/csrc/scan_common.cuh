@@ -44,6 +44,7 @@ struct ScanParams {
   const uint8_t* fcmap;          // [256] classes of the folded bytes
   const uint32_t* fcand_off;     // [n_fstates + 1]
   const uint4* fcand;            // {value, characters, mask low, mask high}
+  const uint4* frec;             // [n_fstates][2]: {n, v0, v1, v2}, {m0, m1, m2, 0} (folded_trie.hpp)
   uint32_t fC;
 };
 

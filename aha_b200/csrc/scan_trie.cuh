@@ -301,7 +301,7 @@ __global__ void __launch_bounds__(128) trie_folded_doc_kernel(const ScanParams p
     uint32_t e = 0;
     bool upper = false;
     if (have && depth < 64) {
-      upper = cp_upper(cp);
+      upper = cp < 0x80u ? (cp - 'A' < 26u) : cp_upper(cp);
       const uint32_t fc = upper ? cp + 32u : cp;
       if (fc < 0x80u) {
         e = fc ? __ldg(fdelta + (node * fC + fcmap[fc])) : 0u;
@@ -332,9 +332,15 @@ __global__ void __launch_bounds__(128) trie_folded_doc_kernel(const ScanParams p
     }
     {
       // the candidate the frontier reaches first: smallest (key mask XOR text mask) with character 0 most significant
-      const uint32_t j0 = __ldg(p.fcand_off + best_node), j1 = __ldg(p.fcand_off + best_node + 1);
-      int32_t best_v = (int32_t)__ldg(p.fcand + j0).x;
-      if (j1 - j0 > 1u) {
+      const uint4 ra = __ldg(p.frec + 2 * (size_t)best_node), rb = __ldg(p.frec + 2 * (size_t)best_node + 1);  // one sector
+      int32_t best_v = (int32_t)ra.y;
+      if (ra.x != 0xFFFFFFFFu) {  // up to three candidates, 32-bit masks
+        const uint32_t w = (uint32_t)best_window;
+        uint32_t bx = rb.x ^ w;
+        if (ra.x > 1u && (rb.y ^ w) < bx) { bx = rb.y ^ w; best_v = (int32_t)ra.z; }
+        if (ra.x > 2u && (rb.z ^ w) < bx) { best_v = (int32_t)ra.w; }
+      } else {
+        const uint32_t j0 = __ldg(p.fcand_off + best_node), j1 = __ldg(p.fcand_off + best_node + 1);
         uint64_t best_x = ~0ull;
         for (uint32_t j = j0; j < j1; ++j) {
           const uint4 c = __ldg(p.fcand + j);

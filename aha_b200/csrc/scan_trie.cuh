@@ -43,6 +43,19 @@ __device__ __forceinline__ int utf8_decode(const uint8_t* s, int64_t i, int64_t 
   *cp = b;
   return 1;
 }
+// the same with 32-bit offsets (a document is < 2^31 bytes)
+__device__ __forceinline__ int utf8_decode32(const uint8_t* s, int32_t i, int32_t n, uint32_t* cp) {
+  const uint32_t b = s[i];
+  if (b < 0x80) { *cp = b; return 1; }
+  if ((b & 0xE0) == 0xC0 && i + 1 < n) { *cp = ((b & 0x1F) << 6) | (s[i + 1] & 0x3F); return 2; }
+  if ((b & 0xF0) == 0xE0 && i + 2 < n) { *cp = ((b & 0x0F) << 12) | ((s[i + 1] & 0x3F) << 6) | (s[i + 2] & 0x3F); return 3; }
+  if ((b & 0xF8) == 0xF0 && i + 3 < n) {
+    *cp = ((b & 0x07) << 18) | ((s[i + 1] & 0x3F) << 12) | ((s[i + 2] & 0x3F) << 6) | (s[i + 3] & 0x3F);
+    return 4;
+  }
+  *cp = b;
+  return 1;
+}
 __device__ __forceinline__ int utf8_encode(uint32_t c, uint8_t* o) {
   if (c < 0x80) { o[0] = (uint8_t)c; return 1; }
   if (c < 0x800) { o[0] = 0xC0 | (c >> 6); o[1] = 0x80 | (c & 0x3F); return 2; }
@@ -242,14 +255,17 @@ __global__ void __launch_bounds__(128) trie_folded_doc_kernel(const ScanParams p
   if (d >= p.n_docs) return;
   auto sep_at = [&](uint32_t chr) -> bool { return chr < 256u && ((s_sep[chr >> 5] >> (chr & 31u)) & 1u); };
   const uint8_t* s = p.text + p.doc_off[d];
-  const int64_t n = p.doc_off[d + 1] - p.doc_off[d];
+  const int32_t n = (int32_t)(p.doc_off[d + 1] - p.doc_off[d]);  // documents are < 2^31 bytes (validated)
   const int64_t sc_base = p.doc_off[d] >> 2, sc_cap = p.doc_scratch ? (p.doc_off[d + 1] >> 2) - sc_base : 0;
   if (EMIT && p.doc_scratch && (int64_t)p.counts[d] <= sc_cap) return;
   const bool use_sep = (p.mode & AHA_SEP) != 0;
   const uint32_t* const fdelta = p.fdelta;
   const uint32_t fC = p.fC;
-  uint64_t run = EMIT ? p.offsets[d] : 0;
-  int64_t pos = 0, c_bpos = 0;
+  // where this document's hits go: its final place (EMIT) or its scratch slice (count pass, up to out_cap records)
+  aha_hit* const out = EMIT ? (p.hits ? p.hits + p.offsets[d] : nullptr) : (p.doc_scratch ? p.doc_scratch + sc_base : nullptr);
+  const uint32_t out_cap = EMIT ? 0xFFFFFFFFu : (uint32_t)min(sc_cap, (int64_t)0x7FFFFFFF);
+  uint32_t run = 0;
+  int32_t pos = 0, c_bpos = 0;
   int32_t cidx = 0;
   int phase = 0, depth = 0, first_l = 1;
   uint32_t node = 0;
@@ -265,17 +281,17 @@ __global__ void __launch_bounds__(128) trie_folded_doc_kernel(const ScanParams p
   // walk's first character is kept for the miss.  Nothing is decoded twice and the phases share one instruction stream.
   while (phase != 3) {
     const bool walking = phase == 1;
-    const int64_t cur = walking ? c_bpos : pos;
+    const int32_t cur = walking ? c_bpos : pos;
     const bool have = cur < n;
     uint32_t cp = 0;
     int l = 1;
-    if (have) l = utf8_decode(s, cur, n, &cp);
+    if (have) l = utf8_decode32(s, cur, n, &cp);
     const bool sep = have && sep_at(cp);
     if (pending && (!use_sep || !have || sep)) {
       best_node = node;
       best_window = depth >= 64 ? tmask : (tmask & ((1ull << depth) - 1ull));
       best_n = depth;
-      best_bytes = (int32_t)(c_bpos - pos);
+      best_bytes = c_bpos - pos;
     }
     pending = false;
     if (!walking) {
@@ -351,11 +367,7 @@ __global__ void __launch_bounds__(128) trie_folded_doc_kernel(const ScanParams p
           }
         }
       }
-      if (EMIT) {
-        if (p.hits) p.hits[run] = aha_hit{cidx, cidx + best_n, best_v};
-      } else if ((int64_t)run < sc_cap) {
-        p.doc_scratch[sc_base + (int64_t)run] = aha_hit{cidx, cidx + best_n, best_v};
-      }
+      if (out && run < out_cap) out[run] = aha_hit{cidx, cidx + best_n, best_v};
       ++run;
       pos += best_bytes;
       cidx += best_n;

@@ -238,8 +238,13 @@ __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams 
 #endif
 // (measured: asking the compiler for a minimum number of resident blocks -- 1, 12 or 16 -- is slower than its own choice of
 // 54 registers: 29 / 40 / 33 GB/s against 50)
+#ifdef AHA_TRIE_BLOCKS
+#define AHA_TRIE_BOUNDS __launch_bounds__(128, AHA_TRIE_BLOCKS)
+#else
+#define AHA_TRIE_BOUNDS __launch_bounds__(128)
+#endif
 template <bool EMIT>
-__global__ void __launch_bounds__(128) trie_folded_doc_kernel(const ScanParams p) {
+__global__ void AHA_TRIE_BOUNDS trie_folded_doc_kernel(const ScanParams p) {
   __shared__ uint8_t fcmap[256];
   __shared__ uint32_t s_sep[8];
   for (int i = threadIdx.x; i < 256; i += blockDim.x) fcmap[i] = p.fcmap[i];
@@ -294,29 +299,28 @@ __global__ void __launch_bounds__(128) trie_folded_doc_kernel(const ScanParams p
       best_bytes = c_bpos - pos;
     }
     pending = false;
-    if (!walking) {
-      if (!have) {
-        phase = 3;
-        continue;
-      }
-      if (phase == 2 || (use_sep && sep)) {  // phase 2 runs up to (and over) the next separator, phase 0 over all of them
-        pos += l;
-        ++cidx;
-        if (sep) phase = 0;
-        continue;
-      }
-      phase = 1;  // a walk starts at this character (this iteration is its first step)
-      depth = 0;
-      node = 0;
-      c_bpos = pos;
-      tmask = 0;
-      best_n = 0;
-      first_l = l;
+    if (!walking && !have) {  // the document is finished (once per document)
+      phase = 3;
+      continue;
     }
+    // Straight-line from here to the end of a step: lanes that skip, start and walk run the same instructions.
+    // skip: phase 2 runs up to (and over) the next separator, phase 0 over all of them
+    const bool skip = !walking && (phase == 2 || (use_sep && sep));
+    const bool start = !walking && !skip;  // a walk starts at this character (this iteration is its first step)
+    pos += skip ? l : 0;
+    cidx += skip ? 1 : 0;
+    phase = (skip && sep) ? 0 : (start ? 1 : phase);
+    depth = start ? 0 : depth;
+    node = start ? 0u : node;
+    c_bpos = start ? pos : c_bpos;
+    tmask = start ? 0ull : tmask;
+    best_n = start ? 0 : best_n;
+    first_l = start ? l : first_l;
+    const bool step = walking || start;
     // one step: the folded character's edge (a multi-byte character walks its bytes)
     uint32_t e = 0;
     bool upper = false;
-    if (have && depth < 64) {
+    if (step && have && depth < 64) {
       upper = cp < 0x80u ? (cp - 'A' < 26u) : cp_upper(cp);
       const uint32_t fc = upper ? cp + 32u : cp;
       if (fc < 0x80u) {
@@ -331,14 +335,13 @@ __global__ void __launch_bounds__(128) trie_folded_doc_kernel(const ScanParams p
         }
       }
     }
-    if (e != 0u) {
-      node = e & ~kFoldCand;
-      c_bpos += l;
-      ++depth;
-      tmask = (tmask << 1) | (upper ? 1ull : 0ull);
-      pending = (e & kFoldCand) != 0u;
-      continue;
-    }
+    const bool adv = e != 0u;
+    node = adv ? (e & ~kFoldCand) : node;
+    c_bpos += adv ? l : 0;
+    depth += adv ? 1 : 0;
+    tmask = adv ? ((tmask << 1) | (upper ? 1ull : 0ull)) : tmask;
+    pending = adv && (e & kFoldCand) != 0u;
+    if (!step || adv) continue;
     // the walk from this start is over: the deepest candidate that passed the separator test wins
     if (best_n == 0) {
       pos += first_l;

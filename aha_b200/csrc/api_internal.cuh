@@ -158,7 +158,7 @@ struct DeviceDfa {
   int folded_state = 0;         // 0 = not tried yet, 1 = on the device, -1 = the dictionary does not qualify
   uint8_t* folded_dev = nullptr;  // one allocation: fdelta | fcand_off | fcand | fcmap
   size_t off_fcand_off = 0, off_fcand = 0, off_fcmap = 0, off_frec = 0;
-  uint32_t folded_classes = 0;
+  uint32_t folded_classes = 0, folded_max_chars = 0;
 };
 
 // Result buffers (hits, doc_hit_off) are handed to the caller and come back through aha_b200_hits_free: they are

@@ -301,6 +301,7 @@ static bool ensure_folded(const aha_dfa* d, DeviceDfa* dd) {
     return false;
   }
   dd->folded_classes = F.n_classes;
+  dd->folded_max_chars = F.max_chars;
   dd->folded_state = 1;
   return true;
 }
@@ -331,9 +332,22 @@ static int32_t run_v1(ScanParams p, ScanCall& c) {
   const int tpb = 128;
   // trie path: the count pass keeps its hits in a scratch slice per document (3 bytes of scratch per byte of text), so
   // that the walk runs once; not for inputs whose scratch would not be reasonable to ask for
+  // ignore_case: the case-folded trie (one lookup per character) when the dictionary qualifies; knob 1 keeps the
+  // depth-first walk with the frontier
+  const bool folded = trie && (p.mode & AHA_IGNORE_CASE) && !knobs().force_v1 && ensure_folded(c.dfa, c.dd);
   aha_hit* doc_scratch = nullptr;
-  if (trie && !(p.mode & AHA_COUNT_ONLY) && p.total > 0 && p.total <= ((int64_t)16 << 30))
-    AHA_CUDA(ws->get(kWsDocScratch, (size_t)((p.total >> 2) + 1), &doc_scratch));
+  if (trie && !(p.mode & AHA_COUNT_ONLY) && p.total > 0 && p.total <= ((int64_t)16 << 30)) {
+    if (folded && c.dd->folded_max_chars <= 32) {
+      // 16-byte records {first character, characters, folded node, case window}: which key stands behind the node is
+      // settled by the compaction kernel, not inside the walk
+      uint4* s16 = nullptr;
+      AHA_CUDA(ws->get(kWsDocScratch, (size_t)((p.total >> 2) + 1), &s16));
+      p.doc_scratch16 = s16;
+      doc_scratch = reinterpret_cast<aha_hit*>(s16);  // (non-null: "the count pass records")
+    } else {
+      AHA_CUDA(ws->get(kWsDocScratch, (size_t)((p.total >> 2) + 1), &doc_scratch));
+    }
+  }
   p.doc_scratch = doc_scratch;
   AHA_CUDA(cudaEventRecord(ws->ev0, st));
   if (!c.validated) {
@@ -346,9 +360,6 @@ static int32_t run_v1(ScanParams p, ScanCall& c) {
     if (rc) return rc;
     p.lead_prefix = lead_prefix;
   }
-  // ignore_case: the case-folded trie (one lookup per character) when the dictionary qualifies; knob 1 keeps the
-  // depth-first walk with the frontier
-  const bool folded = trie && (p.mode & AHA_IGNORE_CASE) && !knobs().force_v1 && ensure_folded(c.dfa, c.dd);
   if (folded) {
     p.fdelta = reinterpret_cast<const uint32_t*>(c.dd->folded_dev);
     p.fcand_off = reinterpret_cast<const uint32_t*>(c.dd->folded_dev + c.dd->off_fcand_off);
@@ -380,7 +391,8 @@ static int32_t run_v1(ScanParams p, ScanCall& c) {
   if (units > 0) {
     if (longest) {
       if (trie && p.doc_scratch && p.hits) {
-        trie_compact_kernel<<<(unsigned)((p.n_docs + 7) / 8), 256, 0, st>>>(p);
+        if (p.doc_scratch16) trie_compact_folded_kernel<<<(unsigned)((p.n_docs + 7) / 8), 256, 0, st>>>(p);
+        else trie_compact_kernel<<<(unsigned)((p.n_docs + 7) / 8), 256, 0, st>>>(p);
         count_launch();
       }
       if (folded) trie_folded_doc_kernel<true><<<grid, tpb, 0, st>>>(p);

@@ -46,6 +46,8 @@ struct ScanParams {
   const uint4* fcand;            // {value, characters, mask low, mask high}
   const uint4* frec;             // [n_fstates][2]: {n, v0, v1, v2}, {m0, m1, m2, 0} (folded_trie.hpp)
   uint32_t fC;
+  uint4* doc_scratch16;          // folded path, keys of at most 32 characters: {first character, characters, folded node, window} per hit,
+                                 // the key behind the node is settled by trie_compact_folded_kernel (coalesced, off the walk)
 };
 
 // "chr < sep.size && !sep[chr]" (ac.cr:326,333): neighbour byte vetoes the hit

@@ -229,6 +229,31 @@ __global__ void __launch_bounds__(128) trie_longest_doc_kernel(const ScanParams 
   if (!EMIT) p.counts[d] = (uint32_t)run;
 }
 
+// The candidate of folded node `nd` that the reference's frontier reaches first: smallest (key mask XOR text window) with
+// character 0 most significant (folded_trie.hpp).  One 32-byte record for the common case, the node's list otherwise.
+__device__ __forceinline__ int32_t folded_pick(const ScanParams& p, uint32_t nd, uint64_t window) {
+  const uint4 ra = __ldg(p.frec + 2 * (size_t)nd), rb = __ldg(p.frec + 2 * (size_t)nd + 1);  // one sector
+  int32_t best_v = (int32_t)ra.y;
+  if (ra.x != 0xFFFFFFFFu) {  // up to three candidates, 32-bit masks
+    const uint32_t w = (uint32_t)window;
+    uint32_t bx = rb.x ^ w;
+    if (ra.x > 1u && (rb.y ^ w) < bx) { bx = rb.y ^ w; best_v = (int32_t)ra.z; }
+    if (ra.x > 2u && (rb.z ^ w) < bx) { best_v = (int32_t)ra.w; }
+  } else {
+    const uint32_t j0 = __ldg(p.fcand_off + nd), j1 = __ldg(p.fcand_off + nd + 1);
+    uint64_t best_x = ~0ull;
+    for (uint32_t j = j0; j < j1; ++j) {
+      const uint4 c = __ldg(p.fcand + j);
+      const uint64_t x = (((uint64_t)c.w << 32) | c.z) ^ window;
+      if (x < best_x || j == j0) {
+        best_x = x;
+        best_v = (int32_t)c.x;
+      }
+    }
+  }
+  return best_v;
+}
+
 // ---- ignore_case over the case-folded trie (folded_trie.hpp): one lookup per character, no frontier ------------------
 // Same flat state machine and the same count / record / compact / emit scheme as trie_longest_doc_kernel.  A walk step
 // folds the text character, follows ONE edge of the folded trie and shifts the character's case into the window mask;
@@ -269,6 +294,7 @@ __global__ void AHA_TRIE_BOUNDS trie_folded_doc_kernel(const ScanParams p) {
   // where this document's hits go: its final place (EMIT) or its scratch slice (count pass, up to out_cap records)
   aha_hit* const out = EMIT ? (p.hits ? p.hits + p.offsets[d] : nullptr) : (p.doc_scratch ? p.doc_scratch + sc_base : nullptr);
   const uint32_t out_cap = EMIT ? 0xFFFFFFFFu : (uint32_t)min(sc_cap, (int64_t)0x7FFFFFFF);
+  uint4* const out16 = EMIT ? nullptr : (p.doc_scratch16 ? p.doc_scratch16 + sc_base : nullptr);
   uint32_t run = 0;
   int32_t pos = 0, c_bpos = 0;
   int32_t cidx = 0;
@@ -350,27 +376,13 @@ __global__ void AHA_TRIE_BOUNDS trie_folded_doc_kernel(const ScanParams p) {
       continue;
     }
     {
-      // the candidate the frontier reaches first: smallest (key mask XOR text mask) with character 0 most significant
-      const uint4 ra = __ldg(p.frec + 2 * (size_t)best_node), rb = __ldg(p.frec + 2 * (size_t)best_node + 1);  // one sector
-      int32_t best_v = (int32_t)ra.y;
-      if (ra.x != 0xFFFFFFFFu) {  // up to three candidates, 32-bit masks
-        const uint32_t w = (uint32_t)best_window;
-        uint32_t bx = rb.x ^ w;
-        if (ra.x > 1u && (rb.y ^ w) < bx) { bx = rb.y ^ w; best_v = (int32_t)ra.z; }
-        if (ra.x > 2u && (rb.z ^ w) < bx) { best_v = (int32_t)ra.w; }
+      if (!EMIT && out16) {
+        // the count pass only notes the node: the compaction settles the key, coalesced and off the walk
+        if (run < out_cap) out16[run] = make_uint4((uint32_t)cidx, (uint32_t)best_n, best_node, (uint32_t)best_window);
       } else {
-        const uint32_t j0 = __ldg(p.fcand_off + best_node), j1 = __ldg(p.fcand_off + best_node + 1);
-        uint64_t best_x = ~0ull;
-        for (uint32_t j = j0; j < j1; ++j) {
-          const uint4 c = __ldg(p.fcand + j);
-          const uint64_t x = (((uint64_t)c.w << 32) | c.z) ^ best_window;
-          if (x < best_x || j == j0) {
-            best_x = x;
-            best_v = (int32_t)c.x;
-          }
-        }
+        const int32_t best_v = folded_pick(p, best_node, best_window);
+        if (out && run < out_cap) out[run] = aha_hit{cidx, cidx + best_n, best_v};
       }
-      if (out && run < out_cap) out[run] = aha_hit{cidx, cidx + best_n, best_v};
       ++run;
       pos += best_bytes;
       cidx += best_n;
@@ -378,6 +390,22 @@ __global__ void AHA_TRIE_BOUNDS trie_folded_doc_kernel(const ScanParams p) {
     }
   }
   if (!EMIT) p.counts[d] = (uint32_t)run;
+}
+
+// deferred records of the folded path -> final hits: one warp per document, the key behind each node settled here
+__global__ void __launch_bounds__(256) trie_compact_folded_kernel(const ScanParams p) {
+  const int64_t d = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (d >= p.n_docs || !p.hits) return;
+  const int64_t sc_base = p.doc_off[d] >> 2, sc_cap = (p.doc_off[d + 1] >> 2) - sc_base;
+  const int64_t cnt = p.counts[d];
+  if (cnt > sc_cap) return;  // walked again by the EMIT pass
+  const uint4* src = p.doc_scratch16 + sc_base;
+  aha_hit* dst = p.hits + p.offsets[d];
+  for (int64_t i = lane; i < cnt; i += 32) {
+    const uint4 r = src[i];
+    dst[i] = aha_hit{(int32_t)r.x, (int32_t)(r.x + r.y), folded_pick(p, r.z, (uint64_t)r.w)};
+  }
 }
 
 // scratch slices -> final positions: one warp per document, 12-byte records copied as words

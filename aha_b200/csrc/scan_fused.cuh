@@ -36,7 +36,10 @@ constexpr int kMarkCapC = 2;      // ... per sub-chunk (scan_char.cuh walks two 
 #endif
 constexpr int kFusedWarps = AHA_B200_CHAR_WARPS;   // warps per CTA of scan_char_kernel (register- and shared-memory-bound)
 constexpr int kByteChunkDefault = 132;  // bytes per lane of the byte kernel (AHA_B200_BYTE_CHUNK overrides; see fused_geometry)
-constexpr int kByteWarps = 32;    // warps per CTA of scan_fused_kernel<ByteGlobal>: latency-bound on L2, so as many as fit
+#ifndef AHA_BYTE_WARPS
+#define AHA_BYTE_WARPS 32
+#endif
+constexpr int kByteWarps = AHA_BYTE_WARPS;  // warps per CTA of scan_fused_kernel<ByteGlobal>: latency-bound on L2, so as many as fit
 
 struct FusedParams {
   ScanParams sp;

@@ -1162,7 +1162,12 @@ int32_t aha_b200_scan(const aha_dfa* d, const uint8_t* text, const int64_t* doc_
     // (a 64 MB run of 4 KiB documents is 16 k threads on a GPU that holds 300 k)
     if ((mode & AHA_TRIE_LONGEST) && n_docs > 0 && knobs().e2e_chunk_mb >= 16) {
       const int64_t avg = std::max<int64_t>(1, doc_off[n_docs] / n_docs);
-      target = std::min<int64_t>(std::max<int64_t>(target, avg * ((int64_t)1 << 18)), (int64_t)2 << 30);
+      static const int64_t run_docs = [] {  // AHA_B200_TRIE_RUN_DOCS: documents per run of the per-document machine
+        const char* e = getenv("AHA_B200_TRIE_RUN_DOCS");
+        const long long v = e ? atoll(e) : 0;
+        return (int64_t)(v > 0 ? v : ((long long)1 << 16));  // measured on C4 (2 GiB, e2e GB/s): 32 k 26.4, 64 k 34.9, 128 k 33.5, 256 k 27.8
+      }();
+      target = std::min<int64_t>(std::max<int64_t>(target, avg * run_docs), (int64_t)2 << 30);
     }
     int64_t start = 0;
     for (int64_t i = 0; i < n_docs; ++i) {

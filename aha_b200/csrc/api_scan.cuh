@@ -520,7 +520,7 @@ static int32_t run_char_split(ScanParams p, ScanCall& c) {
   fp.n_tiles = (p.total + fp.tile - 1) / fp.tile;
   const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
   const bool count_only = (p.mode & AHA_COUNT_ONLY) != 0;
-  const bool sep = (p.mode & AHA_SEP) != 0;  // byte offsets only (scan_on_device)
+  const bool sep = (p.mode & AHA_SEP) != 0;  // events carry byte positions; character offsets are counted by the expansion
   const HotTable& h = c.dd->hot;
   fill_char_tables(&cp.t, h);
   cp.cmap_g = p.classmap;
@@ -790,9 +790,8 @@ static int32_t scan_on_device(const aha_dfa* d, const void* dev_text, const void
   fill_params(&p, dd, dev_text, dev_doc_off, n_docs, total, mode, sep_bits, sep_size);
   const Knobs& k = knobs();
   const bool tiled_ok = !k.force_v1 && !(mode & (AHA_LONGEST | AHA_TRIE_LONGEST)) && dd->view.max_key_len <= 1024;
-  // sep with character offsets stays on the byte kernel: the neighbour tests need byte positions, the character path's
-  // events carry character positions in that mode
-  const bool sep_chars = (mode & AHA_SEP) && (mode & (AHA_UNITS_CHAR | AHA_SEP_CODEPOINT));
+  // the code-point form of the neighbour test (Array(Char) overloads) stays on the byte kernel
+  const bool sep_chars = (mode & AHA_SEP) && (mode & AHA_SEP_CODEPOINT);
   const bool split = tiled_ok && dd->hot.ok && !k.no_char && !sep_chars;
   // match_longest: speculative chunks inside documents (knob 1 keeps the one-thread-per-document machine)
   const bool long_chunks = (mode & AHA_LONGEST) && !(mode & AHA_TRIE_LONGEST) && !k.force_v1;

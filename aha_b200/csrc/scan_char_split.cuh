@@ -245,6 +245,19 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
   }
 }
 
+// unit starts (non-continuation bytes) of text[from, to): byte head, aligned words, byte tail
+__device__ __forceinline__ uint32_t count_leads_global(const uint8_t* text, int64_t from, int64_t to) {
+  uint32_t c = 0;
+  int64_t i = from;
+  for (; i < to && (i & 3); ++i) c += ((__ldg(text + i) & 0xC0) != 0x80);
+  for (; i + 4 <= to; i += 4) {
+    const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(text + i));
+    c += 4u - (uint32_t)__popc(w & 0x80808080u & ~(w << 1));
+  }
+  for (; i < to; ++i) c += ((__ldg(text + i) & 0xC0) != 0x80);
+  return c;
+}
+
 // ---- 2. / 3. count and expansion: one warp per tile ---------------------------------------------------------------
 // An event's end offset = its tile-relative `rel` + the tile's base - the base of the document it lies in (bytes:
 // tile start / document start; characters: unit starts in front of the tile / in front of the document).  The
@@ -363,6 +376,9 @@ __global__ void __launch_bounds__(256, 4) char_expand_kernel(const __grid_consta
   const FusedParams& F = P.f;
   const ScanParams& p = F.sp;
   const bool chars = !kSep && (p.mode & AHA_UNITS_CHAR) != 0;
+  // kSep with character offsets (String overloads): the events carry BYTE positions (the vetoes need them); the hit's
+  // character offsets are counted here -- unit starts of the tile in front of the event, from the text itself
+  const bool sep_chars = kSep && !kCount && (p.mode & AHA_UNITS_CHAR) != 0;
   const int lane = threadIdx.x & 31;
   const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   for (int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < F.n_tiles; t += n_warps) {
@@ -379,6 +395,20 @@ __global__ void __launch_bounds__(256, 4) char_expand_kernel(const __grid_consta
     // bases as 64-bit differences: end = rel + (tile base - document base)
     const int64_t tile_base = chars ? (int64_t)F.tile_lead[t] : t * (int64_t)F.tile;
     int64_t delta = tile_base - (chars ? (int64_t)p.doc_lead_base[td.doc] : td.doc_start);  // warp-uniform, updated at markers
+    // sep_chars: unit starts of the tile in front of each lane's chunk, and of the text in front of the current document
+    uint32_t lead_excl = 0;
+    int64_t doc_lead = 0;
+    if (sep_chars) {
+      const int64_t ca = min(t * (int64_t)F.tile + (int64_t)lane * F.chunk, p.total), cb = min(ca + (int64_t)F.chunk, p.total);
+      const uint32_t mine = count_leads_global(p.text, ca, cb);
+      uint32_t incl = mine;
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+      }
+      lead_excl = incl - mine;
+      doc_lead = (int64_t)p.doc_lead_base[td.doc];
+    }
     uint32_t run = 0;
     for (uint32_t base = 0; base < te.E; base += 32) {
       const uint32_t ev = te.fetch(base + lane);
@@ -387,7 +417,7 @@ __global__ void __launch_bounds__(256, 4) char_expand_kernel(const __grid_consta
       uint2 r8 = make_uint2(0u, 0u);
       if (live && !mark) r8 = Q.ref8_g[ev & 0xFFFFu];
       uint32_t n = (r8.y & 0x80000000u) ? (r8.y & 0x7FFFFFFFu) : (r8.y != 0u ? 1u : 0u);
-      int64_t my_delta = delta, my_lo = doc_lo, my_hi = doc_hi;
+      int64_t my_delta = delta, my_lo = doc_lo, my_hi = doc_hi, my_dlead = doc_lead;
       if (__any_sync(0xffffffffu, mark)) {
         // document of every event of this round: the last marker at or in front of it, else the carried one
         int64_t d_here = mark ? (int64_t)(ev & ~kEvMark) : -1;
@@ -400,12 +430,14 @@ __global__ void __launch_bounds__(256, 4) char_expand_kernel(const __grid_consta
           if (kSep) {
             my_lo = p.doc_off[d_here];
             my_hi = p.doc_off[d_here + 1];
+            if (sep_chars) my_dlead = (int64_t)p.doc_lead_base[d_here];
           }
         }
         delta = __shfl_sync(0xffffffffu, my_delta, 31);
         if (kSep) {
           doc_lo = __shfl_sync(0xffffffffu, my_lo, 31);
           doc_hi = __shfl_sync(0xffffffffu, my_hi, 31);
+          if (sep_chars) doc_lead = __shfl_sync(0xffffffffu, my_dlead, 31);
         }
       }
       const int64_t abs_end = t * (int64_t)F.tile + (int64_t)((ev >> 16) & 0x7FFFu);  // kSep: first byte after the match
@@ -424,6 +456,16 @@ __global__ void __launch_bounds__(256, 4) char_expand_kernel(const __grid_consta
           n = keep;
         }
       }
+      int32_t end_char = 0;
+      if (sep_chars) {
+        const uint32_t rel = (ev >> 16) & 0x7FFFu;                       // the match ends rel bytes behind the tile start
+        const uint32_t j = rel ? min((rel - 1u) / (uint32_t)F.chunk, 31u) : 0u;  // the lane chunk that holds its last byte
+        const uint32_t before = __shfl_sync(0xffffffffu, lead_excl, j);
+        if (n != 0) {
+          const int64_t cs = t * (int64_t)F.tile + (int64_t)j * F.chunk;
+          end_char = (int32_t)((int64_t)F.tile_lead[t] - my_dlead + before + count_leads_global(p.text, cs, abs_end));
+        }
+      }
       uint32_t len_incl = n;
       for (int o = 1; o < 32; o <<= 1) {
         uint32_t v = __shfl_up_sync(0xffffffffu, len_incl, o);
@@ -438,7 +480,9 @@ __global__ void __launch_bounds__(256, 4) char_expand_kernel(const __grid_consta
         const int32_t end = (int32_t)((int64_t)((ev >> 16) & 0x7FFFu) + my_delta);
         if (!(r8.y & 0x80000000u)) {
           if (at < F.hit_cap)
-            p.hits[at] = chars ? aha_hit{end - 1 - (int32_t)(r8.y & 0xFFFFu), end, (int32_t)r8.x} : aha_hit{end - (int32_t)(r8.y >> 16), end, (int32_t)r8.x};
+            p.hits[at] = sep_chars ? aha_hit{end_char - 1 - (int32_t)(r8.y & 0xFFFFu), end_char, (int32_t)r8.x}
+                                   : (chars ? aha_hit{end - 1 - (int32_t)(r8.y & 0xFFFFu), end, (int32_t)r8.x}
+                                            : aha_hit{end - (int32_t)(r8.y >> 16), end, (int32_t)r8.x});
         } else if (kSep) {
           const uint32_t n_all = r8.y & 0x7FFFFFFFu;
           for (uint32_t j = r8.x; j < r8.x + n_all; ++j) {
@@ -446,7 +490,7 @@ __global__ void __launch_bounds__(256, 4) char_expand_kernel(const __grid_consta
             const int32_t len = (int32_t)p.key_len[v];
             const int64_t start = abs_end - len;
             if (start > my_lo && sep_rejects(p, __ldg(p.text + start - 1))) continue;
-            if (at < F.hit_cap) p.hits[at] = aha_hit{end - len, end, v};
+            if (at < F.hit_cap) p.hits[at] = sep_chars ? aha_hit{end_char - 1 - (int32_t)p.key_tail[v], end_char, v} : aha_hit{end - len, end, v};
             ++at;
           }
         } else {

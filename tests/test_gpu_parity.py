@@ -477,6 +477,13 @@ def test_sep_on_the_character_path():
     docs = ["".join(rng.choice(alpha) for _ in range(rng.choice([0, 5, 700, 9000]))) for _ in range(120)]
     check_batch(big, docs, sep=[" "])
     check_batch(big, docs, sep=[" ", "a"], sep_size=200)
+    # the String overloads (character offsets) on the same path: the expansion counts the characters
+    U = aha_b200.UNITS_CHAR
+    check_batch(big, docs, U, sep=[" "])
+    check_batch(big, docs, U, sep=[" ", "a"], sep_size=200)
+    check_batch(keys, ["的的 的一的 的", "的", "", "的的", " 的 ", "ab abc b", "abc", "c d c d", "xab", "ab的", "的ab 的"], U, sep=[" "])
+    check_batch(keys, ["的", "的的", "ab", "b", ""] * 700, U, sep=[" "])
+    check_batch(keys, ["的" * 6000, "的 " * 3000, "ab " * 2000 + "的一的" * 800, "é的 ab é" * 900], U, sep=[" "])
 
 
 def test_match_longest_inside_long_documents():

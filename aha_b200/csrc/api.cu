@@ -40,6 +40,8 @@ Knobs& knobs() {
     v.byte_chunk = num("AHA_B200_BYTE_CHUNK", 0);
     v.e2e_chunk_mb = num("AHA_B200_E2E_CHUNK_MB", 64);
     if (v.e2e_chunk_mb <= 0) v.e2e_chunk_mb = 64;
+    v.byte_span = num("AHA_B200_BYTE_SPAN", kByteSpanDefault);
+    if (v.byte_span < 0 || v.byte_span > 8192 || (v.byte_span & 15)) v.byte_span = 0;
     return v;
   }();
   return k;
@@ -348,6 +350,7 @@ int32_t aha_b200_debug_set(int32_t knob, int32_t value) {
     case 1: k.force_v1 = value != 0; return AHA_OK;
     case 2: k.byte_chunk = value; return AHA_OK;
     case 3: k.e2e_chunk_mb = value > 0 ? value : 64; return AHA_OK;
+    case 4: k.byte_span = value < 0 ? kByteSpanDefault : ((value <= 8192 && !(value & 15)) ? value : 0); return AHA_OK;  // -1: default
     default: return set_err(AHA_ERR_ARG, "unknown knob");
   }
 }

@@ -194,6 +194,7 @@ struct Knobs {
   int force_v1 = 0;         // AHA_B200_IMPL=0: two-pass checker kernels (the fallback for keys > 1024 bytes)
   int byte_chunk = 0;       // AHA_B200_BYTE_CHUNK: bytes per lane of the byte kernel (0 = default)
   int e2e_chunk_mb = 64;    // AHA_B200_E2E_CHUNK_MB: run size of the host pipeline
+  int byte_span = 0;        // AHA_B200_BYTE_SPAN: bytes per lane of the byte kernel's span mode (0 = staged tiles)
 };
 Knobs& knobs();
 

@@ -656,6 +656,8 @@ static int32_t launch_fused(const FusedParams& fp, const Policy& pol, int n_sm, 
   if ((fp.sp.mode & AHA_SEP) || !fp.ev_scratch) {
     AHA_CUDA(cudaFuncSetAttribute(scan_fused_kernel<Policy, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     scan_fused_kernel<Policy, false><<<n_sm, kByteWarps * 32, smem, st>>>(fp, pol);
+  } else if (fp.span) {
+    scan_fused_kernel<Policy, true, true><<<n_sm, kSpanWarps * 32, smem, st>>>(fp, pol);
   } else {
     AHA_CUDA(cudaFuncSetAttribute(scan_fused_kernel<Policy, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     scan_fused_kernel<Policy, true><<<n_sm, kByteWarps * 32, smem, st>>>(fp, pol);
@@ -672,11 +674,21 @@ static int32_t run_fused(ScanParams p, ScanCall& c) {
   FusedParams fp;
   memset(&fp, 0, sizeof(fp));
   fused_geometry(p.warm + 1, false, &fp.chunk, &fp.w16, &fp.buf_bytes);
+  fp.ev_cap = kByteEvCap;
+  // Span mode (event delivery, documents that are not tiny): no staging, every lane reads a span of kSpanBytes from
+  // global memory; the warm-up in front of a span is then a few percent of the walk, and no shared memory is taken from L1.
+  // Tiny documents keep the staged tiles (a span would hold more document starts than a lane has marker slots).
+  if (!(p.mode & AHA_SEP) && knobs().byte_span && p.n_docs > 0 && p.total / p.n_docs >= 4 * knobs().byte_span) {
+    fp.span = 1;
+    fp.chunk = knobs().byte_span;
+    fp.buf_bytes = 0;
+    fp.ev_cap = std::max(kByteEvCap, fp.chunk / 4);
+  }
   fp.tile = 32 * fp.chunk;
   fp.n_tiles = (p.total + fp.tile - 1) / fp.tile;
   const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
   const bool count_only = (p.mode & AHA_COUNT_ONLY) != 0;
-  const int64_t n_warps = (int64_t)n_sm * kByteWarps;
+  const int64_t n_warps = (int64_t)n_sm * std::max(kByteWarps, kSpanWarps);
   unsigned long long* tile_state = nullptr;
   unsigned int* counters = nullptr;  // ScanStatus {total_hits, n_direct, bad_docs} | [4] ticket
   const int64_t n_groups = (fp.n_tiles + 31) / 32;
@@ -684,7 +696,7 @@ static int32_t run_fused(ScanParams p, ScanCall& c) {
   AHA_CUDA(ws->get(kWsTileState, state_words, &tile_state));
   AHA_CUDA(ws->get(kWsStatus, 8, &counters));
   if (p.mode & AHA_SEP) AHA_CUDA(ws->get(kWsScratch, (size_t)n_warps * 32 * kLaneCap, &fp.scratch));
-  else AHA_CUDA(ws->get(kWsEvScratch, (size_t)n_warps * 32 * kByteEvCap, &fp.ev_scratch));
+  else AHA_CUDA(ws->get(kWsEvScratch, (size_t)n_warps * 32 * (size_t)fp.ev_cap, &fp.ev_scratch));
   AHA_CUDA(ws->get(kWsMarks, (size_t)n_warps * 2 * 32 * kMarkCap, &fp.marks));
   int32_t rc = alloc_doc_hit_off(c, p.n_docs, &p.doc_hit_off);
   if (rc) return rc;

@@ -245,19 +245,6 @@ __global__ void __launch_bounds__(kFusedWarps * 32, 1) char_walk_kernel(const __
   }
 }
 
-// unit starts (non-continuation bytes) of text[from, to): byte head, aligned words, byte tail
-__device__ __forceinline__ uint32_t count_leads_global(const uint8_t* text, int64_t from, int64_t to) {
-  uint32_t c = 0;
-  int64_t i = from;
-  for (; i < to && (i & 3); ++i) c += ((__ldg(text + i) & 0xC0) != 0x80);
-  for (; i + 4 <= to; i += 4) {
-    const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(text + i));
-    c += 4u - (uint32_t)__popc(w & 0x80808080u & ~(w << 1));
-  }
-  for (; i < to; ++i) c += ((__ldg(text + i) & 0xC0) != 0x80);
-  return c;
-}
-
 // ---- 2. / 3. count and expansion: one warp per tile ---------------------------------------------------------------
 // An event's end offset = its tile-relative `rel` + the tile's base - the base of the document it lies in (bytes:
 // tile start / document start; characters: unit starts in front of the tile / in front of the document).  The

@@ -35,10 +35,15 @@ constexpr int kMarkCapC = 2;      // ... per sub-chunk (scan_char.cuh walks two 
 #define AHA_B200_CHAR_CHUNK 126
 #endif
 constexpr int kFusedWarps = AHA_B200_CHAR_WARPS;   // warps per CTA of scan_char_kernel (register- and shared-memory-bound)
+constexpr int kByteSpanDefault = 512;   // bytes per lane of the byte kernel's span mode (AHA_B200_BYTE_SPAN; 0 = staged tiles only); C3 GB/s: 256 -> 84.1, 512 -> 84.9, 768 -> 80.9, staged 73.3
 constexpr int kByteChunkDefault = 132;  // bytes per lane of the byte kernel (AHA_B200_BYTE_CHUNK overrides; see fused_geometry)
 #ifndef AHA_BYTE_WARPS
 #define AHA_BYTE_WARPS 32
 #endif
+#ifndef AHA_SPAN_WARPS
+#define AHA_SPAN_WARPS 32
+#endif
+constexpr int kSpanWarps = AHA_SPAN_WARPS;  // ... of its span mode (no shared memory: bounded by registers only)
 constexpr int kByteWarps = AHA_BYTE_WARPS;  // warps per CTA of scan_fused_kernel<ByteGlobal>: latency-bound on L2, so as many as fit
 
 struct FusedParams {
@@ -59,6 +64,8 @@ struct FusedParams {
   int2* marks;                     // [n_warps_total][32][kMarkCap] (doc index low/high packed, seq)
   unsigned int* n_direct;          // diagnostics: tiles that took the direct pass
   const uint64_t* tile_lead;       // [n_tiles + 1] non-continuation bytes before each tile (AHA_UNITS_CHAR)
+  int32_t span;                    // != 0: span mode of the byte kernel -- no staging, every lane reads its own `chunk` bytes from global memory
+  int32_t ev_cap;                  // events per lane slice of ev_scratch
 };
 
 // ---- PTX helpers ---------------------------------------------------------------------------------
@@ -128,11 +135,12 @@ struct DirectSink {
 // four dependent loads, and at one hit per 5-10 bytes some lane fires at nearly every step.
 struct EventSink {
   static constexpr bool kEvents = true;
-  uint2* ev;      // lane slot [kByteEvCap]
+  uint2* ev;      // lane slot [cap]
   int2* mark;     // lane slot [kMarkCap]: {document, events before it}
+  uint32_t cap = kByteEvCap;
   uint32_t n = 0, n_mark = 0;
   __device__ __forceinline__ void event(uint32_t state, int32_t end) {
-    if (n < (uint32_t)kByteEvCap) ev[n] = make_uint2(state, (uint32_t)end);
+    if (n < cap) ev[n] = make_uint2(state, (uint32_t)end);
     ++n;
   }
   __device__ __forceinline__ void hit(int32_t, int32_t, int32_t) {}
@@ -171,6 +179,37 @@ __device__ __forceinline__ void emit_list(const ScanParams& p, Sink& sink, uint3
 // edge if the row has it, else on to the fail link's row: the loop of ACX#match_ (ac.cr:179-190) itself.  A wide state
 // (numbered first: id < n_wide) owns a dense closure row and always answers with one 4-byte entry.  The dense table of
 // the 1 M-pattern dictionary is 3.1 GB (every lookup an HBM sector); its rows are 100 MB and stay in L2.
+// Where the walk reads its text.  StagedText: the warp's tile in shared memory (bulk copy).  SpanText: the lane's own span
+// straight from global memory, sixteen bytes at a time into registers (positions only ever grow): no shared memory, so
+// a lane's span can be a kilobyte long -- the warm-up in front of it is then 3 % of the walk instead of 23 % -- and the
+// SM's memory is L1 for the table lookups.
+struct StagedText {
+  const uint8_t* sbuf;
+  __device__ __forceinline__ uint32_t get(int32_t pos) { return sbuf[pos]; }
+};
+struct SpanText {
+  const uint8_t* base;   // text + buf_origin (16-byte aligned)
+  int32_t limit;         // bytes of text from base on
+  uint4 w;
+  int32_t wpos = -16;
+  __device__ __forceinline__ uint32_t get(int32_t pos) {
+    const int32_t blk = pos & ~15;
+    if (blk != wpos) {
+      wpos = blk;
+      if (blk + 16 <= limit) {
+        w = __ldg(reinterpret_cast<const uint4*>(base + blk));
+      } else {  // the last bytes of the text: never read past them
+        uint32_t t[4] = {0u, 0u, 0u, 0u};
+        for (int i = 0; i < 16 && blk + i < limit; ++i) t[i >> 2] |= (uint32_t)base[blk + i] << ((i & 3) * 8);
+        w = make_uint4(t[0], t[1], t[2], t[3]);
+      }
+    }
+    const uint32_t k = (uint32_t)pos & 15u;
+    const uint32_t x = (k & 8u) ? ((k & 4u) ? w.w : w.z) : ((k & 4u) ? w.y : w.x);
+    return (x >> ((k & 3u) * 8u)) & 0xFFu;
+  }
+};
+
 struct ByteGlobal {
   static constexpr int kExtraWarm = 0;
   const uint8_t* cmap_g;  // class map in global memory
@@ -187,8 +226,8 @@ struct ByteGlobal {
   // loop over bytes every byte would cost the warp the LONGEST fail chain of its 32 lanes, and with a branch per kind of
   // row the load latencies of the kinds would add up instead of overlapping.
   //   kDense: the automaton has a dense closure table (small dictionaries): every iteration consumes.
-  template <bool kDense, class Sink>
-  __device__ __forceinline__ void walk_impl(const FusedParams& P, const uint8_t* sbuf, int64_t buf_origin, int64_t a, int64_t b,
+  template <bool kDense, class Text, class Sink>
+  __device__ __forceinline__ void walk_impl(const FusedParams& P, Text text, int64_t buf_origin, int64_t a, int64_t b,
                                             uint32_t lead0, Sink& sink) const {
     const ScanParams& p = P.sp;
     int64_t d = last_le(p.doc_off, p.n_docs, a);
@@ -210,7 +249,7 @@ struct ByteGlobal {
       const int32_t seg_end = (int32_t)(min(b, doc_end) - buf_origin);
       const int32_t end_base = (int32_t)(buf_origin - doc_start) + 1;  // end offset in the document = pos + end_base
       while (pos < seg_end) {
-        const uint32_t byte = sbuf[pos];
+        const uint32_t byte = text.get(pos);
         const uint32_t cls = cmap[byte];
         uint32_t e, fail = 0;
         bool consume;
@@ -254,12 +293,21 @@ struct ByteGlobal {
       doc_end = p.doc_off[d + 1];
     }
   }
-  template <class Sink>
+  template <bool kSpan = false, class Sink>
   __device__ __forceinline__ void walk(const FusedParams& P, const uint8_t* sbuf, int64_t buf_origin, int64_t a, int64_t b,
                                        uint32_t lead0, Sink& sink) const {
     if (a >= b) return;
-    if (P.sp.delta) walk_impl<true>(P, sbuf, buf_origin, a, b, lead0, sink);
-    else walk_impl<false>(P, sbuf, buf_origin, a, b, lead0, sink);
+    if (kSpan) {  // sbuf is not used: the lane reads its span from global memory
+      SpanText t;
+      t.base = P.sp.text + buf_origin;
+      t.limit = (int32_t)min(P.sp.total - buf_origin, (int64_t)0x7FFFFFF0);
+      if (P.sp.delta) walk_impl<true>(P, t, buf_origin, a, b, lead0, sink);
+      else walk_impl<false>(P, t, buf_origin, a, b, lead0, sink);
+      return;
+    }
+    StagedText t{sbuf};
+    if (P.sp.delta) walk_impl<true>(P, t, buf_origin, a, b, lead0, sink);
+    else walk_impl<false>(P, t, buf_origin, a, b, lead0, sink);
   }
 };
 
@@ -275,6 +323,19 @@ __device__ __forceinline__ uint32_t count_leads_smem(const uint8_t* sbuf, int64_
     c += 4u - (uint32_t)__popc(w & 0x80808080u & ~(w << 1));
   }
   for (; i < e; ++i) c += ((sbuf[i] & 0xC0) != 0x80);
+  return c;
+}
+
+// unit starts (non-continuation bytes) of text[from, to): byte head, aligned words, byte tail
+__device__ __forceinline__ uint32_t count_leads_global(const uint8_t* text, int64_t from, int64_t to) {
+  uint32_t c = 0;
+  int64_t i = from;
+  for (; i < to && (i & 3); ++i) c += ((__ldg(text + i) & 0xC0) != 0x80);
+  for (; i + 4 <= to; i += 4) {
+    const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(text + i));
+    c += 4u - (uint32_t)__popc(w & 0x80808080u & ~(w << 1));
+  }
+  for (; i < to; ++i) c += ((__ldg(text + i) & 0xC0) != 0x80);
   return c;
 }
 
@@ -343,8 +404,8 @@ __device__ unsigned long long g_phase_cycles[8];
 #define AHA_PHASE_FLUSH
 #endif
 
-template <class Policy, bool EV>
-__global__ void __launch_bounds__(kByteWarps * 32, 1) scan_fused_kernel(const FusedParams P, const Policy policy_in) {
+template <class Policy, bool EV, bool kSpan = false>
+__global__ void __launch_bounds__((kSpan ? kSpanWarps : kByteWarps) * 32, 1) scan_fused_kernel(const FusedParams P, const Policy policy_in) {
   extern __shared__ __align__(128) uint8_t smem[];
   const ScanParams& p = P.sp;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -360,7 +421,7 @@ __global__ void __launch_bounds__(kByteWarps * 32, 1) scan_fused_kernel(const Fu
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   __syncthreads();
 
-  const int64_t gwarp = (int64_t)blockIdx.x * kByteWarps + warp;
+  const int64_t gwarp = (int64_t)blockIdx.x * (kSpan ? kSpanWarps : kByteWarps) + warp;
   aha_hit* my_rec = P.scratch + (gwarp * 32 + lane) * kLaneCap;
   int2* my_mark = P.marks + (gwarp * 32 + lane) * kMarkCap;
   uint32_t parity = 0;
@@ -377,16 +438,18 @@ __global__ void __launch_bounds__(kByteWarps * 32, 1) scan_fused_kernel(const Fu
     const int64_t origin = max((int64_t)0, tile_start - (int64_t)P.w16);
     const int64_t want_end = min(p.total, tile_end + 1);              // +1: right neighbour for the sep test
     const int64_t bulk_end = origin + ((want_end - origin) & ~(int64_t)15);
-    if (lane == 0) {
-      if (bulk_end > origin) {
-        mbar_expect_tx(bar, (uint32_t)(bulk_end - origin));
-        bulk_g2s(sbuf, p.text + origin, (uint32_t)(bulk_end - origin), bar);
+    if (!kSpan) {
+      if (lane == 0) {
+        if (bulk_end > origin) {
+          mbar_expect_tx(bar, (uint32_t)(bulk_end - origin));
+          bulk_g2s(sbuf, p.text + origin, (uint32_t)(bulk_end - origin), bar);
+        }
       }
-    }
-    for (int64_t i = bulk_end + lane; i < want_end; i += 32) sbuf[i - origin] = p.text[i];
-    if (bulk_end > origin) {
-      mbar_wait(bar, parity);
-      parity ^= 1u;
+      for (int64_t i = bulk_end + lane; i < want_end; i += 32) sbuf[i - origin] = p.text[i];
+      if (bulk_end > origin) {
+        mbar_wait(bar, parity);
+        parity ^= 1u;
+      }
     }
     __syncwarp();
     AHA_PHASE(0)  // ticket + staging
@@ -397,7 +460,7 @@ __global__ void __launch_bounds__(kByteWarps * 32, 1) scan_fused_kernel(const Fu
     uint32_t lead0 = 0;
     if (p.mode & AHA_UNITS_CHAR) {
       // per-lane count of its own chunk, exclusive warp scan, plus the tile prefix, minus the document base
-      uint32_t mine = count_leads_smem(sbuf, origin, a, b);
+      uint32_t mine = kSpan ? count_leads_global(p.text, a, b) : count_leads_smem(sbuf, origin, a, b);
       uint32_t incl = mine;
       for (int o = 1; o < 32; o <<= 1) {
         uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
@@ -413,15 +476,16 @@ __global__ void __launch_bounds__(kByteWarps * 32, 1) scan_fused_kernel(const Fu
     if constexpr (EV) {
       // ---- event mode: walk (one dependent table load per byte, nothing else), count, look-back, expand in place
       const bool chars = (p.mode & AHA_UNITS_CHAR) != 0;
-      uint2* my_ev = P.ev_scratch + (gwarp * 32 + lane) * kByteEvCap;
+      uint2* my_ev = P.ev_scratch + (gwarp * 32 + lane) * (int64_t)P.ev_cap;
       EventSink es;
       es.ev = my_ev;
       es.mark = my_mark;
-      policy.walk(P, sbuf, origin, a, b, lead0, es);
+      es.cap = (uint32_t)P.ev_cap;
+      policy.template walk<kSpan>(P, sbuf, origin, a, b, lead0, es);
       __syncwarp();
       AHA_PHASE(1)  // walk
       const uint32_t ne = es.n, nm = es.n_mark;
-      const bool any_over = __any_sync(0xffffffffu, ne > (uint32_t)kByteEvCap || nm > (uint32_t)kMarkCap);
+      const bool any_over = __any_sync(0xffffffffu, ne > (uint32_t)P.ev_cap || nm > (uint32_t)kMarkCap);
       uint32_t n_lane = 0;
       if (!any_over) {
         for (uint32_t k0 = 0; k0 < ne; k0 += 4) {  // list lengths of four events at a time: independent loads
@@ -438,7 +502,7 @@ __global__ void __launch_bounds__(kByteWarps * 32, 1) scan_fused_kernel(const Fu
         }
       } else {
         TallySink ts;
-        policy.walk(P, sbuf, origin, a, b, lead0, ts);
+        policy.template walk<kSpan>(P, sbuf, origin, a, b, lead0, ts);
         n_lane = ts.n;
       }
       uint32_t incl = n_lane;
@@ -503,13 +567,13 @@ __global__ void __launch_bounds__(kByteWarps * 32, 1) scan_fused_kernel(const Fu
         ds.doc_hit_off = p.doc_hit_off;
         ds.idx = (int64_t)(prefix + excl_lane);
         ds.cap = P.hit_cap;
-        policy.walk(P, sbuf, origin, a, b, lead0, ds);
+        policy.template walk<kSpan>(P, sbuf, origin, a, b, lead0, ds);
       }
     } else {
       ScratchSink ss;
       ss.rec = my_rec;
       ss.mark = my_mark;
-      policy.walk(P, sbuf, origin, a, b, lead0, ss);
+      policy.template walk<kSpan>(P, sbuf, origin, a, b, lead0, ss);
 
       // ---- warp prefix of lane counts, tile aggregate
       uint32_t incl = ss.n;
@@ -554,7 +618,7 @@ __global__ void __launch_bounds__(kByteWarps * 32, 1) scan_fused_kernel(const Fu
         ds.doc_hit_off = p.doc_hit_off;
         ds.idx = (int64_t)(prefix + excl_lane);
         ds.cap = P.hit_cap;
-        policy.walk(P, sbuf, origin, a, b, lead0, ds);
+        policy.template walk<kSpan>(P, sbuf, origin, a, b, lead0, ds);
       }
     }
     __syncwarp();

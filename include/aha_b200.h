@@ -154,7 +154,8 @@ int32_t aha_b200_scan_device_noalloc(const aha_dfa* d, const void* dev_text, con
 /* ---- diagnostics ------------------------------------------------------------------------- */
 /* Test knobs (also read once from the environment): 0 = AHA_B200_NO_CHAR (byte automaton even when
  * the character tables fit shared memory), 1 = two-pass checker kernels (AHA_B200_IMPL=0; otherwise
- * only the path of keys > 1024 bytes), 2 = AHA_B200_BYTE_CHUNK, 3 = AHA_B200_E2E_CHUNK_MB.      */
+ * only the path of keys > 1024 bytes), 2 = AHA_B200_BYTE_CHUNK, 3 = AHA_B200_E2E_CHUNK_MB,
+ * 4 = AHA_B200_BYTE_SPAN (bytes per lane of the byte kernel's span mode, 0 = off, -1 = default). */
 int32_t aha_b200_debug_set(int32_t knob, int32_t value);
 /* Host-side replay of the shared-memory character automaton the fused kernel uses (same table builder,
  * same per-lane walk, lanes emulated sequentially with `chunk`-byte owned regions) over ONE document.

@@ -14,22 +14,26 @@ from tests.test_oracle_kat import _rand_keys
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(autouse=True, params=["default", "byte", "two-pass"])
+@pytest.fixture(autouse=True, params=["default", "byte", "two-pass", "span"])
 def scan_impl(request):
     """every parity test runs against the default device path (character automaton in shared memory where the
     dictionary allows: walk / scan / expand kernels, else the fused byte-automaton kernel), the fused kernel forced to
-    the byte automaton, and the two-pass checker kernels (the path of keys > 1024 bytes); the heavy full-size tests
-    run on the default path only.  The knobs are test hooks of the C ABI (aha_b200_debug_set), not product switches."""
+    the byte automaton (once with staged tiles / the default span, once with 64-byte spans read from global memory), and
+    the two-pass checker kernels (the path of keys > 1024 bytes); the heavy full-size tests run on the default path only.  The knobs are test hooks of the C ABI (aha_b200_debug_set), not product switches."""
     from aha_b200 import _lib
     heavy = request.node.get_closest_marker("heavy") is not None
     if heavy and request.param != "default":
         pytest.skip("full-size test: default path only")
     L = _lib.lib()
-    L.aha_b200_debug_set(0, 1 if request.param == "byte" else 0)
+    L.aha_b200_debug_set(0, 1 if request.param in ("byte", "span") else 0)
     L.aha_b200_debug_set(1, 1 if request.param == "two-pass" else 0)
+    # "span": the byte kernel's span mode with 64-byte spans, so that batches of small documents (average >= 256 bytes)
+    # exercise it too; the other runs keep the default span, which only engages for documents of kilobytes
+    L.aha_b200_debug_set(4, 64 if request.param == "span" else -1)
     yield request.param
     L.aha_b200_debug_set(0, 0)
     L.aha_b200_debug_set(1, 0)
+    L.aha_b200_debug_set(4, -1)
 
 
 def as_tuples(h):

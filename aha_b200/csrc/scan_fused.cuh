@@ -180,13 +180,40 @@ __device__ __forceinline__ void emit_list(const ScanParams& p, Sink& sink, uint3
 // (numbered first: id < n_wide) owns a dense closure row and always answers with one 4-byte entry.  The dense table of
 // the 1 M-pattern dictionary is 3.1 GB (every lookup an HBM sector); its rows are 100 MB and stay in L2.
 // Where the walk reads its text.  StagedText: the warp's tile in shared memory (bulk copy).  SpanText: the lane's own span
-// straight from global memory, sixteen bytes at a time into registers (positions only ever grow): no shared memory, so
+// straight from global memory, eight (or sixteen) bytes at a time into registers (positions only ever grow): no shared memory, so
 // a lane's span can be a kilobyte long -- the warm-up in front of it is then 3 % of the walk instead of 23 % -- and the
 // SM's memory is L1 for the table lookups.
 struct StagedText {
   const uint8_t* sbuf;
   __device__ __forceinline__ uint32_t get(int32_t pos) { return sbuf[pos]; }
 };
+#ifndef AHA_SPAN_WIN8
+#define AHA_SPAN_WIN8 1   // 1: an 8-byte window (two registers less, twice the text loads): C3 86.0 against 84.8 GB/s with 16 bytes
+#endif
+#if AHA_SPAN_WIN8
+struct SpanText {
+  const uint8_t* base;
+  int32_t limit;
+  uint2 w;
+  int32_t wpos = -8;
+  __device__ __forceinline__ uint32_t get(int32_t pos) {
+    const int32_t blk = pos & ~7;
+    if (blk != wpos) {
+      wpos = blk;
+      if (blk + 8 <= limit) {
+        w = __ldg(reinterpret_cast<const uint2*>(base + blk));
+      } else {
+        uint32_t t[2] = {0u, 0u};
+        for (int i = 0; i < 8 && blk + i < limit; ++i) t[i >> 2] |= (uint32_t)base[blk + i] << ((i & 3) * 8);
+        w = make_uint2(t[0], t[1]);
+      }
+    }
+    const uint32_t k = (uint32_t)pos & 7u;
+    const uint32_t x = (k & 4u) ? w.y : w.x;
+    return (x >> ((k & 3u) * 8u)) & 0xFFu;
+  }
+};
+#else
 struct SpanText {
   const uint8_t* base;   // text + buf_origin (16-byte aligned)
   int32_t limit;         // bytes of text from base on
@@ -209,6 +236,7 @@ struct SpanText {
     return (x >> ((k & 3u) * 8u)) & 0xFFu;
   }
 };
+#endif
 
 struct ByteGlobal {
   static constexpr int kExtraWarm = 0;

@@ -553,7 +553,9 @@ static int32_t run_char_split(ScanParams p, ScanCall& c) {
   static std::once_flag attr_once[64];
   cudaError_t attr_err = cudaSuccess;
   std::call_once(attr_once[c.dd->device & 63], [&] {
-    attr_err = cudaFuncSetAttribute(char_walk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    attr_err = cudaFuncSetAttribute(char_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(char_walk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (attr_err == cudaSuccess)
       attr_err = cudaFuncSetAttribute(char_walk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   });
@@ -589,7 +591,7 @@ static int32_t run_char_split(ScanParams p, ScanCall& c) {
       char_expand_kernel<true, true><<<grid, 256, 0, st>>>(sp);
     } else {
       const unsigned grid = (unsigned)std::min<int64_t>((nt + 7) / 8, (int64_t)n_sm * 8);
-      char_count_kernel<<<grid, 256, (size_t)h.n_mwords * 4, st>>>(sp);
+      char_count_kernel<<<grid, 256, (size_t)h.n_mwords * 16, st>>>(sp);  // one byte per ref (<= 64 KB)
     }
     count_launch();
   }

@@ -115,8 +115,22 @@ static int32_t build_hot_table(const aha_dfa* d, DeviceDfa* dd) {
     }
   }
   h.off_ref8 = place(cursor, ref8.size() * sizeof(uint2));
+  // every entry of the output lists in the same 8 bytes {key id, key length << 16 | characters after the first}: a list of
+  // several keys is then expanded with one load per hit instead of out_val[] -> key_len[]
+  const DfaView hv = view_of(d->header, d->blob.data());
+  std::vector<uint2> out8(hv.n_out);
+  for (uint64_t j = 0; j < hv.n_out; ++j) {
+    const int32_t v = hv.out_val[j];
+    if (v < 0 || (uint64_t)v >= hv.n_keys || hv.key_len[v] >= 0x8000u || hv.key_tail[v] >= 0x10000u) {
+      ref8_ok = false;
+      break;
+    }
+    out8[j] = make_uint2((uint32_t)v, (hv.key_len[v] << 16) | hv.key_tail[v]);
+  }
+  h.off_out8 = place(cursor, (out8.size() + 1) * sizeof(uint2));
   std::vector<uint8_t> stage(cursor, 0);
   memcpy(stage.data() + h.off_ref8, ref8.data(), ref8.size() * sizeof(uint2));
+  if (!out8.empty()) memcpy(stage.data() + h.off_out8, out8.data(), out8.size() * sizeof(uint2));
   if (!ref8_ok) return AHA_OK;  // a key longer than 32 KB: the byte automaton serves this dictionary (h.ok stays false)
   h.n_ref8 = (uint32_t)ref8.size();
   memcpy(stage.data() + h.off_root, T.root.data(), T.root.size() * 2);

@@ -48,7 +48,7 @@ struct HotTable {
   uint32_t n_root = 0, m = 0, m_pad = 0, n_mwords = 0, n_gfail_s = 0;
   uint32_t lo[3] = {0, 0, 0}, n[3] = {0, 0, 0}, off[3] = {0, 0, 0};
   uint8_t* dev = nullptr;     // one allocation: root | val | check | gfail | ref_rec | mbits
-  size_t off_root = 0, off_val = 0, off_check = 0, off_gfail = 0, off_ref = 0, off_mbits = 0, off_ref8 = 0;
+  size_t off_root = 0, off_val = 0, off_check = 0, off_gfail = 0, off_ref = 0, off_mbits = 0, off_ref8 = 0, off_out8 = 0;
   uint32_t n_ref8 = 0;        // entries of the 8-byte ref table
   size_t smem_bytes = 0;
 };

@@ -540,6 +540,7 @@ static int32_t run_char_split(ScanParams p, ScanCall& c) {
   sp.mbits_g = reinterpret_cast<const uint32_t*>(h.dev + h.off_mbits);
   sp.ref8_g = reinterpret_cast<const uint2*>(h.dev + h.off_ref8);
   sp.n_ref8 = h.n_ref8;
+  sp.out8_g = reinterpret_cast<const uint2*>(h.dev + h.off_out8);
   int32_t rc = alloc_doc_hit_off(c, p.n_docs, &p.doc_hit_off);
   if (rc) return rc;
   int64_t cap = 0;

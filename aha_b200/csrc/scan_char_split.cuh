@@ -52,6 +52,7 @@ struct SplitParams {
   const uint32_t* mbits_g;   // 2 bits per ref: hits it expands to when 1..3, 0 = see ref_rec[ref].n
   const uint2* ref8_g;       // [n_ref8] ref_rec in 8 bytes (see char_expand_kernel)
   uint32_t n_ref8;
+  const uint2* out8_g;       // [n_out] every output-list entry as {key id, key length << 16 | characters after the first}
   uint32_t* direct_list;     // [n_tiles] tiles for char_direct_kernel
   ScanStatus* status;        // total_hits, n_direct (= length of direct_list), bad_docs
 };
@@ -439,7 +440,7 @@ __global__ void __launch_bounds__(256, 4) char_expand_kernel(const __grid_consta
         } else {
           uint32_t keep = 0;
           for (uint32_t j = r8.x; j < r8.x + n; ++j) {
-            const int64_t start = abs_end - (int64_t)p.key_len[p.out_val[j]];
+            const int64_t start = abs_end - (int64_t)(Q.out8_g[j].y >> 16);
             keep += (start > my_lo && sep_rejects(p, __ldg(p.text + start - 1))) ? 0u : 1u;
           }
           n = keep;
@@ -475,17 +476,18 @@ __global__ void __launch_bounds__(256, 4) char_expand_kernel(const __grid_consta
         } else if (kSep) {
           const uint32_t n_all = r8.y & 0x7FFFFFFFu;
           for (uint32_t j = r8.x; j < r8.x + n_all; ++j) {
-            const int32_t v = p.out_val[j];
-            const int32_t len = (int32_t)p.key_len[v];
+            const uint2 o = Q.out8_g[j];
+            const int32_t v = (int32_t)o.x, len = (int32_t)(o.y >> 16);
             const int64_t start = abs_end - len;
             if (start > my_lo && sep_rejects(p, __ldg(p.text + start - 1))) continue;
-            if (at < F.hit_cap) p.hits[at] = sep_chars ? aha_hit{end_char - 1 - (int32_t)p.key_tail[v], end_char, v} : aha_hit{end - len, end, v};
+            if (at < F.hit_cap) p.hits[at] = sep_chars ? aha_hit{end_char - 1 - (int32_t)(o.y & 0xFFFFu), end_char, v} : aha_hit{end - len, end, v};
             ++at;
           }
         } else {
           for (uint32_t j = r8.x; j < r8.x + n; ++j, ++at) {
-            const int32_t v = p.out_val[j];
-            if (at < F.hit_cap) p.hits[at] = chars ? aha_hit{end - 1 - (int32_t)p.key_tail[v], end, v} : aha_hit{end - (int32_t)p.key_len[v], end, v};
+            const uint2 o = Q.out8_g[j];
+            if (at < F.hit_cap)
+              p.hits[at] = chars ? aha_hit{end - 1 - (int32_t)(o.y & 0xFFFFu), end, (int32_t)o.x} : aha_hit{end - (int32_t)(o.y >> 16), end, (int32_t)o.x};
           }
         }
       }

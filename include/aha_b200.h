@@ -95,7 +95,8 @@ void aha_b200_builder_free(aha_builder* b);
 
 /* ---- automaton --------------------------------------------------------------------------- */
 /* Flattens the arrays of a compiled Aha::AC (@da.array, @fails, @output, @key_lens: ac.cr:35-39,
- * cedar.cr:29-36,147-148) into the dense byte-class DFA and uploads it to every selected device. */
+ * cedar.cr:29-36,147-148) into the automaton blob (sparse 16-byte rows, closure rows for the wide
+ * states, a dense table only while it stays small) and uploads it to every selected device.        */
 int32_t aha_b200_dfa_from_cedar(const void* nodes, int64_t array_size, const int32_t* fails, const int32_t* output,
                                 const uint32_t* key_lens, int64_t n_keys, aha_dfa** out);
 /* Aha::AC.compile(keys) (ac.cr:62-69) in one call: keys concatenated, key_off has n_keys+1 entries.
@@ -112,7 +113,8 @@ int32_t aha_b200_dfa_from_blob(const uint8_t* blob, int64_t bytes, aha_dfa** out
 /* rebuild from a blob already resident on the current device (after ncclBroadcast) */
 int32_t aha_b200_dfa_from_device_blob(const void* dev_blob, int64_t bytes, aha_dfa** out);
 /* info: 0 n_states, 1 n_classes, 2 n_keys, 3 max_key_len, 4 n_out_entries, 5 blob bytes,
- *       6 hot states resident in shared memory, 7 entry width of the global table in bytes   */
+ *       6 states of the character automaton resident in shared memory (0: byte path),
+ *       7 entry width of the global table in bytes                                           */
 int64_t aha_b200_dfa_info(const aha_dfa* d, int32_t what);
 void aha_b200_dfa_free(aha_dfa* d);
 

@@ -170,6 +170,21 @@ static int32_t upload(aha_dfa* d) {
     AHA_CUDA(cudaMalloc(&dd.blob, d->blob.size()));
     AHA_CUDA(cudaMemcpy(dd.blob, d->blob.data(), d->blob.size(), cudaMemcpyHostToDevice));
     dd.view = view_of(d->header, dd.blob);
+    {
+      // the output lists as {key id, length << 16 | tail characters}: one load per hit in the byte path's expansion
+      const DfaView hv = view_of(d->header, d->blob.data());
+      std::vector<uint2> out8(hv.n_out + 1);
+      bool fits = true;
+      for (uint64_t j = 0; j < hv.n_out && fits; ++j) {
+        const int32_t v = hv.out_val[j];
+        fits = v >= 0 && (uint64_t)v < hv.n_keys && hv.key_len[v] < 0x10000u && hv.key_tail[v] < 0x10000u;
+        if (fits) out8[j] = make_uint2((uint32_t)v, (hv.key_len[v] << 16) | hv.key_tail[v]);
+      }
+      if (fits) {
+        AHA_CUDA(cudaMalloc(&dd.out8, out8.size() * sizeof(uint2)));
+        AHA_CUDA(cudaMemcpy(dd.out8, out8.data(), out8.size() * sizeof(uint2), cudaMemcpyHostToDevice));
+      }
+    }
     rc = build_hot_table(d, &dd);
     if (rc) return rc;
   }
@@ -185,6 +200,7 @@ static void free_dfa(aha_dfa* d) {
     if (dd.blob) cudaFree(dd.blob);
     if (dd.hot.dev) cudaFree(dd.hot.dev);
     if (dd.folded_dev) cudaFree(dd.folded_dev);
+    if (dd.out8) cudaFree(dd.out8);
   }
   delete d;
 }

@@ -151,6 +151,7 @@ struct DeviceDfa {
   uint8_t* blob = nullptr;  // device copy of the whole blob
   DfaView view;             // device pointers
   HotTable hot;
+  uint2* out8 = nullptr;    // device: the output lists in 8 bytes per entry (byte-path expansion); NULL when a key does not fit
   // scan workspaces that are not in use (guarded by pool_mu of the owning aha_dfa)
   std::vector<std::unique_ptr<Workspace>> idle;
   double hits_per_byte = -1.0;  // largest hit density seen so far on this device: sizes the hit buffer up front

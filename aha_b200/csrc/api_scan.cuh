@@ -180,6 +180,7 @@ static void fill_params(ScanParams* p, const DeviceDfa* dd, const void* dev_text
   p->out_val = dd->view.out_val;
   p->key_len = dd->view.key_len;
   p->key_tail = dd->view.key_tail;
+  p->out8 = dd->out8;
   p->C = dd->view.n_classes;
   p->warm = dd->view.max_key_len > 0 ? dd->view.max_key_len - 1 : 0;
   p->mode = mode;

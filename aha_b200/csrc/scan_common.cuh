@@ -24,6 +24,8 @@ struct ScanParams {
   const int32_t* out_val;
   const uint32_t* key_len;
   const uint32_t* key_tail;
+  const uint2* out8;         // [n_out] output-list entries as {key id, key length << 16 | characters after the first}; NULL:
+                             // a key too long for the packing (the lists are then read through out_val / key_len / key_tail)
   uint32_t C;
   uint32_t warm;             // max_key_len - 1 bytes of warm-up before an owned region
   uint32_t mode;

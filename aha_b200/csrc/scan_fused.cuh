@@ -564,7 +564,14 @@ __global__ void __launch_bounds__((kSpan ? kSpanWarps : kByteWarps) * 32, 1) sca
               cnt[u] = __ldg(p.out_off + e[u].x + 1) - j0[u];
             }
           }
-          if (out) {
+          if (out && p.out8) {  // one 8-byte record per list entry: key id and both lengths
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const uint2 o = cnt[u] ? __ldg(p.out8 + j0[u]) : make_uint2(0u, 0u);
+              v0[u] = (int32_t)o.x;
+              kl[u] = chars ? (o.y & 0xFFFFu) : (o.y >> 16);
+            }
+          } else if (out) {
 #pragma unroll
             for (int u = 0; u < 4; ++u) v0[u] = cnt[u] ? __ldg(p.out_val + j0[u]) : 0;
 #pragma unroll
@@ -578,8 +585,15 @@ __global__ void __launch_bounds__((kSpan ? kSpanWarps : kByteWarps) * 32, 1) sca
                 const int32_t end = (int32_t)e[u].y;
                 if (idx < P.hit_cap) out[idx] = chars ? aha_hit{end - 1 - (int32_t)kl[u], end, v0[u]} : aha_hit{end - (int32_t)kl[u], end, v0[u]};
                 for (uint32_t j = 1; j < cnt[u]; ++j) {
-                  const int32_t v = __ldg(p.out_val + j0[u] + j);
-                  const int32_t l = (int32_t)(chars ? __ldg(p.key_tail + v) : __ldg(p.key_len + v));
+                  int32_t v, l;
+                  if (p.out8) {
+                    const uint2 o = __ldg(p.out8 + j0[u] + j);
+                    v = (int32_t)o.x;
+                    l = (int32_t)(chars ? (o.y & 0xFFFFu) : (o.y >> 16));
+                  } else {
+                    v = __ldg(p.out_val + j0[u] + j);
+                    l = (int32_t)(chars ? __ldg(p.key_tail + v) : __ldg(p.key_len + v));
+                  }
                   if (idx + j < P.hit_cap) out[idx + j] = chars ? aha_hit{end - 1 - l, end, v} : aha_hit{end - l, end, v};
                 }
               }

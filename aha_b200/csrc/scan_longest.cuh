@@ -23,8 +23,14 @@
 
 namespace aha {
 
-constexpr int kLongChunk = 512;  // bytes per thread
-constexpr int kLongWarm = 96;    // bytes of speculative run-up in front of a chunk
+#ifndef AHA_LONG_CHUNK
+#define AHA_LONG_CHUNK 512
+#endif
+#ifndef AHA_LONG_WARM
+#define AHA_LONG_WARM 96
+#endif
+constexpr int kLongChunk = AHA_LONG_CHUNK;  // bytes per thread
+constexpr int kLongWarm = AHA_LONG_WARM;    // bytes of speculative run-up in front of a chunk
 
 struct alignas(16) LongState {
   uint32_t s;       // automaton state

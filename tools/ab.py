@@ -28,7 +28,7 @@ def main():
             print("build", tag, flags, flush=True)
             _lib.build(out=so(tag), extra_flags=flags)
         return
-    workload, reps, nbytes, steps = "c2", 2, "0", "20"
+    workload, reps, nbytes, steps, mode = "c2", 2, "0", "20", "match"
     while args and args[0].startswith("--"):
         if args[0] == "--workload":
             workload = args[1]
@@ -38,18 +38,21 @@ def main():
             nbytes = args[1]
         elif args[0] == "--steps":
             steps = args[1]
+        elif args[0] == "--mode":
+            mode = args[1]
         args = args[2:]
     for rep in range(reps):
         for tag in args:
             env = dict(os.environ, AHA_B200_SO=so(tag))
             out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--workload", workload, "--bytes", nbytes, "--steps", steps, "--warmup", "3",
-                                  "--no-cpu", "--e2e-steps", "0"], env=env, capture_output=True, text=True)
+                                  "--no-cpu", "--e2e-steps", "0", "--mode", mode], env=env, capture_output=True, text=True)
             try:
                 d = json.loads(out.stdout.strip().splitlines()[-1])
                 r = d["per_rank"][0]
+                med = lambda k: (r.get(k) or {}).get("median") or 0.0
                 print("%-12s %7.1f GB/s  step %.3f  scan %.3f  walk %.3f  expand %.3f  gap %.3f  hits %d" % (
-                    tag, d["value"], d["ms_per_step"], r["scan_ms"]["median"], r["walk_ms"]["median"], r["expand_ms"]["median"],
-                    r["host_gap_ms"]["median"], d["config"]["hits_per_gpu_step"]), flush=True)
+                    tag, d["value"], d["ms_per_step"], med("scan_ms"), med("walk_ms"), med("expand_ms"),
+                    med("host_gap_ms"), d["config"]["hits_per_gpu_step"]), flush=True)
             except Exception:
                 print(tag, "FAILED", out.stderr[-600:], flush=True)
 

@@ -71,7 +71,7 @@ EXPORTS = [
     "aha_b200_dfa_blob", "aha_b200_dfa_from_blob", "aha_b200_dfa_from_device_blob", "aha_b200_dfa_info",
     "aha_b200_dfa_free", "aha_b200_scan", "aha_b200_scan_device", "aha_b200_hits_free",
     "aha_b200_gen_text_host", "aha_b200_gen_text_device", "aha_b200_debug_char_scan", "aha_b200_debug_set",
-    "aha_b200_scan_device_noalloc",
+    "aha_b200_scan_device_noalloc", "aha_b200_debug_folded_longest",
 ]
 
 _lib = None
@@ -113,6 +113,7 @@ def lib():
     L.aha_b200_hits_free.argtypes = [P(Hits)]
     L.aha_b200_hits_free.restype = None
     L.aha_b200_debug_char_scan.argtypes = [vp, i64, vp, i64, i32, i64, vp, i64, P(i64), P(i64)]
+    L.aha_b200_debug_folded_longest.argtypes = [vp, i64, vp, i64, u32, C.c_char_p, i32, vp, i64, P(i64), P(i64)]
     L.aha_b200_debug_set.argtypes = [i32, i32]
     L.aha_b200_gen_text_host.argtypes = [i32, u64, i64, i64, vp]
     L.aha_b200_gen_text_device.argtypes = [i32, u64, i64, i64, vp, vp]

@@ -432,6 +432,121 @@ int32_t aha_b200_debug_char_scan(const uint8_t* blob, int64_t blob_bytes, const 
   return AHA_OK;
 }
 
+// Host replay of trie_folded_doc_kernel (scan_trie.cuh) over one document: the same folded trie, the same flat state
+// machine, the same candidate pick -- so that the builder's claim (one folded node = the whole frontier of
+// cedar.cr:993-1019, first-of-longest = smallest mask distance) is checked against the oracle without a device.
+int32_t aha_b200_debug_folded_longest(const uint8_t* blob, int64_t blob_bytes, const uint8_t* text, int64_t n64, uint32_t mode,
+                                      const uint8_t* sep_bits, int32_t sep_size, aha_hit* hits, int64_t cap, int64_t* n_hits,
+                                      int64_t* info) {
+  if (!blob || !n_hits || !info || n64 < 0 || n64 > INT32_MAX - 64 || (n64 && !text)) return set_err(AHA_ERR_ARG, "bad argument");
+  if ((mode & AHA_SEP) && (!sep_bits || sep_size < 0 || sep_size > 256)) return set_err(AHA_ERR_ARG, "bad separator set");
+  BlobHeader h;
+  std::string err;
+  if (!parse_blob(blob, blob_bytes, &h, &err)) return set_err(AHA_ERR_ARG, err);
+  memset(info, 0, 8 * sizeof(int64_t));
+  *n_hits = 0;
+  const FoldedTrieHost F = build_folded_trie(h, blob);
+  if (!F.ok) return set_err(AHA_OK, "no folded trie for this dictionary");
+  info[0] = 1; info[1] = F.n_states; info[2] = F.n_classes; info[3] = F.max_chars; info[4] = (int64_t)F.cand.size();
+  for (uint32_t i = 0; i < F.n_states; ++i) info[5] += F.rec[(size_t)i * 8] == 0xFFFFFFFFu;
+  const bool use_sep = (mode & AHA_SEP) != 0;
+  auto sep_at = [&](uint32_t c) { return c < 256u && (int32_t)c < sep_size && ((sep_bits[c >> 3] >> (c & 7u)) & 1u); };
+  const int32_t n = (int32_t)n64;
+  const uint8_t* s = text;
+  auto decode = [&](int32_t i, uint32_t* cp) -> int {  // utf8_decode32
+    const uint32_t b = s[i];
+    if (b < 0x80) { *cp = b; return 1; }
+    if ((b & 0xE0) == 0xC0 && i + 1 < n) { *cp = ((b & 0x1F) << 6) | (s[i + 1] & 0x3F); return 2; }
+    if ((b & 0xF0) == 0xE0 && i + 2 < n) { *cp = ((b & 0x0F) << 12) | ((s[i + 1] & 0x3F) << 6) | (s[i + 2] & 0x3F); return 3; }
+    if ((b & 0xF8) == 0xF0 && i + 3 < n) {
+      *cp = ((b & 0x07) << 18) | ((s[i + 1] & 0x3F) << 12) | ((s[i + 2] & 0x3F) << 6) | (s[i + 3] & 0x3F);
+      return 4;
+    }
+    *cp = b;
+    return 1;
+  };
+  auto pick = [&](uint32_t nd, uint64_t window) -> int32_t {  // folded_pick
+    const uint32_t* r = &F.rec[(size_t)nd * 8];
+    int32_t best_v = (int32_t)r[1];
+    if (r[0] != 0xFFFFFFFFu) {
+      const uint32_t w = (uint32_t)window;
+      uint32_t bx = r[4] ^ w;
+      if (r[0] > 1u && (r[5] ^ w) < bx) { bx = r[5] ^ w; best_v = (int32_t)r[2]; }
+      if (r[0] > 2u && (r[6] ^ w) < bx) best_v = (int32_t)r[3];
+    } else {
+      uint64_t best_x = ~0ull;
+      for (uint32_t j = F.cand_off[nd]; j < F.cand_off[nd + 1]; ++j) {
+        const uint64_t x = F.cand[j].mask ^ window;
+        if (x < best_x || j == F.cand_off[nd]) { best_x = x; best_v = F.cand[j].value; }
+      }
+    }
+    return best_v;
+  };
+  int64_t run = 0;
+  int32_t pos = 0, c_bpos = 0, cidx = 0, best_n = 0, best_bytes = 0;
+  int phase = 0, depth = 0, first_l = 1;
+  uint32_t node = 0, best_node = 0;
+  uint64_t tmask = 0, best_window = 0;
+  bool pending = false;
+  while (phase != 3) {
+    const bool walking = phase == 1;
+    const int32_t cur = walking ? c_bpos : pos;
+    const bool have = cur < n;
+    uint32_t cp = 0;
+    int l = 1;
+    if (have) l = decode(cur, &cp);
+    const bool sep = have && sep_at(cp);
+    if (pending && (!use_sep || !have || sep)) {
+      best_node = node;
+      best_window = depth >= 64 ? tmask : (tmask & ((1ull << depth) - 1ull));
+      best_n = depth;
+      best_bytes = c_bpos - pos;
+    }
+    pending = false;
+    if (!walking && !have) break;
+    const bool skip = !walking && (phase == 2 || (use_sep && sep));
+    const bool start = !walking && !skip;
+    if (skip) { pos += l; ++cidx; if (sep) phase = 0; }
+    if (start) { phase = 1; depth = 0; node = 0; c_bpos = pos; tmask = 0; best_n = 0; first_l = l; }
+    const bool step = walking || start;
+    uint32_t e = 0;
+    bool upper = false;
+    if (step && have && depth < 64) {
+      upper = fold_is_upper(cp);
+      const uint32_t fc = upper ? cp + 32u : cp;
+      std::string enc;
+      fold_encode(fc, &enc);
+      e = fc ? node : 0u;
+      for (size_t j = 0; j < enc.size() && fc; ++j) {
+        e = F.delta[(size_t)(e & ~kFoldCand) * F.n_classes + F.cmap[(uint8_t)enc[j]]];
+        if (e == 0u) break;
+      }
+    }
+    const bool adv = e != 0u;
+    if (adv) {
+      node = e & ~kFoldCand;
+      c_bpos += l;
+      ++depth;
+      tmask = (tmask << 1) | (upper ? 1ull : 0ull);
+      pending = (e & kFoldCand) != 0u;
+    }
+    if (!step || adv) continue;
+    if (best_n == 0) {
+      pos += first_l;
+      ++cidx;
+      phase = use_sep ? 2 : 0;
+      continue;
+    }
+    if (hits && run < cap) hits[run] = aha_hit{cidx, cidx + best_n, pick(best_node, best_window)};
+    ++run;
+    pos += best_bytes;
+    cidx += best_n;
+    phase = 0;
+  }
+  *n_hits = run;
+  return AHA_OK;
+}
+
 }  // extern "C"
 
 #include "api_scan.cuh"

@@ -166,6 +166,15 @@ int32_t aha_b200_debug_set(int32_t knob, int32_t value);
  * Writes at most cap hits (byte offsets); *n_hits = number found.  No device needed.            */
 int32_t aha_b200_debug_char_scan(const uint8_t* blob, int64_t blob_bytes, const uint8_t* text, int64_t n, int32_t chunk,
                                  int64_t smem_budget, aha_hit* hits, int64_t cap, int64_t* n_hits, int64_t* info);
+/* Host-side replay of the case-folded trie walk behind CedarX#match_longest(ignore_case: true) (cedar.cr:984-1027,
+ * 1075-1121; aha_b200/csrc/folded_trie.hpp): the same table builder, state machine and candidate pick as the kernel,
+ * over ONE document; mode = AHA_TRIE_LONGEST | AHA_IGNORE_CASE [| AHA_SEP], sep_bits / sep_size as in aha_b200_scan.
+ * info[0] = 1 if the dictionary has a folded trie (keys <= 64 characters, valid UTF-8, table <= 256 MB),
+ * info[1..5] = folded nodes, byte classes, longest key in characters, candidates, nodes with an overflow record.
+ * Writes at most cap hits (character offsets); *n_hits = number found.  No device needed.       */
+int32_t aha_b200_debug_folded_longest(const uint8_t* blob, int64_t blob_bytes, const uint8_t* text, int64_t n, uint32_t mode,
+                                      const uint8_t* sep_bits, int32_t sep_size, aha_hit* hits, int64_t cap, int64_t* n_hits,
+                                      int64_t* info);
 
 /* ---- synthetic corpora: counter-based, identical bytes on host and device -- */
 enum aha_corpus { AHA_CORPUS_EN = 0, AHA_CORPUS_ZH = 1, AHA_CORPUS_MIX = 2 };

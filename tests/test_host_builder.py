@@ -241,3 +241,60 @@ def test_threaded_flatten_is_byte_identical(monkeypatch):
         monkeypatch.setenv("AHA_B200_FLATTEN_THREADS", "7")
         many = _blob_of(keys)
         assert len(one) > (1 << 22) and one == many
+
+
+def _folded_longest(blob, text, sep=None):
+    L = _lib.lib()
+    a = np.frombuffer(text, dtype=np.uint8)
+    cap = 1 << 18
+    hits = np.zeros(cap, dtype=aha_b200.HIT_DTYPE)
+    n, info = C.c_int64(), (C.c_int64 * 8)()
+    bl = np.frombuffer(blob, dtype=np.uint8)
+    mode = aha_b200.TRIE_LONGEST | aha_b200.IGNORE_CASE | (aha_b200.SEP if sep is not None else 0)
+    bits, size = O.sep_bits(sep) if sep is not None else (bytes(32), 0)
+    _lib.check(L.aha_b200_debug_folded_longest(bl.ctypes.data, bl.size, a.ctypes.data if a.size else None, a.size, mode, bits, size,
+                                               hits.ctypes.data, cap, C.byref(n), info))
+    return hits[: n.value], list(info)
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_folded_trie_replay_matches_oracle(seed):
+    """CedarX#match_longest(ignore_case: true) over the case-folded trie (table builder + walk + candidate pick, replayed
+    on the host) == the oracle's frontier walk (cedar.cr:984-1027, 1075-1121), keys that differ only in case included"""
+    rng = random.Random(100 + seed)
+    alpha = ["abAB", "abcABC ,", "aAbBéÉñÑ -", "αβγΑΒΓдДжЖ ab", "abAB日本 ", "xyXY"][seed % 6]
+    n_keys = rng.choice([6, 40, 300])
+    keys = list(dict.fromkeys("".join(rng.choice(alpha.replace(" ", "").replace(",", "").replace("-", "")) for _ in range(rng.randint(1, 6)))
+                              for _ in range(n_keys)))
+    if seed % 6 == 5:  # four and more case variants of one key under one folded node: the overflow records
+        keys += ["xyx", "Xyx", "xYx", "xyX", "XYx", "XyX", "xYX", "XYX"]
+        keys = list(dict.fromkeys(keys))
+    da, o = aha_b200.Cedar(), O.Cedar()
+    for k in keys:
+        da.insert(k)
+        o.insert(k)
+    nodes, fails, output, kl = da.compiled_arrays()
+    blob, n = C.c_void_p(), C.c_int64()
+    L = _lib.lib()
+    _lib.check(L.aha_b200_flatten_host(nodes.ctypes.data, len(fails), fails.ctypes.data, output.ctypes.data,
+                                       kl.ctypes.data if len(kl) else None, len(kl), C.byref(blob), C.byref(n)))
+    raw = C.string_at(blob.value, n.value)
+    L.aha_b200_blob_free(blob)
+    for trial in range(4):
+        text = "".join(rng.choice(alpha) for _ in range(rng.choice([0, 1, 50, 3000]))).encode()
+        for sep in (None, [" ", ",", "-"]):
+            got, info = _folded_longest(raw, text, sep)
+            assert info[0] == 1, info
+            want = o.match_longest(text, ignore_case=True, sep=sep)
+            assert got.tobytes() == want.tobytes(), (seed, trial, sep, len(got), len(want))
+    if seed % 6 == 5:
+        assert info[5] >= 1  # the eight variants share one node: its record is the overflow form
+
+
+def test_folded_trie_refuses_what_it_cannot_hold():
+    blob = _blob_of(["a" * 65, "b"])  # a key of more than 64 characters: the depth-first kernel keeps the dictionary
+    _, info = _folded_longest(blob, b"aaab")
+    assert info[0] == 0
+    blob = _blob_of([b"\xe4\xb8", b"ab"])  # a key that is not valid UTF-8
+    _, info = _folded_longest(blob, b"ab")
+    assert info[0] == 0
